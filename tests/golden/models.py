@@ -1,0 +1,100 @@
+"""Small seeded models shared by the golden generator (runs against the reference)
+and by the tests (run against this repo).  No dependency on either K-FAC package
+except for the LSTM case, which takes the LSTM class as an argument because the
+reference and this repo each ship their own ``kfac.modules.LSTM``."""
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+
+class SmallCNN(nn.Module):
+    """Covers every conv geometry class of ResNet-50 in miniature:
+    3x3 s1 p1 with bias, 3x3 s2 p1, 1x1 s1, 1x1 s2, 5x5 s2 p2 (conv1-like) and a
+    Linear with bias.  Non-square input (H != W) catches transposition bugs."""
+
+    def __init__(self):
+        super().__init__()
+        self.c1 = nn.Conv2d(3, 8, 5, stride=2, padding=2, bias=False)     # da=75
+        self.c2 = nn.Conv2d(8, 16, 3, stride=1, padding=1, bias=True)     # da=73
+        self.c3 = nn.Conv2d(16, 12, 1, stride=1, bias=False)              # da=16
+        self.c4 = nn.Conv2d(12, 20, 3, stride=2, padding=1, bias=False)   # da=108
+        self.c5 = nn.Conv2d(20, 24, 1, stride=2, bias=False)              # da=20
+        self.fc = nn.Linear(24, 10)                                       # da=25
+
+    def forward(self, x):
+        x = F.relu(self.c1(x))
+        x = F.relu(self.c2(x))
+        x = F.relu(self.c3(x))
+        x = F.relu(self.c4(x))
+        x = F.relu(self.c5(x))
+        x = F.adaptive_avg_pool2d(x, 1).flatten(1)
+        return self.fc(x)
+
+
+CNN_INPUT = (6, 3, 24, 20)      # N, C, H, W
+CNN_CLASSES = 10
+
+
+class SmallLSTMModel(nn.Module):
+    """Embedding -> K-FAC-friendly LSTM -> decoder, seq-first, like
+    examples/rnn_utils/lstm.py but tiny."""
+
+    def __init__(self, lstm_cls, ntoken=30, ninp=12, nhid=12):
+        super().__init__()
+        self.encoder = nn.Embedding(ntoken, ninp)
+        self.rnn = lstm_cls(ninp, nhid, num_layers=2, batch_first=False)
+        self.decoder = nn.Linear(nhid, ntoken)
+        self.ntoken = ntoken
+
+    def forward(self, tokens):
+        x = self.encoder(tokens)
+        x, _ = self.rnn(x)
+        return F.log_softmax(self.decoder(x).view(-1, self.ntoken), dim=1)
+
+
+LSTM_SEQ, LSTM_BATCH, LSTM_NTOKEN = 5, 4, 30
+
+
+def make_cnn(seed=0):
+    torch.manual_seed(seed)
+    return SmallCNN()
+
+
+def make_lstm(lstm_cls, seed=0):
+    torch.manual_seed(seed)
+    return SmallLSTMModel(lstm_cls)
+
+
+def cnn_batch(step, rank=0):
+    g = torch.Generator().manual_seed(1000 + 17 * step + 100 * rank)
+    x = torch.randn(*CNN_INPUT, generator=g)
+    y = torch.randint(0, CNN_CLASSES, (CNN_INPUT[0],), generator=g)
+    return x, y
+
+
+def lstm_batch(step, rank=0):
+    g = torch.Generator().manual_seed(2000 + 17 * step + 100 * rank)
+    x = torch.randint(0, LSTM_NTOKEN, (LSTM_SEQ, LSTM_BATCH), generator=g)
+    y = torch.randint(0, LSTM_NTOKEN, (LSTM_SEQ * LSTM_BATCH,), generator=g)
+    return x, y
+
+
+def resnet_factor_dims(name):
+    """(da, dg) per K-FAC layer of torchvision resnet50/152 in registration order
+    (kfac/preconditioner.py:382-402 walks named_children in definition order)."""
+    import torchvision
+    model = getattr(torchvision.models, name)()
+    dims = []
+
+    def walk(m):
+        for child in m.children():
+            cname = child.__class__.__name__.lower()
+            if cname == 'conv2d':
+                da = child.in_channels * child.kernel_size[0] * child.kernel_size[1]
+                dims.append((da + (child.bias is not None), child.out_channels))
+            elif cname == 'linear':
+                dims.append((child.in_features + (child.bias is not None), child.out_features))
+            else:
+                walk(child)
+    walk(model)
+    return dims
