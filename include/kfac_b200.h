@@ -1,0 +1,178 @@
+/*
+ * kfac_b200.h — C ABI of libkfac_b200.so, the B200 (sm_100a) implementation of the
+ * K-FAC preconditioner hot path of MLHPC/Distributed_KFAC_Pytorch.
+ *
+ * The reference is pure Python (no FFI of its own), so the "binding" a maintainer
+ * adds is the ctypes stub shown in INTEGRATION.md; each entry point below cites the
+ * reference function(s) it replaces as /root/reference file:line.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a kfb_status code otherwise;
+ *     kfb_last_error() returns a thread-local message for the last failure;
+ *   - all matrices are fp32, row-major, with an explicit row pitch `ld*` in ELEMENTS;
+ *   - device pointers are plain `void*` / `float*` (tensor.data_ptr()); `stream` is a
+ *     cudaStream_t passed as void* (0 = legacy default stream);
+ *   - job arrays live in HOST memory and are consumed before the call returns;
+ *   - nothing here allocates device memory: scratch comes from the caller, sized by
+ *     the matching *_workspace_bytes() function;
+ *   - calls are asynchronous with respect to the host unless stated otherwise.
+ */
+#ifndef KFAC_B200_H_
+#define KFAC_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  KFB_OK = 0,
+  KFB_ERR_INVALID = 1,     /* bad argument (null pointer, negative size, pitch too small ...) */
+  KFB_ERR_CUDA = 2,        /* a CUDA runtime/driver call failed; message has the cudaError string */
+  KFB_ERR_UNSUPPORTED = 3, /* shape outside what the kernels support */
+  KFB_ERR_CUSOLVER = 4,
+  KFB_ERR_WORKSPACE = 5    /* caller-provided workspace too small */
+} kfb_status;
+
+#define KFB_ABI_VERSION 1
+
+/* ---- library ------------------------------------------------------------------ */
+int kfb_version(void);
+const char* kfb_last_error(void);
+/* Create the per-device context (cuSOLVER handle, SM count, TMA driver entry point) for
+ * `device` and make it the context used by later calls from this thread. Idempotent. */
+int kfb_init(int device);
+/* Which code path the GEMM-shaped kernels use: 0 = SIMT fp32 (exact fp32 FMA, the
+ * first-correct path), 1 = tcgen05 TF32 tensor cores (default when available). */
+int kfb_set_mma_mode(int mode);
+int kfb_get_mma_mode(void);
+
+/* ---- factor computation + running average ------------------------------------------
+ * Replaces Conv2dLayer._get_A_factor/_get_G_factor/_extract_patches (kfac/layers/conv.py:24-70),
+ * LinearLayer / LinearMultiLayer._get_{A,G}_factor (kfac/layers/linear.py:12-59),
+ * append_bias_ones/get_cov/reshape_data (kfac/layers/utils.py:4-43,107-124),
+ * update_running_avg (kfac/layers/utils.py:164-178) and the identity seed of
+ * KFACLayer.update_{A,G}_factor (kfac/layers/base.py:381-417).
+ *
+ * A factor is   F = sum_segments weight_s * X_s^T X_s   (upper triangle computed, mirrored),
+ * followed by   state <- (state * alpha/(1-alpha) + F) * (1-alpha)    (skipped when alpha == 1).
+ * X_s is never materialised; it is read through one of three layouts: */
+enum {
+  KFB_SEG_ROWS = 0,   /* X[r][f] = data[r*ld + f], r < n, f < c  (Linear a / g, any leading dims collapsed) */
+  KFB_SEG_NCHW = 1,   /* X[(i,s)][f] = data[(i*c + f)*h*w + s], i < n, s < h*w  (conv grad_output; 1x1/s1 conv input) */
+  KFB_SEG_IM2COL = 2  /* X[(i,oy,ox)][(f,ky,kx)] = data[i][f][oy*sh+ky-ph][ox*sw+kx-pw], 0 outside  (conv input) */
+};
+
+typedef struct kfb_segment {
+  int32_t kind;
+  int32_t has_bias;      /* 1: X has one extra trailing feature that is constant 1 (ROWS, IM2COL) */
+  const float* data;
+  int64_t n;             /* ROWS: row count; NCHW / IM2COL: batch size */
+  int64_t c;             /* feature / channel count (without the bias feature) */
+  int64_t h, w;          /* NCHW: spatial extent; IM2COL: INPUT height and width */
+  int32_t kh, kw, sh, sw, ph, pw;   /* IM2COL kernel, stride, padding */
+  int64_t ld;            /* ROWS: row pitch in elements */
+  float weight;          /* e.g. 1/(N*S^3) for conv, 1/M for linear */
+  int32_t reserved;
+} kfb_segment;
+
+typedef struct kfb_factor_job {
+  int32_t d;                     /* factor dimension, = c*kh*kw + has_bias */
+  int32_t n_segments;
+  const kfb_segment* segments;   /* host array */
+  float* state;                  /* d x d running average, pitch ld_state */
+  int64_t ld_state;
+  int32_t seed_identity;         /* 1: treat the old state as the identity (first update) */
+  int32_t write_state;           /* 1: write the full (mirrored) square into state */
+  float* tri_out;                /* NULL, or d(d+1)/2 floats: packed upper triangle (row by row) of the
+                                    new state - a slot of the caller's allreduce fusion buffer */
+} kfb_factor_job;
+
+size_t kfb_factor_workspace_bytes(const kfb_factor_job* jobs, int32_t n_jobs);
+int kfb_factor_update(const kfb_factor_job* jobs, int32_t n_jobs, float alpha,
+                      void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- packed-triangle fusion buffer ----------------------------------------------------
+ * Replaces get_triu / fill_triu (kfac/layers/utils.py:126-162) and the deferred
+ * `tensor /= world` of TorchBackend.sync (kfac/comm.py:254-262). */
+typedef struct kfb_tri_job {
+  float* tri;          /* d(d+1)/2 */
+  float* state;        /* d x d, pitch ld_state */
+  int64_t ld_state;
+  int32_t d;
+  int32_t reserved;
+} kfb_tri_job;
+/* state <- scale * unpack(tri), both triangles */
+int kfb_tri_unpack(const kfb_tri_job* jobs, int32_t n_jobs, float scale, void* stream);
+/* tri <- upper triangle of state */
+int kfb_tri_pack(const kfb_tri_job* jobs, int32_t n_jobs, void* stream);
+
+/* ---- eigendecomposition (the one library call: cuSOLVER syevd) ----------------------------
+ * Replaces get_eigendecomp (kfac/layers/utils.py:45-74) as used by
+ * KFACLayer._compute_factor_inverse (kfac/layers/base.py:432-441): eigenvalues are clipped
+ * at 0.  Outputs: E (rows are eigenvectors, E = Q^T), Q (columns are eigenvectors, the
+ * reference's state['QA'|'QG']) and w.  `factor` is not modified. `dev_info` is a device
+ * int32 written by cuSOLVER (0 = converged); the call does not synchronise. */
+size_t kfb_syevd_workspace_bytes(int32_t d);
+int kfb_syevd(const float* factor, int64_t ld_factor, int32_t d,
+              float* E, int64_t ld_e, float* Q, int64_t ld_q, float* w,
+              void* workspace, size_t workspace_bytes, int32_t* dev_info, void* stream);
+/* out <- in^T  (receivers of a broadcast Q rebuild E) */
+int kfb_transpose(const float* in, int64_t ld_in, int32_t rows, int32_t cols,
+                  float* out, int64_t ld_out, void* stream);
+/* out[i][j] = 1 / (dG[i]*dA[j] + damping)    (kfac/layers/base.py:305-306) */
+int kfb_outer_recip(const float* dG, const float* dA, int32_t dg, int32_t da, float damping,
+                    float* out, int64_t ld_out, void* stream);
+
+/* ---- preconditioning -------------------------------------------------------------------
+ * Replaces KFACLayer.get_gradient (kfac/layers/base.py:310-319, conv.py:17-22),
+ * _get_precondition_gradient_eigen (base.py:459-470) and the per-layer `.sum().item()` of
+ * KFAC._compute_grad_scale (kfac/preconditioner.py:661-682).
+ *
+ *   gmat = [weight_grad.view(dg,-1) | bias_grad]
+ *   out  = QG ((QG^T gmat QA) * dGdA) QA^T
+ *   *vg_acc += sum(out * gmat)          (device scalar, NOT multiplied by lr^2)
+ *
+ * run as four grouped "TN" GEMM stages over all jobs (D[m][n] = sum_k A[m][k] B[n][k]):
+ *   T = EA gmat^T ; V = (EG T^T) * dGdA ; T = QA V^T ; out = QG T^T.            */
+typedef struct kfb_precond_job {
+  int32_t da, dg;          /* da includes the bias column */
+  int32_t has_bias;
+  int32_t reserved;
+  const float* weight_grad;   /* contiguous [dg][da - has_bias] */
+  const float* bias_grad;     /* [dg] or NULL */
+  const float* EA; const float* QA; int64_t ld_a;   /* da x da */
+  const float* EG; const float* QG; int64_t ld_g;   /* dg x dg */
+  const float* dGdA; int64_t ld_dgda;               /* dg x da */
+  float* gmat; float* V; float* out; int64_t ld_v;  /* dg x da each, same pitch */
+  float* T; int64_t ld_t;                           /* da x dg */
+} kfb_precond_job;
+int kfb_precondition(const kfb_precond_job* jobs, int32_t n_jobs, float* vg_acc, void* stream);
+
+/* *vg_acc += sum_jobs sum(v * [weight_grad | bias_grad])   — for layers whose preconditioned
+ * gradient arrived by broadcast (MEM_OPT / HYBRID_OPT). */
+typedef struct kfb_grad_job {
+  float* weight_grad;      /* contiguous [dg][da - has_bias] */
+  float* bias_grad;        /* [dg] or NULL */
+  const float* v;          /* dg x da preconditioned gradient, pitch ld_v */
+  int64_t ld_v;
+  int32_t da, dg, has_bias;
+  int32_t reserved;
+} kfb_grad_job;
+int kfb_dot_accumulate(const kfb_grad_job* jobs, int32_t n_jobs, float* vg_acc, void* stream);
+
+/* Replaces KFAC.update_gradients / KFACLayer.update_gradient / _set_*_grad
+ * (kfac/preconditioner.py:587-590, kfac/layers/base.py:419-430,477-483) and the scalar part of
+ * _compute_grad_scale: writes nu * v into weight_grad / bias_grad IN PLACE, where
+ *   nu = min(1, sqrt(kl_clip / |*vg_acc * lr^2|))   if vg_acc != NULL and *vg_acc != 0,
+ *   nu = fixed_scale                                otherwise.
+ * No host synchronisation. */
+int kfb_scale_writeback(const kfb_grad_job* jobs, int32_t n_jobs, const float* vg_acc,
+                        float lr, float kl_clip, float fixed_scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KFAC_B200_H_ */

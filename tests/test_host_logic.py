@@ -1,0 +1,268 @@
+"""Host logic of the drop-in package on CPU: the native ops are replaced by the
+oracle-backed stand-in (tests/_cpu_ops.py), everything else is the product code.
+Checked against fixtures produced by the unmodified reference (tests/golden)."""
+import json
+import os
+import warnings
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from conftest import GOLDEN, load_golden
+import models
+import distributed_kfac_pytorch_b200 as kfac
+from distributed_kfac_pytorch_b200 import _native, comm, utils
+from _cpu_ops import OracleOps
+
+GRAD_TOL = dict(rtol=1e-2, atol=1e-4)      # north_star: preconditioned gradients
+FACTOR_TOL = dict(rtol=1e-3, atol=1e-6)    # north_star: factors
+
+
+@pytest.fixture()
+def cpu_ops():
+    ops = OracleOps()
+    _native.set_ops(ops)
+    comm.reset_comm_backend()
+    yield ops
+    _native.set_ops(None)
+    comm.reset_comm_backend()
+
+
+def _run_like_golden(rec, model, batch_fn, loss_fn, kfac_kwargs):
+    model.load_state_dict(rec['init_state'])
+    opt = torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.9)
+    pre = kfac.KFAC(model, **kfac_kwargs)
+    for s, gold in enumerate(rec['steps']):
+        x, y = batch_fn(s)
+        opt.zero_grad()
+        loss = loss_fn(model(x), y)
+        loss.backward()
+        assert abs(loss.item() - gold['loss']) < 1e-3 * max(1.0, abs(gold['loss']))
+        pre.step()
+        for i, layer in enumerate(pre.layers):
+            torch.testing.assert_close(layer.state['A'], gold['A'][i], **FACTOR_TOL)
+            torch.testing.assert_close(layer.state['G'], gold['G'][i], **FACTOR_TOL)
+            w, b = gold['grads_out'][i]
+            torch.testing.assert_close(layer.module.weight.grad, w, **GRAD_TOL)
+            if b is not None:
+                torch.testing.assert_close(layer.module.bias.grad, b, **GRAD_TOL)
+        opt.step()
+    return pre
+
+
+def test_cnn_matches_reference(cpu_ops):
+    rec = load_golden('cnn_single.pt')
+    pre = _run_like_golden(rec, models.make_cnn(), models.cnn_batch, F.cross_entropy,
+                           rec['kfac_kwargs'])
+    assert [repr(l) for l in pre.layers] == rec['layer_reprs']
+    assert sorted(pre.state_dict().keys()) == rec['state_dict_keys']
+    # one native call per stage, not per layer
+    assert ('factor_update', 12) in cpu_ops.calls and ('precondition', 6) in cpu_ops.calls
+
+
+def test_lstm_matches_reference(cpu_ops):
+    rec = load_golden('lstm_single.pt')
+    pre = _run_like_golden(rec, models.make_lstm(kfac.modules.LSTM), models.lstm_batch,
+                           F.nll_loss, rec['kfac_kwargs'])
+    assert len(pre.layers) == 4
+    assert all(l.__class__.__name__ == 'LinearMultiLayer' for l in pre.layers)
+
+
+def test_state_dict_roundtrip_and_layout(cpu_ops):
+    rec = load_golden('cnn_single.pt')
+    pre = _run_like_golden(rec, models.make_cnn(), models.cnn_batch, F.cross_entropy,
+                           rec['kfac_kwargs'])
+    sd = pre.state_dict()
+    assert len(sd['layers']) == 6
+    for entry, layer in zip(sd['layers'], pre.layers):
+        assert set(entry.keys()) == {'A', 'G'}
+        assert entry['A'].shape == (layer.state['A'].shape[0],) * 2
+        assert entry['A'].dtype == torch.float32
+    # legacy key names are accepted (kfac/layers/base.py:64-68)
+    legacy = dict(sd)
+    legacy['layers'] = [{'A_factor': e['A'].clone(), 'G_factor': e['G'].clone()} for e in sd['layers']]
+    model2 = models.make_cnn()
+    pre2 = kfac.KFAC(model2, **rec['kfac_kwargs'])
+    pre2.load_state_dict(legacy)
+    assert pre2.param_groups[0]['step'] == pre.param_groups[0]['step']
+    for a, b in zip(pre.layers, pre2.layers):
+        torch.testing.assert_close(a.state['A'], b.state['A'], rtol=0, atol=0)
+        assert 'QA' in b.state and 'dGdA' in b.state     # inverses recomputed on load
+    with pytest.raises(ValueError):
+        bad = dict(sd)
+        bad['layers'] = sd['layers'][:-1]
+        pre2.load_state_dict(bad)
+
+
+def test_argument_validation(cpu_ops):
+    m = models.make_cnn()
+    for kw in (dict(lr=-1), dict(factor_decay=0), dict(factor_decay=1.5), dict(damping=0),
+               dict(kl_clip=0), dict(factor_update_freq=0), dict(inv_update_freq=0),
+               dict(assignment_strategy='x')):
+        with pytest.raises(ValueError):
+            kfac.KFAC(m, **kw)
+    with pytest.warns(UserWarning):
+        p = kfac.KFAC(m, comm_method=kfac.CommMethod.MEM_OPT)
+    assert p.distribute_layer_factors is False and p.grad_worker_fraction == 0
+    p = kfac.KFAC(models.make_cnn(), skip_layers='Linear')
+    assert len(p.layers) == 5
+    assert 'registered_layers: 5' in repr(p)
+    with pytest.raises(RuntimeError):
+        p.layers[0].update_gradient()
+    with pytest.raises(ValueError):
+        p.layers[0].compute_A_inv()
+
+
+def test_eval_and_off_steps_do_not_capture(cpu_ops):
+    m = models.make_cnn()
+    p = kfac.KFAC(m, factor_update_freq=2, inv_update_freq=2)
+    x, y = models.cnn_batch(0)
+    with torch.no_grad():
+        m(x)
+    assert all(len(l.a_inputs) == 0 for l in p.layers)
+    F.cross_entropy(m(x), y).backward()
+    assert all(len(l.a_inputs) == 1 and len(l.g_outputs) == 1 for l in p.layers)
+    p.step()
+    assert all(len(l.a_inputs) == 0 for l in p.layers)
+    m.zero_grad()
+    F.cross_entropy(m(x), y).backward()      # step 1: not a factor step
+    assert all(len(l.a_inputs) == 0 and len(l.g_outputs) == 0 for l in p.layers)
+
+
+def test_scheduler(cpu_ops):
+    p = kfac.KFAC(models.make_cnn(), damping=0.01, factor_update_freq=10, inv_update_freq=100)
+    s = kfac.KFACParamScheduler(p, damping_alpha=0.5, damping_schedule=[2, 4],
+                                update_freq_alpha=2, update_freq_schedule=[3])
+    vals = []
+    for _ in range(5):
+        s.step()
+        g = p.param_groups[0]
+        vals.append((round(g['damping'], 6), g['factor_update_freq'], g['inv_update_freq']))
+    assert vals == [(0.01, 10, 100), (0.005, 10, 100), (0.005, 20, 200), (0.0025, 20, 200),
+                    (0.0025, 20, 200)]
+    sd = s.state_dict()
+    assert 'kfac' not in sd and not any('func' in k for k in sd)
+
+
+def test_lr_scheduler_wraps_kfac(cpu_ops):
+    p = kfac.KFAC(models.make_cnn(), lr=0.1)
+    sched = torch.optim.lr_scheduler.LambdaLR(p, lambda e: 0.5 ** e)
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        sched.step()
+    assert abs(p.param_groups[0]['lr'] - 0.05) < 1e-12
+
+
+# ---- placement: bit-exact -------------------------------------------------------
+
+def test_utils_kats():
+    from test_oracle_vs_golden import LOAD_BALANCE_KATS, GRAD_RANK_KATS, INV_RANK_KATS
+    for n, work, expected in LOAD_BALANCE_KATS:
+        assert utils.load_balance(n, work) == expected
+    with pytest.raises(ValueError):
+        utils.load_balance(1, [])
+    for args, expected in GRAD_RANK_KATS:
+        assert utils.partition_grad_ranks(*args) == expected
+    for args, expected in INV_RANK_KATS:
+        assert utils.partition_inv_ranks(*args) == expected
+    assert utils.get_block_boundary(1, 2, [4, 6]) == ([2, 3], [4, 6])
+    with pytest.raises(ValueError):
+        utils.get_block_boundary(2, 2, [4, 4])
+
+
+def test_placement_matches_reference_bit_exact():
+    comm.reset_comm_backend()
+    comm.init_comm_backend()
+    with open(os.path.join(GOLDEN, 'allocator.json')) as f:
+        gold = json.load(f)
+    for name in ('resnet50', 'resnet152'):
+        dims = gold['load_balance'][name + '/dims']
+        for strategy, p in (('compute', 3), ('memory', 2)):
+            for world in (2, 4, 8):
+                costs = [a ** p + g ** p for a, g in dims]
+                assert utils.load_balance(world, costs) == \
+                    gold['load_balance']['%s/%s/W%d' % (name, strategy, world)]['locs']
+    for key, ref in gold['groups'].items():
+        world, frac = key.split('/')
+        world, frac = int(world[1:]), float(frac[1:])
+        if 'error' in ref:
+            with pytest.raises(ValueError):
+                utils.WorkerAllocator(world, frac)
+            continue
+        alloc = utils.WorkerAllocator(world, frac)
+        assert alloc.bcast_grad_ranks == ref['grad_ranks']
+        assert alloc.bcast_inv_ranks == ref['inv_ranks']
+        for inv_rank, r in ref['per_inv_rank'].items():
+            src = alloc.get_inv_ranks(int(inv_rank))
+            assert src == r['inv_ranks']
+            assert [[s, g.ranks] for s, g in alloc.get_grad_groups(src)] == r['grad_src_group']
+    comm.reset_comm_backend()
+
+
+# ---- two ranks over gloo ----------------------------------------------------------
+
+def _world2_worker(rank, world, port, method_name, fraction, out_path):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port), LOCAL_RANK=str(rank))
+    torch.set_num_threads(1)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    _native.set_ops(OracleOps())
+    comm.reset_comm_backend()
+    model = models.make_cnn()
+    ddp = torch.nn.parallel.DistributedDataParallel(model)
+    opt = torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.9)
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        pre = kfac.KFAC(model, comm_method=getattr(kfac.CommMethod, method_name),
+                        grad_worker_fraction=fraction, distribute_layer_factors=False,
+                        damping=0.003, factor_decay=0.95, factor_update_freq=1,
+                        inv_update_freq=1, kl_clip=0.001, lr=0.1)
+    steps = []
+    for s in range(3):
+        x, y = models.cnn_batch(s, rank)
+        opt.zero_grad()
+        F.cross_entropy(ddp(x), y).backward()
+        pre.step()
+        steps.append({'grads_out': [(l.module.weight.grad.clone(),
+                                     None if l.module.bias is None else l.module.bias.grad.clone())
+                                    for l in pre.layers],
+                      'A': [l.state['A'].clone() for l in pre.layers],
+                      'G': [l.state['G'].clone() for l in pre.layers]})
+        opt.step()
+    assign = [{'a_rank': l.compute_A_inv_rank, 'g_rank': l.compute_G_inv_rank,
+               'grad_ranks': list(l.compute_grad_ranks),
+               'grad_src_group': [(src, list(grp.ranks)) for src, grp in l.broadcast_grad_groups]}
+              for l in pre.layers]
+    held = [sorted(k for k, v in l.state.items() if v is not None) for l in pre.layers]
+    torch.save({'steps': steps, 'assign': assign, 'held': held}, out_path % rank)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('idx,method,fraction', [(0, 'COMM_OPT', 1.0), (1, 'MEM_OPT', 0.0),
+                                                 (2, 'HYBRID_OPT', 0.5)])
+def test_world2_gloo_matches_reference(tmp_path, idx, method, fraction):
+    import torch.multiprocessing as mp
+    gold = load_golden('cnn_world2.pt')[method]
+    out = str(tmp_path / 'rank%d.pt')
+    mp.spawn(_world2_worker, args=(2, 29711 + idx, method, fraction, out), nprocs=2, join=True)
+    ranks = [torch.load(out % r, weights_only=False) for r in range(2)]
+    for r in ranks:
+        assert r['assign'] == gold['assign']          # worker-to-layer assignment: bit-exact
+        for s in range(3):
+            for i in range(6):
+                torch.testing.assert_close(r['steps'][s]['A'][i], gold['steps'][s]['A'][i], **FACTOR_TOL)
+                torch.testing.assert_close(r['steps'][s]['G'][i], gold['steps'][s]['G'][i], **FACTOR_TOL)
+                torch.testing.assert_close(r['steps'][s]['grads_out'][i][0],
+                                           gold['steps'][s]['grads_out'][i][0], **GRAD_TOL)
+    # both ranks end with the same gradients
+    for i in range(6):
+        torch.testing.assert_close(ranks[0]['steps'][2]['grads_out'][i][0],
+                                   ranks[1]['steps'][2]['grads_out'][i][0], rtol=1e-5, atol=1e-7)
+    if method == 'MEM_OPT':
+        # only the inverse rank holds a layer's eigenvectors (memory story of SURVEY §8c)
+        for i, a in enumerate(gold['assign']):
+            for rank in range(2):
+                has = 'QA' in ranks[rank]['held'][i]
+                assert has == (rank == a['a_rank'])
