@@ -1,0 +1,86 @@
+// Shared host/device helpers for libkfac_b200.so (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/kfac_b200.h"
+
+#define KFB_HIDDEN __attribute__((visibility("hidden")))
+
+namespace kfb {
+
+// ---- error reporting -----------------------------------------------------------------
+KFB_HIDDEN void set_error(const char* fmt, ...);
+KFB_HIDDEN const char* get_error();
+
+#define KFB_FAIL(code, ...)           \
+  do {                                \
+    ::kfb::set_error(__VA_ARGS__);    \
+    return (code);                    \
+  } while (0)
+
+#define KFB_CUDA(expr)                                                                   \
+  do {                                                                                   \
+    cudaError_t _e = (expr);                                                             \
+    if (_e != cudaSuccess) {                                                             \
+      ::kfb::set_error("%s failed at %s:%d: %s", #expr, __FILE__, __LINE__,              \
+                       cudaGetErrorString(_e));                                          \
+      return KFB_ERR_CUDA;                                                               \
+    }                                                                                    \
+  } while (0)
+
+#define KFB_CHECK_LAUNCH() KFB_CUDA(cudaGetLastError())
+
+#define KFB_REQUIRE(cond, ...)                      \
+  do {                                              \
+    if (!(cond)) KFB_FAIL(KFB_ERR_INVALID, __VA_ARGS__); \
+  } while (0)
+
+// ---- per-device context ----------------------------------------------------------------
+struct Context {
+  int device = -1;
+  int num_sms = 0;
+  int cc_major = 0, cc_minor = 0;
+  void* cusolver = nullptr;       // cusolverDnHandle_t
+  void* encode_tiled = nullptr;   // cuTensorMapEncodeTiled entry point (driver API, via cudart)
+  bool umma_ok = false;           // sm_100 device and TMA entry point available
+};
+
+KFB_HIDDEN Context* current_context();          // context selected by the last kfb_init on this thread
+KFB_HIDDEN int require_context(Context** out);  // KFB_OK or error if kfb_init was never called
+KFB_HIDDEN int mma_mode();                      // 0 SIMT, 1 tcgen05
+
+static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
+static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+// ---- batched launches ---------------------------------------------------------------------
+// Job descriptors travel as a by-value kernel parameter (CUDA >= 12.1 allows ~32 KB), so a
+// whole stage over all layers is ONE launch with no descriptor upload.  `start[i]` is the
+// first block of job i; blocks find their job with a binary search.
+template <typename Job, int kMaxJobs>
+struct Batch {
+  int n;
+  int start[kMaxJobs + 1];
+  Job jobs[kMaxJobs];
+};
+
+template <typename BatchT>
+__device__ __forceinline__ int find_job(const BatchT& b, int block) {
+  int lo = 0, hi = b.n;   // invariant: start[lo] <= block < start[hi]
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (b.start[mid] <= block) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+}  // namespace kfb

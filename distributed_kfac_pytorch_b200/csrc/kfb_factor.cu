@@ -1,0 +1,502 @@
+// Factor computation: symmetric rank-k update over implicitly-unfolded activations, split-K
+// accumulation into caller scratch, and a finalize pass that fuses the scale, the running
+// average, the mirror and the packed-triangle export.
+//
+// This file holds the host planning, the SIMT fp32 SYRK (exact-fp32 path, also the path for
+// shapes the tensor-core kernel does not take) and the finalize / pack / unpack kernels.
+// The tcgen05 SYRK lives in kfb_syrk_tc.cu and writes the same scratch convention.
+#include <algorithm>
+#include <vector>
+
+#include "kfb_factor.cuh"
+
+namespace kfb {
+
+// ============================================================================================
+// SIMT SYRK: one CTA = one 64x64 upper-triangle tile pair x one K chunk of one segment
+// ============================================================================================
+namespace {
+
+constexpr int TS = 64;     // tile side
+constexpr int BK = 32;     // K step
+constexpr int NT = 256;    // threads
+
+struct IDecode {           // decode of a feature index for IM2COL
+  int off;                 // ci*h*w + ky*w + kx
+  int ky, kx;
+  int valid;               // 0: index >= d (padding), 1: data, 2: bias column
+};
+
+__device__ __forceinline__ IDecode decode_feature(const DevSegment& s, int d, int i) {
+  IDecode r;
+  r.off = 0; r.ky = 0; r.kx = 0;
+  if (i >= d) { r.valid = 0; return r; }
+  if (s.has_bias && i == d - 1) { r.valid = 2; return r; }
+  r.valid = 1;
+  if (s.kind == KFB_SEG_IM2COL) {
+    int khw = s.kh * s.kw;
+    int ci = i / khw;
+    int q = i - ci * khw;
+    r.ky = q / s.kw;
+    r.kx = q - r.ky * s.kw;
+    r.off = (ci * s.h + r.ky) * s.w + r.kx;
+  } else if (s.kind == KFB_SEG_NCHW) {
+    r.off = i * s.h * s.w;
+  } else {
+    r.off = i;
+  }
+  return r;
+}
+
+// Loads a BK x TS operand tile: dst[kk][ii] = X[k0+kk][i0+ii] (0 outside).
+__device__ __forceinline__ void load_tile(const DevSegment& s, int d, int64_t k0, int64_t k_end,
+                                          const IDecode* dec /*8 per thread, K-major map*/,
+                                          int i0, float (*dst)[TS + 1]) {
+  const int t = threadIdx.x;
+  if (s.kind == KFB_SEG_ROWS) {
+    // features are contiguous: lanes run along ii
+    const int ii = t & (TS - 1);
+    const int i = i0 + ii;
+    const bool bias = s.has_bias && i == d - 1;
+    const bool in = i < d;
+#pragma unroll
+    for (int j = 0; j < BK / (NT / TS); ++j) {
+      int kk = (t >> 6) + j * (NT / TS);
+      int64_t k = k0 + kk;
+      float v = 0.f;
+      if (in && k < k_end) v = bias ? 1.f : __ldg(s.data + k * s.ld + i);
+      dst[kk][ii] = v;
+    }
+  } else {
+    // rows (k) are contiguous in memory: lanes run along kk
+    const int kk = t & (BK - 1);
+    const int64_t k = k0 + kk;
+    const bool kin = k < k_end;
+    const int S = s.oh * s.ow;
+    int64_t base = 0;
+    int y0 = 0, x0 = 0;
+    if (kin) {
+      int64_t n = k / S;
+      int r = (int)(k - n * S);
+      if (s.kind == KFB_SEG_NCHW) {
+        base = n * (int64_t)s.c * S + r;
+      } else {
+        int oy = r / s.ow;
+        int ox = r - oy * s.ow;
+        y0 = oy * s.sh - s.ph;
+        x0 = ox * s.sw - s.pw;
+        base = n * (int64_t)s.c * s.h * s.w + (int64_t)y0 * s.w + x0;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < TS / (NT / BK); ++j) {
+      int ii = (t >> 5) + j * (NT / BK);
+      const IDecode& e = dec[j];
+      float v = 0.f;
+      if (kin && e.valid) {
+        if (e.valid == 2) {
+          v = 1.f;
+        } else if (s.kind == KFB_SEG_NCHW) {
+          v = __ldg(s.data + base + e.off);
+        } else {
+          int y = y0 + e.ky, x = x0 + e.kx;
+          if (y >= 0 && y < s.h && x >= 0 && x < s.w) v = __ldg(s.data + base + e.off);
+        }
+      }
+      dst[kk][ii] = v;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(NT) syrk_simt_kernel(const DevJob* __restrict__ jobs,
+                                                      const DevSegment* __restrict__ segs,
+                                                      const int* __restrict__ item_start,
+                                                      int n_jobs) {
+  __shared__ float As[BK][TS + 1];
+  __shared__ float Bs[BK][TS + 1];
+
+  // ---- which work item am I
+  int lo = 0, hi = n_jobs;
+  const int b = blockIdx.x;
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (item_start[mid] <= b) lo = mid; else hi = mid;
+  }
+  const DevJob job = jobs[lo];
+  int local = b - item_start[lo];
+  int pair = local % job.n_pairs;
+  int chunk = local / job.n_pairs;
+  // pair -> (ti, tj), ti <= tj, row-major over the upper triangle
+  int ti = 0, rem = pair, rowlen = job.T;
+  while (rem >= rowlen) { rem -= rowlen; --rowlen; ++ti; }
+  int tj = ti + rem;
+  // chunk -> segment
+  int sidx = job.seg_start;
+  while (chunk >= segs[sidx].chunk_start + segs[sidx].n_chunks) ++sidx;
+  const DevSegment s = segs[sidx];
+  chunk -= s.chunk_start;
+  const int64_t k_begin = (int64_t)chunk * s.chunk_len;
+  const int64_t k_end = min(s.K, k_begin + s.chunk_len);
+  const int d = job.d;
+  const int i0 = ti * TS, j0 = tj * TS;
+  const bool diag = ti == tj;
+
+  IDecode decA[8], decB[8];
+  if (s.kind != KFB_SEG_ROWS) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      int ii = (threadIdx.x >> 5) + j * 8;
+      decA[j] = decode_feature(s, d, i0 + ii);
+      decB[j] = decode_feature(s, d, j0 + ii);
+    }
+  }
+
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  float acc[4][4];
+#pragma unroll
+  for (int p = 0; p < 4; ++p)
+#pragma unroll
+    for (int q = 0; q < 4; ++q) acc[p][q] = 0.f;
+
+  float (*Bt)[TS + 1] = diag ? As : Bs;
+  for (int64_t k0 = k_begin; k0 < k_end; k0 += BK) {
+    load_tile(s, d, k0, k_end, decA, i0, As);
+    if (!diag) load_tile(s, d, k0, k_end, decB, j0, Bs);
+    __syncthreads();
+#pragma unroll 8
+    for (int kk = 0; kk < BK; ++kk) {
+      float a[4], bb[4];
+#pragma unroll
+      for (int p = 0; p < 4; ++p) a[p] = As[kk][ty * 4 + p];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) bb[q] = Bt[kk][tx * 4 + q];
+#pragma unroll
+      for (int p = 0; p < 4; ++p)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) acc[p][q] = fmaf(a[p], bb[q], acc[p][q]);
+    }
+    __syncthreads();
+  }
+
+#pragma unroll
+  for (int p = 0; p < 4; ++p) {
+    int i = i0 + ty * 4 + p;
+    if (i >= d) continue;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      int j = j0 + tx * 4 + q;
+      if (j >= d || j < i) continue;
+      atomicAdd(job.scratch + (int64_t)i * job.ld_scratch + j, acc[p][q] * s.weight);
+    }
+  }
+}
+
+// ============================================================================================
+// finalize: new = (old * alpha/(1-alpha) + F) * (1-alpha); mirror; optional packed export
+// ============================================================================================
+__global__ void __launch_bounds__(256) finalize_kernel(const DevJob* __restrict__ jobs,
+                                                      const int* __restrict__ fin_start,
+                                                      int n_jobs, float alpha) {
+  __shared__ float tile[32][33];
+  int lo = 0, hi = n_jobs;
+  const int b = blockIdx.x;
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (fin_start[mid] <= b) lo = mid; else hi = mid;
+  }
+  const DevJob job = jobs[lo];
+  int rem = b - fin_start[lo], rowlen = job.T32, bi = 0;
+  while (rem >= rowlen) { rem -= rowlen; --rowlen; ++bi; }
+  const int bj = bi + rem;
+  const int d = job.d;
+  const float ratio = alpha / (1.f - alpha);
+  const float one_m = 1.f - alpha;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
+
+  // pass 1: rows of the (bi, bj) block; value valid where j >= i
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    int li = ty + r * 8;
+    int i = bi * 32 + li, j = bj * 32 + tx;
+    float v = 0.f;
+    if (i < d && j < d && j >= i) {
+      float f = job.scratch[(int64_t)i * job.ld_scratch + j];
+      float old = job.seed_identity ? (i == j ? 1.f : 0.f) : job.state[(int64_t)i * job.ld_state + j];
+      v = (old * ratio + f) * one_m;
+      if (job.tri_out) job.tri_out[(int64_t)i * d - ((int64_t)i * (i - 1)) / 2 + (j - i)] = v;
+    }
+    tile[li][tx] = v;
+  }
+  __syncthreads();
+  if (!job.write_state) return;
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    int li = ty + r * 8;
+    int i = bi * 32 + li, j = bj * 32 + tx;
+    if (i < d && j < d) {
+      // diagonal block: the strictly-lower part comes from the transposed element
+      float v = (j >= i) ? tile[li][tx] : tile[tx][li];
+      job.state[(int64_t)i * job.ld_state + j] = v;
+    }
+    if (bi != bj) {   // mirrored block (bj, bi): element (bj*32+li, bi*32+tx) = tile[tx][li]
+      int mi = bj * 32 + li, mj = bi * 32 + tx;
+      if (mi < d && mj < d) job.state[(int64_t)mi * job.ld_state + mj] = tile[tx][li];
+    }
+  }
+}
+
+// ============================================================================================
+// packed upper triangle <-> full symmetric square
+// ============================================================================================
+struct TriJob {
+  float* tri;
+  float* state;
+  int64_t ld;
+  int d, T32;
+};
+constexpr int kTriBatch = 512;
+typedef Batch<TriJob, kTriBatch> TriBatch;
+
+template <bool kUnpack>
+__global__ void __launch_bounds__(256) tri_kernel(const __grid_constant__ TriBatch batch, float scale) {
+  __shared__ float tile[32][33];
+  const int jidx = find_job(batch, blockIdx.x);
+  const TriJob job = batch.jobs[jidx];
+  int rem = blockIdx.x - batch.start[jidx], rowlen = job.T32, bi = 0;
+  while (rem >= rowlen) { rem -= rowlen; --rowlen; ++bi; }
+  const int bj = bi + rem;
+  const int d = job.d;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    int li = ty + r * 8;
+    int i = bi * 32 + li, j = bj * 32 + tx;
+    float v = 0.f;
+    if (i < d && j < d && j >= i) {
+      int64_t o = (int64_t)i * d - ((int64_t)i * (i - 1)) / 2 + (j - i);
+      if (kUnpack) {
+        v = job.tri[o] * scale;
+      } else {
+        job.tri[o] = job.state[(int64_t)i * job.ld + j];
+      }
+    }
+    tile[li][tx] = v;
+  }
+  if (!kUnpack) return;
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    int li = ty + r * 8;
+    int i = bi * 32 + li, j = bj * 32 + tx;
+    if (i < d && j < d) job.state[(int64_t)i * job.ld + j] = (j >= i) ? tile[li][tx] : tile[tx][li];
+    if (bi != bj) {
+      int mi = bj * 32 + li, mj = bi * 32 + tx;
+      if (mi < d && mj < d) job.state[(int64_t)mi * job.ld + mj] = tile[tx][li];
+    }
+  }
+}
+
+int run_tri(const kfb_tri_job* jobs, int n_jobs, float scale, bool unpack, cudaStream_t stream) {
+  KFB_REQUIRE(n_jobs >= 0 && (jobs || n_jobs == 0), "bad job array");
+  for (int base = 0; base < n_jobs; base += kTriBatch) {
+    TriBatch batch;
+    batch.n = std::min(kTriBatch, n_jobs - base);
+    int blocks = 0;
+    for (int i = 0; i < batch.n; ++i) {
+      const kfb_tri_job& j = jobs[base + i];
+      KFB_REQUIRE(j.tri && j.state && j.d > 0 && j.ld_state >= j.d, "tri job %d is malformed", base + i);
+      TriJob& t = batch.jobs[i];
+      t.tri = j.tri; t.state = j.state; t.ld = j.ld_state; t.d = j.d; t.T32 = ceil_div(j.d, 32);
+      batch.start[i] = blocks;
+      blocks += t.T32 * (t.T32 + 1) / 2;
+    }
+    batch.start[batch.n] = blocks;
+    if (unpack) tri_kernel<true><<<blocks, 256, 0, stream>>>(batch, scale);
+    else tri_kernel<false><<<blocks, 256, 0, stream>>>(batch, scale);
+    KFB_CHECK_LAUNCH();
+  }
+  return KFB_OK;
+}
+
+}  // namespace
+
+// ============================================================================================
+// planning (host)
+// ============================================================================================
+static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, FactorPlan* plan) {
+  KFB_REQUIRE(n_jobs >= 0 && (jobs || n_jobs == 0), "bad job array");
+  plan->jobs.clear(); plan->segs.clear(); plan->item_start.clear(); plan->fin_start.clear();
+  plan->scratch_floats = 0;
+  int items = 0, fins = 0;
+  const int target = std::max(1, num_sms) * 4;
+  for (int ji = 0; ji < n_jobs; ++ji) {
+    const kfb_factor_job& j = jobs[ji];
+    KFB_REQUIRE(j.d > 0 && j.n_segments > 0 && j.segments, "factor job %d: empty", ji);
+    KFB_REQUIRE(j.state && j.ld_state >= j.d, "factor job %d: bad state / pitch", ji);
+    DevJob dj;
+    memset(&dj, 0, sizeof(dj));
+    dj.d = j.d;
+    dj.seg_start = (int)plan->segs.size();
+    dj.n_segments = j.n_segments;
+    dj.state = j.state; dj.ld_state = j.ld_state;
+    dj.seed_identity = j.seed_identity; dj.write_state = j.write_state; dj.tri_out = j.tri_out;
+    dj.ld_scratch = (j.d + 3) / 4 * 4;
+    dj.scratch_off = plan->scratch_floats;
+    plan->scratch_floats += align_up((size_t)dj.ld_scratch * j.d, 64);
+    dj.T = ceil_div(j.d, TS);
+    dj.n_pairs = dj.T * (dj.T + 1) / 2;
+    dj.T32 = ceil_div(j.d, 32);
+    int64_t k_total = 0;
+    for (int si = 0; si < j.n_segments; ++si) {
+      const kfb_segment& s = j.segments[si];
+      KFB_REQUIRE(s.data && s.n > 0 && s.c > 0, "factor job %d segment %d: empty", ji, si);
+      DevSegment ds;
+      memset(&ds, 0, sizeof(ds));
+      ds.data = s.data; ds.kind = s.kind; ds.has_bias = s.has_bias; ds.c = (int)s.c;
+      ds.h = (int)s.h; ds.w = (int)s.w; ds.ld = s.ld; ds.weight = s.weight;
+      ds.kh = ds.kw = ds.sh = ds.sw = 1;
+      int feat;
+      switch (s.kind) {
+        case KFB_SEG_ROWS:
+          KFB_REQUIRE(s.ld >= s.c, "segment pitch %lld < feature count %lld", (long long)s.ld, (long long)s.c);
+          ds.K = s.n; ds.oh = 1; ds.ow = 1; feat = (int)s.c + (s.has_bias ? 1 : 0);
+          break;
+        case KFB_SEG_NCHW:
+          KFB_REQUIRE(!s.has_bias && s.h > 0 && s.w > 0, "NCHW segment cannot carry a bias column");
+          ds.oh = (int)s.h; ds.ow = (int)s.w; ds.K = s.n * s.h * s.w; feat = (int)s.c;
+          break;
+        case KFB_SEG_IM2COL:
+          KFB_REQUIRE(s.kh > 0 && s.kw > 0 && s.sh > 0 && s.sw > 0 && s.ph >= 0 && s.pw >= 0, "bad conv geometry");
+          ds.kh = s.kh; ds.kw = s.kw; ds.sh = s.sh; ds.sw = s.sw; ds.ph = s.ph; ds.pw = s.pw;
+          ds.oh = (int)((s.h + 2 * s.ph - s.kh) / s.sh + 1);
+          ds.ow = (int)((s.w + 2 * s.pw - s.kw) / s.sw + 1);
+          KFB_REQUIRE(ds.oh > 0 && ds.ow > 0, "conv output is empty");
+          KFB_REQUIRE(s.n * s.c * s.h * s.w < (int64_t)1 << 40, "tensor too large");
+          ds.K = s.n * ds.oh * ds.ow; feat = (int)s.c * s.kh * s.kw + (s.has_bias ? 1 : 0);
+          break;
+        default:
+          KFB_FAIL(KFB_ERR_INVALID, "unknown segment kind %d", s.kind);
+      }
+      KFB_REQUIRE(feat == j.d, "factor job %d segment %d: feature count %d != d %d", ji, si, feat, j.d);
+      k_total += ds.K;
+      plan->segs.push_back(ds);
+    }
+    // split K so that the job alone offers ~4 CTAs per SM, chunks of at least 256 rows
+    int want = (int)std::max<int64_t>(1, std::min<int64_t>(ceil_div64(k_total, 256), ceil_div(target, dj.n_pairs)));
+    int chunks = 0;
+    for (int si = 0; si < j.n_segments; ++si) {
+      DevSegment& ds = plan->segs[dj.seg_start + si];
+      int64_t n = std::max<int64_t>(1, std::min<int64_t>(ceil_div64(ds.K, 256), ceil_div64((int64_t)want * ds.K, k_total)));
+      ds.chunk_len = ceil_div64(ceil_div64(ds.K, n), BK) * BK;
+      ds.n_chunks = (int)ceil_div64(ds.K, ds.chunk_len);
+      ds.chunk_start = chunks;
+      chunks += ds.n_chunks;
+    }
+    dj.n_chunks = chunks;
+    plan->item_start.push_back(items);
+    plan->fin_start.push_back(fins);
+    items += dj.n_pairs * chunks;
+    fins += dj.T32 * (dj.T32 + 1) / 2;
+    plan->jobs.push_back(dj);
+  }
+  plan->item_start.push_back(items);
+  plan->fin_start.push_back(fins);
+  plan->n_items = items;
+  plan->n_fin = fins;
+  // workspace layout: [jobs][segments][item_start][fin_start][scratch]
+  size_t off = 0;
+  plan->off_jobs = off;   off = align_up(off + plan->jobs.size() * sizeof(DevJob), 256);
+  plan->off_segs = off;   off = align_up(off + plan->segs.size() * sizeof(DevSegment), 256);
+  plan->off_items = off;  off = align_up(off + plan->item_start.size() * sizeof(int), 256);
+  plan->off_fin = off;    off = align_up(off + plan->fin_start.size() * sizeof(int), 256);
+  plan->off_scratch = off;
+  plan->total_bytes = off + plan->scratch_floats * sizeof(float);
+  return KFB_OK;
+}
+
+int upload_plan(FactorPlan* plan, void* workspace, cudaStream_t stream) {
+  char* ws = (char*)workspace;
+  float* scratch = (float*)(ws + plan->off_scratch);
+  for (auto& j : plan->jobs) j.scratch = scratch + j.scratch_off;
+  KFB_CUDA(cudaMemcpyAsync(ws + plan->off_jobs, plan->jobs.data(), plan->jobs.size() * sizeof(DevJob), cudaMemcpyHostToDevice, stream));
+  KFB_CUDA(cudaMemcpyAsync(ws + plan->off_segs, plan->segs.data(), plan->segs.size() * sizeof(DevSegment), cudaMemcpyHostToDevice, stream));
+  KFB_CUDA(cudaMemcpyAsync(ws + plan->off_items, plan->item_start.data(), plan->item_start.size() * sizeof(int), cudaMemcpyHostToDevice, stream));
+  KFB_CUDA(cudaMemcpyAsync(ws + plan->off_fin, plan->fin_start.data(), plan->fin_start.size() * sizeof(int), cudaMemcpyHostToDevice, stream));
+  KFB_CUDA(cudaMemsetAsync(scratch, 0, plan->scratch_floats * sizeof(float), stream));
+  return KFB_OK;
+}
+
+int launch_syrk_simt(const FactorPlan& plan, void* workspace, cudaStream_t stream) {
+  if (plan.n_items == 0) return KFB_OK;
+  char* ws = (char*)workspace;
+  syrk_simt_kernel<<<plan.n_items, NT, 0, stream>>>((const DevJob*)(ws + plan.off_jobs),
+                                                   (const DevSegment*)(ws + plan.off_segs),
+                                                   (const int*)(ws + plan.off_items),
+                                                   (int)plan.jobs.size());
+  KFB_CHECK_LAUNCH();
+  return KFB_OK;
+}
+
+int launch_finalize(const FactorPlan& plan, void* workspace, float alpha, cudaStream_t stream) {
+  if (plan.n_fin == 0) return KFB_OK;
+  char* ws = (char*)workspace;
+  finalize_kernel<<<plan.n_fin, 256, 0, stream>>>((const DevJob*)(ws + plan.off_jobs),
+                                                 (const int*)(ws + plan.off_fin),
+                                                 (int)plan.jobs.size(), alpha);
+  KFB_CHECK_LAUNCH();
+  return KFB_OK;
+}
+
+}  // namespace kfb
+
+// ============================================================================================
+// C ABI
+// ============================================================================================
+extern "C" {
+
+size_t kfb_factor_workspace_bytes(const kfb_factor_job* jobs, int32_t n_jobs) {
+  kfb::FactorPlan plan;
+  kfb::Context* ctx = kfb::current_context();
+  if (kfb::plan_factor(jobs, n_jobs, ctx ? ctx->num_sms : 148, &plan) != KFB_OK) return 0;
+  return plan.total_bytes;
+}
+
+int kfb_factor_update(const kfb_factor_job* jobs, int32_t n_jobs, float alpha, void* workspace,
+                      size_t workspace_bytes, void* stream_) {
+  kfb::Context* ctx;
+  int rc = kfb::require_context(&ctx);
+  if (rc) return rc;
+  if (n_jobs == 0) return KFB_OK;
+  KFB_REQUIRE(alpha > 0.f && alpha <= 1.f, "alpha must be in (0, 1], got %g", alpha);
+  if (alpha == 1.f) return KFB_OK;   // update_running_avg is a no-op (kfac/layers/utils.py:175)
+  cudaStream_t stream = (cudaStream_t)stream_;
+  kfb::FactorPlan plan;
+  rc = kfb::plan_factor(jobs, n_jobs, ctx->num_sms, &plan);
+  if (rc) return rc;
+  if (!workspace || workspace_bytes < plan.total_bytes)
+    KFB_FAIL(KFB_ERR_WORKSPACE, "factor workspace: need %zu bytes, got %zu", plan.total_bytes, workspace_bytes);
+  KFB_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+  rc = kfb::upload_plan(&plan, workspace, stream);
+  if (rc) return rc;
+  rc = kfb::launch_syrk(plan, workspace, ctx, stream);
+  if (rc) return rc;
+  return kfb::launch_finalize(plan, workspace, alpha, stream);
+}
+
+int kfb_tri_unpack(const kfb_tri_job* jobs, int32_t n_jobs, float scale, void* stream) {
+  kfb::Context* ctx;
+  int rc = kfb::require_context(&ctx);
+  if (rc) return rc;
+  return kfb::run_tri(jobs, n_jobs, scale, true, (cudaStream_t)stream);
+}
+
+int kfb_tri_pack(const kfb_tri_job* jobs, int32_t n_jobs, void* stream) {
+  kfb::Context* ctx;
+  int rc = kfb::require_context(&ctx);
+  if (rc) return rc;
+  return kfb::run_tri(jobs, n_jobs, 1.f, false, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,55 @@
+// Device-side descriptors and the host plan of one kfb_factor_update call.
+#pragma once
+#include <vector>
+
+#include "kfb_common.cuh"
+
+namespace kfb {
+
+struct DevSegment {
+  const float* data;
+  int kind, has_bias;
+  int c;                 // features without the bias column
+  int h, w;              // NCHW: spatial extent; IM2COL: input extent
+  int kh, kw, sh, sw, ph, pw;
+  int oh, ow;            // rows per image = oh*ow
+  int64_t ld;            // ROWS pitch
+  int64_t K;             // rows of X
+  float weight;
+  int n_chunks;          // split-K chunks of this segment
+  int chunk_start;       // first chunk index inside the job
+  int64_t chunk_len;
+};
+
+struct DevJob {
+  int d;
+  int seg_start, n_segments;
+  float* state;
+  int64_t ld_state;
+  int seed_identity, write_state;
+  float* tri_out;
+  float* scratch;        // d x d accumulator (upper triangle used), pitch ld_scratch
+  int64_t ld_scratch;
+  size_t scratch_off;    // host only: float offset into the scratch region
+  int T, n_pairs;        // 64-wide tiles per side, upper-triangle tile pairs
+  int n_chunks;          // split-K chunks over all segments
+  int T32;               // 32-wide blocks per side for finalize
+  int use_tc;            // 1: handled by the tcgen05 SYRK
+};
+
+struct FactorPlan {
+  std::vector<DevJob> jobs;
+  std::vector<DevSegment> segs;
+  std::vector<int> item_start, fin_start;
+  int n_items = 0, n_fin = 0;
+  size_t scratch_floats = 0;
+  size_t off_jobs = 0, off_segs = 0, off_items = 0, off_fin = 0, off_scratch = 0, total_bytes = 0;
+};
+
+KFB_HIDDEN int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, FactorPlan* plan);
+KFB_HIDDEN int upload_plan(FactorPlan* plan, void* workspace, cudaStream_t stream);
+KFB_HIDDEN int launch_syrk_simt(const FactorPlan& plan, void* workspace, cudaStream_t stream);
+KFB_HIDDEN int launch_syrk(const FactorPlan& plan, void* workspace, Context* ctx, cudaStream_t stream);
+KFB_HIDDEN int launch_finalize(const FactorPlan& plan, void* workspace, float alpha, cudaStream_t stream);
+
+}  // namespace kfb

@@ -23,6 +23,12 @@
 #include <stddef.h>
 #include <stdint.h>
 
+#if defined(__GNUC__)
+#define KFB_API __attribute__((visibility("default")))
+#else
+#define KFB_API
+#endif
+
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -39,15 +45,15 @@ typedef enum {
 #define KFB_ABI_VERSION 1
 
 /* ---- library ------------------------------------------------------------------ */
-int kfb_version(void);
-const char* kfb_last_error(void);
+KFB_API int kfb_version(void);
+KFB_API const char* kfb_last_error(void);
 /* Create the per-device context (cuSOLVER handle, SM count, TMA driver entry point) for
  * `device` and make it the context used by later calls from this thread. Idempotent. */
-int kfb_init(int device);
+KFB_API int kfb_init(int device);
 /* Which code path the GEMM-shaped kernels use: 0 = SIMT fp32 (exact fp32 FMA, the
  * first-correct path), 1 = tcgen05 TF32 tensor cores (default when available). */
-int kfb_set_mma_mode(int mode);
-int kfb_get_mma_mode(void);
+KFB_API int kfb_set_mma_mode(int mode);
+KFB_API int kfb_get_mma_mode(void);
 
 /* ---- factor computation + running average ------------------------------------------
  * Replaces Conv2dLayer._get_A_factor/_get_G_factor/_extract_patches (kfac/layers/conv.py:24-70),
@@ -90,8 +96,8 @@ typedef struct kfb_factor_job {
                                     new state - a slot of the caller's allreduce fusion buffer */
 } kfb_factor_job;
 
-size_t kfb_factor_workspace_bytes(const kfb_factor_job* jobs, int32_t n_jobs);
-int kfb_factor_update(const kfb_factor_job* jobs, int32_t n_jobs, float alpha,
+KFB_API size_t kfb_factor_workspace_bytes(const kfb_factor_job* jobs, int32_t n_jobs);
+KFB_API int kfb_factor_update(const kfb_factor_job* jobs, int32_t n_jobs, float alpha,
                       void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- packed-triangle fusion buffer ----------------------------------------------------
@@ -105,9 +111,9 @@ typedef struct kfb_tri_job {
   int32_t reserved;
 } kfb_tri_job;
 /* state <- scale * unpack(tri), both triangles */
-int kfb_tri_unpack(const kfb_tri_job* jobs, int32_t n_jobs, float scale, void* stream);
+KFB_API int kfb_tri_unpack(const kfb_tri_job* jobs, int32_t n_jobs, float scale, void* stream);
 /* tri <- upper triangle of state */
-int kfb_tri_pack(const kfb_tri_job* jobs, int32_t n_jobs, void* stream);
+KFB_API int kfb_tri_pack(const kfb_tri_job* jobs, int32_t n_jobs, void* stream);
 
 /* ---- eigendecomposition (the one library call: cuSOLVER syevd) ----------------------------
  * Replaces get_eigendecomp (kfac/layers/utils.py:45-74) as used by
@@ -115,15 +121,15 @@ int kfb_tri_pack(const kfb_tri_job* jobs, int32_t n_jobs, void* stream);
  * at 0.  Outputs: E (rows are eigenvectors, E = Q^T), Q (columns are eigenvectors, the
  * reference's state['QA'|'QG']) and w.  `factor` is not modified. `dev_info` is a device
  * int32 written by cuSOLVER (0 = converged); the call does not synchronise. */
-size_t kfb_syevd_workspace_bytes(int32_t d);
-int kfb_syevd(const float* factor, int64_t ld_factor, int32_t d,
+KFB_API size_t kfb_syevd_workspace_bytes(int32_t d);
+KFB_API int kfb_syevd(const float* factor, int64_t ld_factor, int32_t d,
               float* E, int64_t ld_e, float* Q, int64_t ld_q, float* w,
               void* workspace, size_t workspace_bytes, int32_t* dev_info, void* stream);
 /* out <- in^T  (receivers of a broadcast Q rebuild E) */
-int kfb_transpose(const float* in, int64_t ld_in, int32_t rows, int32_t cols,
+KFB_API int kfb_transpose(const float* in, int64_t ld_in, int32_t rows, int32_t cols,
                   float* out, int64_t ld_out, void* stream);
 /* out[i][j] = 1 / (dG[i]*dA[j] + damping)    (kfac/layers/base.py:305-306) */
-int kfb_outer_recip(const float* dG, const float* dA, int32_t dg, int32_t da, float damping,
+KFB_API int kfb_outer_recip(const float* dG, const float* dA, int32_t dg, int32_t da, float damping,
                     float* out, int64_t ld_out, void* stream);
 
 /* ---- preconditioning -------------------------------------------------------------------
@@ -149,7 +155,7 @@ typedef struct kfb_precond_job {
   float* gmat; float* V; float* out; int64_t ld_v;  /* dg x da each, same pitch */
   float* T; int64_t ld_t;                           /* da x dg */
 } kfb_precond_job;
-int kfb_precondition(const kfb_precond_job* jobs, int32_t n_jobs, float* vg_acc, void* stream);
+KFB_API int kfb_precondition(const kfb_precond_job* jobs, int32_t n_jobs, float* vg_acc, void* stream);
 
 /* *vg_acc += sum_jobs sum(v * [weight_grad | bias_grad])   — for layers whose preconditioned
  * gradient arrived by broadcast (MEM_OPT / HYBRID_OPT). */
@@ -161,7 +167,7 @@ typedef struct kfb_grad_job {
   int32_t da, dg, has_bias;
   int32_t reserved;
 } kfb_grad_job;
-int kfb_dot_accumulate(const kfb_grad_job* jobs, int32_t n_jobs, float* vg_acc, void* stream);
+KFB_API int kfb_dot_accumulate(const kfb_grad_job* jobs, int32_t n_jobs, float* vg_acc, void* stream);
 
 /* Replaces KFAC.update_gradients / KFACLayer.update_gradient / _set_*_grad
  * (kfac/preconditioner.py:587-590, kfac/layers/base.py:419-430,477-483) and the scalar part of
@@ -169,7 +175,7 @@ int kfb_dot_accumulate(const kfb_grad_job* jobs, int32_t n_jobs, float* vg_acc, 
  *   nu = min(1, sqrt(kl_clip / |*vg_acc * lr^2|))   if vg_acc != NULL and *vg_acc != 0,
  *   nu = fixed_scale                                otherwise.
  * No host synchronisation. */
-int kfb_scale_writeback(const kfb_grad_job* jobs, int32_t n_jobs, const float* vg_acc,
+KFB_API int kfb_scale_writeback(const kfb_grad_job* jobs, int32_t n_jobs, const float* vg_acc,
                         float lr, float kl_clip, float fixed_scale, void* stream);
 
 #ifdef __cplusplus

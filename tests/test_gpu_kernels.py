@@ -1,0 +1,302 @@
+"""Parity of every C-ABI entry point against the oracle on a B200 (-m gpu).
+
+Each test builds jobs on the GPU, runs them through libkfac_b200.so (CudaOps), builds the
+same jobs on CPU copies of the tensors and runs them through the oracle-backed stand-in
+(tests/_cpu_ops.py), and compares.  Tolerances are north_star's: factors rtol 1e-3 (measured
+against the factor's own scale: |err| <= 1e-3 * sqrt(F_ii F_jj), since elementwise rtol is
+meaningless for entries that cancel to ~0), preconditioned gradients rtol 1e-2 / atol 1e-4."""
+import math
+
+import pytest
+import torch
+
+from conftest import load_golden
+from distributed_kfac_pytorch_b200 import _native as N
+from distributed_kfac_pytorch_b200.layers.base import alloc2d
+from _cpu_ops import OracleOps, triu_pack
+from oracle import kfac_oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = 'cuda:0'
+
+
+@pytest.fixture(params=[0, 1], ids=['simt', 'tcgen05'])
+def ops(request):
+    N.set_ops(None)
+    o = N.get_ops()
+    o._enter(torch.zeros(1, device=DEV))
+    o.set_mma_mode(request.param)
+    yield o
+    o.set_mma_mode(1)
+
+
+def assert_factor_close(got, ref, tol=1e-3):
+    got = got.detach().cpu().double()
+    ref = ref.detach().cpu().double()
+    dscale = ref.diagonal().clamp_min(0).sqrt()
+    bound = tol * torch.outer(dscale, dscale) + 1e-9
+    err = (got - ref).abs()
+    worst = (err / bound).max().item()
+    assert worst <= 1.0, 'factor error %.3g x tolerance' % worst
+    assert torch.equal(got, got.t()), 'factor is not exactly symmetric'
+
+
+def seg_copy(s, device):
+    t = s.tensor.to(device)
+    return N.Segment(s.kind, t, s.n, s.c, s.weight, has_bias=s.has_bias, h=s.h, w=s.w,
+                     kernel=s.kernel, stride=s.stride, padding=s.padding, ld=s.ld)
+
+
+def run_both(ops, d, segments, alpha=0.95, old=None, with_tri=True):
+    """Run one factor job on GPU and on the oracle; returns (gpu_state, gpu_tri, ref_state)."""
+    buf, state = alloc2d(d, d, DEV)
+    buf.fill_(float('nan'))
+    if old is not None:
+        state.copy_(old)
+    tri = torch.full((d * (d + 1) // 2,), float('nan'), device=DEV) if with_tri else None
+    ops.factor_update([N.FactorJob(d, segments, state, old is None, True, tri)], alpha)
+    torch.cuda.synchronize()
+    ref_state = torch.empty(d, d) if old is None else old.clone()
+    OracleOps().factor_update([N.FactorJob(d, [seg_copy(s, 'cpu') for s in segments], ref_state,
+                                           old is None, True, None)], alpha)
+    return state, tri, ref_state
+
+
+def conv_segments(x, k, s, p, has_bias, dev=DEV):
+    n, c, h, w = x.shape
+    oh = (h + 2 * p[0] - k[0]) // s[0] + 1
+    ow = (w + 2 * p[1] - k[1]) // s[1] + 1
+    S = oh * ow
+    seg = N.Segment(N.KFB_SEG_IM2COL, x.to(dev).contiguous(), n, c, 1.0 / (S * S * n * S),
+                    has_bias=has_bias, h=h, w=w, kernel=k, stride=s, padding=p)
+    return c * k[0] * k[1] + int(has_bias), [seg]
+
+
+CONV_CASES = [
+    # (N, C, H, W, kernel, stride, padding, bias)
+    (4, 3, 17, 13, (3, 3), (1, 1), (1, 1), False),
+    (3, 5, 16, 16, (3, 3), (2, 2), (1, 1), True),
+    (2, 3, 31, 29, (7, 7), (2, 2), (3, 3), False),     # conv1-like, d = 147
+    (5, 16, 9, 9, (1, 1), (2, 2), (0, 0), False),      # downsample 1x1 stride 2
+    (2, 40, 7, 7, (3, 3), (1, 1), (1, 1), False),      # d = 360, 7x7 map (49 not /4)
+    (3, 8, 10, 12, (3, 5), (2, 1), (0, 2), True),      # asymmetric everything
+    (1, 1, 3, 3, (3, 3), (1, 1), (0, 0), False),       # single output pixel, K = 1
+    (2, 70, 14, 14, (3, 3), (1, 1), (1, 1), False),    # d = 630 > several tiles
+]
+
+
+@pytest.mark.parametrize('case', CONV_CASES, ids=lambda c: 'x'.join(map(str, c[:4])) + '_k%d' % c[4][0])
+def test_conv_A_factor(ops, case):
+    n, c, h, w, k, s, p, bias = case
+    g = torch.Generator().manual_seed(hash(case) % 1000)
+    x = torch.randn(n, c, h, w, generator=g)
+    d, segs = conv_segments(x, k, s, p, bias)
+    state, tri, ref = run_both(ops, d, segs)
+    assert_factor_close(state, ref)
+    torch.testing.assert_close(tri.cpu(), triu_pack(state.cpu()), rtol=0, atol=0)
+    # closed form against the oracle's own conv2d_A (not via the stand-in)
+    direct = O.factor_ema(O.conv2d_A([x], k, s, p, bias), None, 0.95)
+    assert_factor_close(state, direct)
+
+
+@pytest.mark.parametrize('shape', [(4, 6, 5, 5), (32, 64, 7, 7), (3, 130, 14, 14), (2, 16, 56, 56), (1, 3, 1, 1)])
+def test_conv_G_factor_nchw(ops, shape):
+    n, c, h, w = shape
+    g = torch.randn(*shape, generator=torch.Generator().manual_seed(7))
+    S = h * w
+    seg = N.Segment(N.KFB_SEG_NCHW, g.to(DEV), n, c, 1.0 / (S * S * n * S), h=h, w=w)
+    state, tri, ref = run_both(ops, c, [seg])
+    assert_factor_close(state, ref)
+    assert_factor_close(state, O.factor_ema(O.conv2d_G([g]), None, 0.95))
+
+
+@pytest.mark.parametrize('rows,feat,bias', [(32, 2048, True), (20, 13, True), (7, 100, False), (1, 5, True),
+                                            (300, 65, False)])
+def test_linear_factor_rows(ops, rows, feat, bias):
+    a = torch.randn(rows, feat, generator=torch.Generator().manual_seed(3))
+    seg = N.Segment(N.KFB_SEG_ROWS, a.to(DEV), rows, feat, 1.0 / rows, has_bias=bias, ld=feat)
+    d = feat + int(bias)
+    state, tri, ref = run_both(ops, d, [seg])
+    assert_factor_close(state, ref)
+    assert_factor_close(state, O.factor_ema(O.linear_A([a], bias), None, 0.95))
+
+
+def test_multi_segment_and_running_average(ops):
+    """LinearMultiLayer: sum over calls, each with its own 1/rows; then a second EMA update."""
+    gen = torch.Generator().manual_seed(11)
+    calls = [torch.randn(r, 37, generator=gen) for r in (20, 20, 5, 33)]
+    segs = [N.Segment(N.KFB_SEG_ROWS, c.to(DEV), c.shape[0], 37, 1.0 / c.shape[0], has_bias=True, ld=37)
+            for c in calls]
+    state, _, ref = run_both(ops, 38, segs)
+    assert_factor_close(state, ref)
+    assert_factor_close(state, O.factor_ema(O.linear_multi_A(calls, True), None, 0.95))
+    # second update starts from the previous state (not the identity)
+    state2, _, ref2 = run_both(ops, 38, segs[:2], alpha=0.5, old=ref)
+    assert_factor_close(state2, ref2)
+    expect = O.factor_ema(O.linear_multi_A(calls[:2], True), ref.clone(), 0.5)
+    assert_factor_close(state2, expect)
+
+
+def test_row_pitch_and_noncontiguous_rows(ops):
+    base = torch.randn(50, 40, generator=torch.Generator().manual_seed(5))
+    view = base[:, :29]                      # pitch 40, 29 features
+    seg = N.Segment(N.KFB_SEG_ROWS, base.to(DEV)[:, :29], 50, 29, 1.0 / 50, ld=40)
+    buf, st = alloc2d(29, 29, DEV)
+    ops.factor_update([N.FactorJob(29, [seg], st, True, True, None)], 0.9)
+    ref = O.factor_ema(O.linear_A([view.contiguous()], False), None, 0.9)
+    assert_factor_close(st, ref)
+    assert st.stride(0) == 32        # padded pitch, logical 29 x 29 view
+
+
+def test_batched_jobs_match_golden_captures(ops):
+    """All 12 factors of the golden SmallCNN step in ONE native call; compared with the
+    factors the unmodified reference produced."""
+    rec = load_golden('cnn_single.pt')
+    import models
+    import distributed_kfac_pytorch_b200 as kfac
+    N.set_ops(ops)
+    model = models.make_cnn().to(DEV)
+    pre = kfac.KFAC(model, **rec['kfac_kwargs'])
+    step = rec['steps'][0]
+    for i, l in enumerate(pre.layers):
+        l.a_inputs = [t.to(DEV) for t in step['a_inputs'][i]]
+        l.g_outputs = [t.to(DEV) for t in step['g_outputs'][i]]
+    pre.compute_factors(alpha=0.95)
+    for i, l in enumerate(pre.layers):
+        assert_factor_close(l.state['A'], step['A'][i])
+        assert_factor_close(l.state['G'], step['G'][i])
+
+
+def test_tri_pack_unpack_roundtrip(ops):
+    pairs, refs = [], []
+    for d in (1, 5, 32, 33, 147, 300):
+        m = torch.randn(d, d, generator=torch.Generator().manual_seed(d))
+        m = m + m.t()
+        _, st = alloc2d(d, d, DEV)
+        st.copy_(m)
+        tri = torch.empty(d * (d + 1) // 2, device=DEV)
+        pairs.append((tri, st))
+        refs.append(m)
+    ops.tri_pack(pairs)
+    for (tri, st), m in zip(pairs, refs):
+        torch.testing.assert_close(tri.cpu(), triu_pack(m), rtol=0, atol=0)
+        st.fill_(float('nan'))
+    ops.tri_unpack(pairs, 0.25)
+    for (tri, st), m in zip(pairs, refs):
+        torch.testing.assert_close(st.cpu(), m * 0.25, rtol=0, atol=0)
+
+
+@pytest.mark.parametrize('d', [1, 7, 64, 147, 500])
+def test_syevd(ops, d):
+    g = torch.Generator().manual_seed(d)
+    x = torch.randn(max(d // 2, 1), d, generator=g)      # rank-deficient: exercises the clip at 0
+    f = x.t() @ x / x.shape[0]
+    _, F_ = alloc2d(d, d, DEV)
+    F_.copy_(f)
+    _, E = alloc2d(d, d, DEV)
+    _, Q = alloc2d(d, d, DEV)
+    w = torch.empty(d, device=DEV)
+    info = torch.ones(1, dtype=torch.int32, device=DEV)
+    ops.syevd(F_, E, Q, w, info)
+    torch.cuda.synchronize()
+    assert info.item() == 0
+    torch.testing.assert_close(F_.cpu(), f, rtol=0, atol=0)       # input preserved
+    Qc, Ec, wc = Q.cpu().double(), E.cpu().double(), w.cpu().double()
+    assert (wc >= 0).all()
+    torch.testing.assert_close(Ec, Qc.t(), rtol=0, atol=0)
+    torch.testing.assert_close(Qc.t() @ Qc, torch.eye(d, dtype=torch.double), rtol=0, atol=1e-4)
+    recon = Qc @ torch.diag(wc) @ Qc.t()
+    scale = f.abs().max().item()
+    assert (recon - f.double()).abs().max().item() <= 1e-4 * max(scale, 1e-6)
+    ref_w = torch.linalg.eigvalsh(f.double()).clamp_min(0)
+    torch.testing.assert_close(wc, ref_w, rtol=1e-3, atol=1e-5 * max(scale, 1e-6))
+
+
+def test_transpose_and_outer_recip(ops):
+    a = torch.randn(70, 45)
+    _, src = alloc2d(70, 45, DEV)
+    src.copy_(a)
+    _, dst = alloc2d(45, 70, DEV)
+    ops.transpose(src, dst)
+    torch.testing.assert_close(dst.cpu(), a.t(), rtol=0, atol=0)
+    dG, dA = torch.rand(33), torch.rand(70)
+    _, out = alloc2d(33, 70, DEV)
+    ops.outer_recip(dG.to(DEV), dA.to(DEV), 0.003, out)
+    torch.testing.assert_close(out.cpu(), O.outer_recip(dG, dA, 0.003), rtol=1e-6, atol=0)
+
+
+def make_precond_job(da, dg, bias, wshape, seed):
+    g = torch.Generator().manual_seed(seed)
+    A = torch.randn(2 * da, da, generator=g)
+    A = A.t() @ A / (2 * da)
+    G = torch.randn(2 * dg, dg, generator=g)
+    G = G.t() @ G / (2 * dg)
+    QA, wA = O.eigh_clipped(A)
+    QG, wG = O.eigh_clipped(G)
+    dGdA = O.outer_recip(wG, wA, 0.003)
+    wgrad = torch.randn(*wshape, generator=g)
+    bgrad = torch.randn(dg, generator=g) if bias else None
+    bufs = {}
+
+    def put(name, t):
+        _, v = alloc2d(t.shape[0], t.shape[1], DEV, zero=True)
+        v.copy_(t)
+        bufs[name] = v
+    put('QA', QA); put('EA', QA.t().contiguous()); put('QG', QG); put('EG', QG.t().contiguous())
+    put('dGdA', dGdA)
+    for name, shape in (('gmat', (dg, da)), ('V', (dg, da)), ('out', (dg, da)), ('T', (da, dg))):
+        put(name, torch.zeros(shape))
+    job = N.PrecondJob(da=da, dg=dg, has_bias=bias, **bufs)
+    job.weight_grad = wgrad.to(DEV)
+    job.bias_grad = bgrad.to(DEV) if bias else None
+    ref = O.precondition_eigen(O.grad_matrix(wgrad, bgrad), QA, QG, dGdA=dGdA)
+    return job, ref, wgrad, bgrad
+
+
+PRECOND_CASES = [(27, 16, False, (16, 3, 3, 3)), (65, 10, True, (10, 64)), (147, 64, False, (64, 3, 7, 7)),
+                 (256, 128, False, (128, 256, 1, 1)), (577, 130, True, (130, 64, 3, 3)), (1, 1, False, (1, 1))]
+
+
+def test_precondition_chain_and_kl_clip(ops):
+    jobs, refs, raw = [], [], []
+    for i, (da, dg, bias, wshape) in enumerate(PRECOND_CASES):
+        job, ref, wg, bg = make_precond_job(da, dg, bias, wshape, 100 + i)
+        jobs.append(job); refs.append(ref); raw.append((wg, bg))
+    vg = torch.zeros(1, device=DEV)
+    ops.precondition(jobs, vg)
+    torch.cuda.synchronize()
+    vg_ref = 0.0
+    for job, ref, (wg, bg) in zip(jobs, refs, raw):
+        scale = ref.abs().max().item()
+        torch.testing.assert_close(job.out.cpu(), ref, rtol=1e-2, atol=1e-4 * max(1.0, scale))
+        vg_ref += (ref * O.grad_matrix(wg, bg)).sum().item()
+    assert abs(vg.item() - vg_ref) <= 1e-2 * abs(vg_ref)
+    # dot_accumulate reproduces the fused reduction
+    vg2 = torch.zeros(1, device=DEV)
+    items = [(j.weight_grad, j.bias_grad, j.out) for j in jobs]
+    ops.dot_accumulate(items, vg2)
+    assert abs(vg2.item() - vg.item()) <= 1e-4 * abs(vg.item())
+    # KL-clipped write-back, no host sync inside
+    lr, kl = 0.1, 0.001
+    ops.scale_writeback(items, vg, lr, kl)
+    nu = min(1.0, math.sqrt(kl / abs(vg.item() * lr * lr)))
+    for job, ref in zip(jobs, refs):
+        n_w = job.da - int(job.has_bias)
+        got = job.weight_grad.cpu().reshape(job.dg, n_w)
+        torch.testing.assert_close(got, nu * job.out.cpu()[:, :n_w], rtol=1e-6, atol=0)
+        if job.has_bias:
+            torch.testing.assert_close(job.bias_grad.cpu(), nu * job.out.cpu()[:, n_w], rtol=1e-6, atol=0)
+    # vg == 0 -> no scaling (reference returns None, preconditioner.py:680-681)
+    vg.zero_()
+    before = jobs[0].out.clone()
+    ops.scale_writeback(items[:1], vg, lr, kl)
+    torch.testing.assert_close(jobs[0].weight_grad.reshape(before.shape), before, rtol=0, atol=0)
+
+
+def test_native_errors_are_loud(ops):
+    _, st = alloc2d(8, 8, DEV)
+    bad = N.Segment(N.KFB_SEG_ROWS, torch.zeros(4, 5, device=DEV), 4, 5, 1.0, ld=5)   # 5 features, d = 8
+    with pytest.raises(N.NativeError, match='feature count'):
+        ops.factor_update([N.FactorJob(8, [bad], st, True, True, None)], 0.9)
+    with pytest.raises(N.NativeError):
+        ops.transpose(torch.zeros(3, 3), torch.zeros(3, 3, device=DEV))
