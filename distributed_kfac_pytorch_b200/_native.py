@@ -67,6 +67,7 @@ _SIGNATURES = {
     'kfb_init': (C.c_int, [C.c_int]),
     'kfb_set_mma_mode': (C.c_int, [C.c_int]),
     'kfb_get_mma_mode': (C.c_int, []),
+    'kfb_launch_count': (C.c_ulonglong, []),
     'kfb_factor_workspace_bytes': (C.c_size_t, [C.POINTER(CFactorJob), C.c_int32]),
     'kfb_factor_update': (C.c_int, [C.POINTER(CFactorJob), C.c_int32, C.c_float, C.c_void_p,
                                     C.c_size_t, C.c_void_p]),
@@ -211,6 +212,9 @@ class CudaOps(object):
 
     def get_mma_mode(self):
         return self.lib.kfb_get_mma_mode()
+
+    def launch_count(self):
+        return int(self.lib.kfb_launch_count())
 
     # -- factors
     def factor_update(self, jobs, alpha):

@@ -15,6 +15,7 @@ namespace kfb {
 // ---- error reporting -----------------------------------------------------------------
 KFB_HIDDEN void set_error(const char* fmt, ...);
 KFB_HIDDEN const char* get_error();
+KFB_HIDDEN void count_launch();
 
 #define KFB_FAIL(code, ...)           \
   do {                                \
@@ -32,7 +33,13 @@ KFB_HIDDEN const char* get_error();
     }                                                                                    \
   } while (0)
 
-#define KFB_CHECK_LAUNCH() KFB_CUDA(cudaGetLastError())
+// every kernel of this library is launched through this macro, so the counter is the number
+// of OUR kernels launched (cuSOLVER's own kernels and memcpy/memset nodes are not counted)
+#define KFB_CHECK_LAUNCH()            \
+  do {                                \
+    ::kfb::count_launch();            \
+    KFB_CUDA(cudaGetLastError());     \
+  } while (0)
 
 #define KFB_REQUIRE(cond, ...)                      \
   do {                                              \

@@ -2,6 +2,7 @@
 #include <cusolverDn.h>
 #include <stdarg.h>
 
+#include <atomic>
 #include <mutex>
 
 #include "kfb_common.cuh"
@@ -13,6 +14,8 @@ static thread_local Context* g_ctx = nullptr;
 static Context g_contexts[64];
 static std::mutex g_mu;
 static int g_mma_mode = 1;
+static std::atomic<unsigned long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -89,5 +92,7 @@ int kfb_set_mma_mode(int mode) {
 }
 
 int kfb_get_mma_mode(void) { return kfb::g_mma_mode; }
+
+unsigned long long kfb_launch_count(void) { return kfb::g_launches.load(); }
 
 }  // extern "C"

@@ -54,6 +54,9 @@ KFB_API int kfb_init(int device);
  * first-correct path), 1 = tcgen05 TF32 tensor cores (default when available). */
 KFB_API int kfb_set_mma_mode(int mode);
 KFB_API int kfb_get_mma_mode(void);
+/* Number of kernels of this library launched so far in this process (all devices); cuSOLVER's
+ * internal kernels and memcpy/memset are not counted. Used by bench.py for "gpu_launches". */
+KFB_API unsigned long long kfb_launch_count(void);
 
 /* ---- factor computation + running average ------------------------------------------
  * Replaces Conv2dLayer._get_A_factor/_get_G_factor/_extract_patches (kfac/layers/conv.py:24-70),

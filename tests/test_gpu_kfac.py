@@ -27,6 +27,11 @@ def mode(request):
 
 
 def _run(rec, model, batch_fn, loss_fn):
+    # the MODEL's forward/backward must be fp32 like the reference's CPU run: cuDNN convs
+    # default to TF32, which perturbs the captured activations and (amplified by 1/damping)
+    # the expected gradients; K-FAC's own precision is what is under test here
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
     model.load_state_dict(rec['init_state'])
     model.to(DEV)
     opt = torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.9)
