@@ -81,6 +81,8 @@ _SIGNATURES = {
     'kfb_outer_recip': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_float,
                                   C.c_void_p, C.c_int64, C.c_void_p]),
     'kfb_precondition': (C.c_int, [C.POINTER(CPrecondJob), C.c_int32, C.c_void_p, C.c_void_p]),
+    'kfb_gemm_tn': (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
+                              C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]),
     'kfb_dot_accumulate': (C.c_int, [C.POINTER(CGradJob), C.c_int32, C.c_void_p, C.c_void_p]),
     'kfb_scale_writeback': (C.c_int, [C.POINTER(CGradJob), C.c_int32, C.c_void_p, C.c_float,
                                       C.c_float, C.c_float, C.c_void_p]),
@@ -326,6 +328,14 @@ class CudaOps(object):
         stream = self._enter(jobs[0].out)
         cjobs = (CPrecondJob * len(jobs))(*[self._precond_c(j) for j in jobs])
         self._call('kfb_precondition', cjobs, len(jobs), _ptr(vg_acc), stream)
+
+    def gemm_tn(self, A, B, D, mul=None):
+        """D = A @ B.T (optionally * mul), all row-major 2-D fp32 views."""
+        stream = self._enter(D)
+        _check_cuda(A, B, mul)
+        _check_f32(A, B, D, mul)
+        self._call('kfb_gemm_tn', A.data_ptr(), _pitch(A), B.data_ptr(), _pitch(B), D.data_ptr(), _pitch(D),
+                   A.shape[0], B.shape[0], A.shape[1], _ptr(mul), 0 if mul is None else _pitch(mul), stream)
 
     @staticmethod
     def _grad_jobs(items):

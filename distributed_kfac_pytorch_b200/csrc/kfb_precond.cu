@@ -250,6 +250,21 @@ int kfb_precondition(const kfb_precond_job* jobs, int32_t n_jobs, float* vg_acc,
   return run_stage(ctx, s4, vg_acc, stream);
 }
 
+int kfb_gemm_tn(const float* A, int64_t lda, const float* B, int64_t ldb, float* D, int64_t ldd, int32_t M,
+                int32_t N, int32_t K, const float* Mul, int64_t ldmul, void* stream) {
+  using namespace kfb;
+  Context* ctx;
+  int rc = require_context(&ctx);
+  if (rc) return rc;
+  KFB_REQUIRE(A && B && D && M > 0 && N > 0 && K > 0 && lda >= K && ldb >= K && ldd >= N, "bad gemm arguments");
+  KFB_REQUIRE(!Mul || ldmul >= N, "bad multiplier pitch");
+  std::vector<GemmProb> p(1);
+  memset(&p[0], 0, sizeof(GemmProb));
+  p[0].A = A; p[0].lda = lda; p[0].B = B; p[0].ldb = ldb; p[0].D = D; p[0].ldd = ldd;
+  p[0].M = M; p[0].N = N; p[0].K = K; p[0].Mul = Mul; p[0].ldmul = ldmul;
+  return run_stage(ctx, p, nullptr, (cudaStream_t)stream);
+}
+
 int kfb_dot_accumulate(const kfb_grad_job* jobs, int32_t n_jobs, float* vg_acc, void* stream) {
   using namespace kfb;
   Context* ctx;

@@ -1,8 +1,5 @@
-// Temporary: tensor-core back ends not built yet.
+// Temporary: tensor-core SYRK not built yet -> everything goes to the SIMT SYRK.
 #include "kfb_factor.cuh"
-#include "kfb_gemm.cuh"
 namespace kfb {
-bool gemm_tc_eligible(const GemmProb&) { return false; }
-int gemm_grouped_tc(Context*, const GemmProb*, int, float*, cudaStream_t) { KFB_FAIL(KFB_ERR_UNSUPPORTED, "tcgen05 GEMM not built"); }
 int launch_syrk(const FactorPlan& plan, void* workspace, Context*, cudaStream_t stream) { return launch_syrk_simt(plan, workspace, stream); }
 }

@@ -160,6 +160,12 @@ typedef struct kfb_precond_job {
 } kfb_precond_job;
 KFB_API int kfb_precondition(const kfb_precond_job* jobs, int32_t n_jobs, float* vg_acc, void* stream);
 
+/* Plain grouped-GEMM utility on the same kernels: D[m][n] = sum_k A[m][k] * B[n][k] (D = A B^T),
+ * optionally multiplied elementwise by Mul[m][n].  This is the building block of the chain above
+ * and of the explicit-inverse mode (G_inv grad A_inv, kfac/layers/base.py:472-475). */
+KFB_API int kfb_gemm_tn(const float* A, int64_t lda, const float* B, int64_t ldb, float* D, int64_t ldd,
+                        int32_t M, int32_t N, int32_t K, const float* Mul, int64_t ldmul, void* stream);
+
 /* *vg_acc += sum_jobs sum(v * [weight_grad | bias_grad])   — for layers whose preconditioned
  * gradient arrived by broadcast (MEM_OPT / HYBRID_OPT). */
 typedef struct kfb_grad_job {

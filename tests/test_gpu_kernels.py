@@ -225,6 +225,38 @@ def test_transpose_and_outer_recip(ops):
     torch.testing.assert_close(out.cpu(), O.outer_recip(dG, dA, 0.003), rtol=1e-6, atol=0)
 
 
+GEMM_SHAPES = [(128, 128, 32), (128, 128, 64), (256, 128, 512), (64, 64, 64), (147, 64, 147), (1000, 2049, 32),
+               (300, 130, 577), (1, 1, 1), (129, 257, 33), (512, 4608, 512), (2048, 512, 2048)]
+
+
+@pytest.mark.parametrize('shape', GEMM_SHAPES, ids=lambda s: 'x'.join(map(str, s)))
+def test_gemm_tn(ops, shape):
+    """D = A B^T against float64; TF32 keeps 10 mantissa bits per operand, so the bound is
+    relative to |A||B| row norms (about 1e-3), well inside the preconditioned-gradient tolerance."""
+    M, Nn, K = shape
+    g = torch.Generator().manual_seed(M * 7 + Nn * 3 + K)
+    A = torch.randn(M, K, generator=g)
+    B = torch.randn(Nn, K, generator=g)
+    mul = torch.rand(M, Nn, generator=g) + 0.5
+    _, a = alloc2d(M, K, DEV, zero=True); a.copy_(A)
+    _, b = alloc2d(Nn, K, DEV, zero=True); b.copy_(B)
+    _, m = alloc2d(M, Nn, DEV, zero=True); m.copy_(mul)
+    buf, d = alloc2d(M, Nn, DEV)
+    buf.fill_(float('nan'))
+    ops.gemm_tn(a, b, d, m)
+    torch.cuda.synchronize()
+    ref = (A.double() @ B.double().t()) * mul.double()
+    bound = 2e-3 * torch.outer(A.double().norm(dim=1), B.double().norm(dim=1)) * mul.double() + 1e-6
+    err = (d.cpu().double() - ref).abs()
+    assert torch.isfinite(d).all()
+    worst = (err / bound).max().item()
+    assert worst <= 1.0, 'gemm error %.3g x bound' % worst
+    if ops.get_mma_mode() == 0:
+        torch.testing.assert_close(d.cpu(), ref.float(), rtol=1e-4, atol=1e-5 * K ** 0.5 * 4)
+    if buf.shape[1] > Nn:     # the pitch padding must not be written
+        assert torch.isnan(buf[:, Nn:]).all()
+
+
 def make_precond_job(da, dg, bias, wshape, seed):
     g = torch.Generator().manual_seed(seed)
     A = torch.randn(2 * da, da, generator=g)
