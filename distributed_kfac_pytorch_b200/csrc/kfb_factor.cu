@@ -325,7 +325,7 @@ int run_tri(const kfb_tri_job* jobs, int n_jobs, float scale, bool unpack, cudaS
 // ============================================================================================
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, FactorPlan* plan) {
+int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_tc, FactorPlan* plan) {
   KFB_REQUIRE(n_jobs >= 0 && (jobs || n_jobs == 0), "bad job array");
   plan->jobs.clear(); plan->segs.clear(); plan->item_start.clear(); plan->fin_start.clear();
   plan->scratch_floats = 0;
@@ -349,6 +349,7 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, FactorPlan*
     dj.n_pairs = dj.T * (dj.T + 1) / 2;
     dj.T32 = ceil_div(j.d, 32);
     int64_t k_total = 0;
+    bool tc = allow_tc;
     for (int si = 0; si < j.n_segments; ++si) {
       const kfb_segment& s = j.segments[si];
       KFB_REQUIRE(s.data && s.n > 0 && s.c > 0, "factor job %d segment %d: empty", ji, si);
@@ -381,6 +382,7 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, FactorPlan*
       }
       KFB_REQUIRE(feat == j.d, "factor job %d segment %d: feature count %d != d %d", ji, si, feat, j.d);
       k_total += ds.K;
+      if (s.kind == KFB_SEG_ROWS) tc = false;   // feature-contiguous operands stay on the SIMT path
       plan->segs.push_back(ds);
     }
     // split K so that the job alone offers ~4 CTAs per SM, chunks of at least 256 rows
@@ -395,9 +397,10 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, FactorPlan*
       chunks += ds.n_chunks;
     }
     dj.n_chunks = chunks;
+    dj.use_tc = tc ? 1 : 0;
     plan->item_start.push_back(items);
     plan->fin_start.push_back(fins);
-    items += dj.n_pairs * chunks;
+    if (!tc) items += dj.n_pairs * chunks;
     fins += dj.T32 * (dj.T32 + 1) / 2;
     plan->jobs.push_back(dj);
   }
@@ -411,6 +414,8 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, FactorPlan*
   plan->off_segs = off;   off = align_up(off + plan->segs.size() * sizeof(DevSegment), 256);
   plan->off_items = off;  off = align_up(off + plan->item_start.size() * sizeof(int), 256);
   plan->off_fin = off;    off = align_up(off + plan->fin_start.size() * sizeof(int), 256);
+  plan_syrk_tc(plan);
+  plan->off_tc_items = off; off = align_up(off + plan->tc_items.size() * sizeof(TcItem), 256);
   plan->off_scratch = off;
   plan->total_bytes = off + plan->scratch_floats * sizeof(float);
   return KFB_OK;
@@ -424,6 +429,8 @@ int upload_plan(FactorPlan* plan, void* workspace, cudaStream_t stream) {
   KFB_CUDA(cudaMemcpyAsync(ws + plan->off_segs, plan->segs.data(), plan->segs.size() * sizeof(DevSegment), cudaMemcpyHostToDevice, stream));
   KFB_CUDA(cudaMemcpyAsync(ws + plan->off_items, plan->item_start.data(), plan->item_start.size() * sizeof(int), cudaMemcpyHostToDevice, stream));
   KFB_CUDA(cudaMemcpyAsync(ws + plan->off_fin, plan->fin_start.data(), plan->fin_start.size() * sizeof(int), cudaMemcpyHostToDevice, stream));
+  if (!plan->tc_items.empty())
+    KFB_CUDA(cudaMemcpyAsync(ws + plan->off_tc_items, plan->tc_items.data(), plan->tc_items.size() * sizeof(TcItem), cudaMemcpyHostToDevice, stream));
   KFB_CUDA(cudaMemsetAsync(scratch, 0, plan->scratch_floats * sizeof(float), stream));
   return KFB_OK;
 }
@@ -459,7 +466,8 @@ extern "C" {
 size_t kfb_factor_workspace_bytes(const kfb_factor_job* jobs, int32_t n_jobs) {
   kfb::FactorPlan plan;
   kfb::Context* ctx = kfb::current_context();
-  if (kfb::plan_factor(jobs, n_jobs, ctx ? ctx->num_sms : 148, &plan) != KFB_OK) return 0;
+  bool tc = ctx && ctx->umma_ok && kfb::mma_mode() == 1;
+  if (kfb::plan_factor(jobs, n_jobs, ctx ? ctx->num_sms : 148, tc, &plan) != KFB_OK) return 0;
   return plan.total_bytes;
 }
 
@@ -473,7 +481,7 @@ int kfb_factor_update(const kfb_factor_job* jobs, int32_t n_jobs, float alpha, v
   if (alpha == 1.f) return KFB_OK;   // update_running_avg is a no-op (kfac/layers/utils.py:175)
   cudaStream_t stream = (cudaStream_t)stream_;
   kfb::FactorPlan plan;
-  rc = kfb::plan_factor(jobs, n_jobs, ctx->num_sms, &plan);
+  rc = kfb::plan_factor(jobs, n_jobs, ctx->num_sms, ctx->umma_ok && kfb::mma_mode() == 1, &plan);
   if (rc) return rc;
   if (!workspace || workspace_bytes < plan.total_bytes)
     KFB_FAIL(KFB_ERR_WORKSPACE, "factor workspace: need %zu bytes, got %zu", plan.total_bytes, workspace_bytes);

@@ -37,7 +37,14 @@ struct DevJob {
   int use_tc;            // 1: handled by the tcgen05 SYRK
 };
 
+struct TcItem {            // one unit of tensor-core SYRK work
+  int job, seg, ti, tj;    // 128-wide tile pair (ti <= tj) of one segment of one job
+  int64_t k_begin, k_end;  // rows of X
+};
+
 struct FactorPlan {
+  std::vector<TcItem> tc_items;
+  size_t off_tc_items = 0;
   std::vector<DevJob> jobs;
   std::vector<DevSegment> segs;
   std::vector<int> item_start, fin_start;
@@ -46,7 +53,8 @@ struct FactorPlan {
   size_t off_jobs = 0, off_segs = 0, off_items = 0, off_fin = 0, off_scratch = 0, total_bytes = 0;
 };
 
-KFB_HIDDEN int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, FactorPlan* plan);
+KFB_HIDDEN int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_tc, FactorPlan* plan);
+KFB_HIDDEN void plan_syrk_tc(FactorPlan* plan);
 KFB_HIDDEN int upload_plan(FactorPlan* plan, void* workspace, cudaStream_t stream);
 KFB_HIDDEN int launch_syrk_simt(const FactorPlan& plan, void* workspace, cudaStream_t stream);
 KFB_HIDDEN int launch_syrk(const FactorPlan& plan, void* workspace, Context* ctx, cudaStream_t stream);
