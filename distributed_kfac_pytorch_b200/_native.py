@@ -71,6 +71,8 @@ _SIGNATURES = {
     'kfb_factor_workspace_bytes': (C.c_size_t, [C.POINTER(CFactorJob), C.c_int32]),
     'kfb_factor_update': (C.c_int, [C.POINTER(CFactorJob), C.c_int32, C.c_float, C.c_void_p,
                                     C.c_size_t, C.c_void_p]),
+    'kfb_static_scratch_bytes': (C.c_size_t, []),
+    'kfb_factor_update_static': (C.c_int, [C.POINTER(CFactorJob), C.c_int32, C.c_float, C.c_void_p]),
     'kfb_tri_unpack': (C.c_int, [C.POINTER(CTriJob), C.c_int32, C.c_float, C.c_void_p]),
     'kfb_tri_pack': (C.c_int, [C.POINTER(CTriJob), C.c_int32, C.c_void_p]),
     'kfb_syevd_workspace_bytes': (C.c_size_t, [C.c_int32]),
@@ -219,10 +221,7 @@ class CudaOps(object):
         return int(self.lib.kfb_launch_count())
 
     # -- factors
-    def factor_update(self, jobs, alpha):
-        if not jobs:
-            return
-        stream = self._enter(jobs[0].state)
+    def _factor_cjobs(self, jobs):
         n = len(jobs)
         cjobs = (CFactorJob * n)()
         keep = []
@@ -246,9 +245,30 @@ class CudaOps(object):
             cj.state, cj.ld_state = j.state.data_ptr(), _pitch(j.state)
             cj.seed_identity, cj.write_state = int(j.seed_identity), int(j.write_state)
             cj.tri_out = _ptr(j.tri_out)
+        return cjobs, keep
+
+    def factor_update(self, jobs, alpha):
+        if not jobs:
+            return
+        stream = self._enter(jobs[0].state)
+        cjobs, keep = self._factor_cjobs(jobs)
+        n = len(jobs)
         nbytes = self.lib.kfb_factor_workspace_bytes(cjobs, n)
         ws = self.workspace(nbytes, jobs[0].state.device)
         self._call('kfb_factor_update', cjobs, n, float(alpha), ws.data_ptr(), ws.numel(), stream)
+
+    def factor_update_static(self, jobs, alpha):
+        """kfb_factor_update_static: same result as factor_update, but the scratch is the
+        library's built-in fixed array, so nothing is allocated (not even by torch).  Raises
+        NativeError if the jobs need more than ``static_scratch_bytes()``."""
+        if not jobs:
+            return
+        stream = self._enter(jobs[0].state)
+        cjobs, keep = self._factor_cjobs(jobs)
+        self._call('kfb_factor_update_static', cjobs, len(jobs), float(alpha), stream)
+
+    def static_scratch_bytes(self):
+        return int(self.lib.kfb_static_scratch_bytes())
 
     def _tri_jobs(self, pairs):
         cjobs = (CTriJob * len(pairs))()

@@ -103,6 +103,24 @@ KFB_API size_t kfb_factor_workspace_bytes(const kfb_factor_job* jobs, int32_t n_
 KFB_API int kfb_factor_update(const kfb_factor_job* jobs, int32_t n_jobs, float alpha,
                       void* workspace, size_t workspace_bytes, void* stream);
 
+/* kfb_factor_update for callers that cannot allocate device memory.  No counterpart in the
+ * reference (which allocates freely through torch); it exists for hosts that own all GPU memory
+ * themselves or that may not call cudaMalloc once running.  Same jobs, same results, but the
+ * scratch (descriptors + split-K accumulators) is a fixed KFB_STATIC_SCRATCH_BYTES array inside the
+ * library: every GPU that loads the library holds that much memory until the process exits.
+ *   - nothing is allocated or freed on the device, here or in any library it calls (planning uses
+ *     ordinary host heap memory);
+ *   - a call whose jobs need more than kfb_static_scratch_bytes() fails with KFB_ERR_WORKSPACE and
+ *     a message giving both sizes - split the jobs over several calls, or use kfb_factor_update;
+ *   - the first call on each device looks up the array's device address (with that device
+ *     current); make that first call before starting any stream capture;
+ *   - all calls on a device share the one array and it keeps the previous call's contents; each
+ *     call clears the part it accumulates into, so back-to-back calls on ONE stream are fine, but
+ *     two calls whose kernels can overlap on the GPU (different streams, different threads) race. */
+#define KFB_STATIC_SCRATCH_BYTES (16u << 20)
+KFB_API size_t kfb_static_scratch_bytes(void);
+KFB_API int kfb_factor_update_static(const kfb_factor_job* jobs, int32_t n_jobs, float alpha, void* stream);
+
 /* ---- packed-triangle fusion buffer ----------------------------------------------------
  * Replaces get_triu / fill_triu (kfac/layers/utils.py:126-162) and the deferred
  * `tensor /= world` of TorchBackend.sync (kfac/comm.py:254-262). */
