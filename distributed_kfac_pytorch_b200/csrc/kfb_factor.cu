@@ -382,7 +382,9 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
       }
       KFB_REQUIRE(feat == j.d, "factor job %d segment %d: feature count %d != d %d", ji, si, feat, j.d);
       k_total += ds.K;
-      if (s.kind == KFB_SEG_ROWS) tc = false;   // feature-contiguous operands stay on the SIMT path
+      KFB_REQUIRE(ds.K < ((int64_t)1 << 31), "segment has %lld rows; at most 2^31-1 are supported", (long long)ds.K);
+      if (s.kind == KFB_SEG_ROWS) tc = false;
+      if (s.c * s.h * s.w >= ((int64_t)1 << 26)) tc = false;   // packed row offsets hold 26 bits   // feature-contiguous operands stay on the SIMT path
       plan->segs.push_back(ds);
     }
     // split K so that the job alone offers ~4 CTAs per SM, chunks of at least 256 rows

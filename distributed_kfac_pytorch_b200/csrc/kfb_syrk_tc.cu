@@ -26,34 +26,41 @@ constexpr int UMMA_K = 8;
 constexpr int kStages = 5;
 constexpr int kTileBytes = TM * BK * 4; // 16 KB
 constexpr int kStageBytes = 2 * kTileBytes;
-constexpr int kProducerWarps = 8;
+constexpr int kProducerWarps = 16;
+constexpr int kRowsPerWarp = TM / kProducerWarps;   // 8 rows of each tile per producer warp
 constexpr int kThreads = 32 * (4 + 1 + kProducerWarps);
 constexpr int kTmemCols = 256;
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256;
 
-constexpr int kBitNever = 62;           // row beyond d: always zero
-constexpr int kBitBias = 61;            // bias feature: 1 wherever the X row exists
-constexpr int kBitAlways = 63;          // NCHW: valid wherever the X row exists
+// A tile row (= one feature of X) is described by ONE packed word: (element offset << 6) | bit,
+// where `bit` selects the bit of the lane's validity mask that says whether this feature exists
+// at the lane's X row.  Bits 0..48 are the (ky,kx) positions of an im2col window (image border /
+// padding), kBitAlways is set whenever the X row exists, kBitNever is never set (features >= d,
+// and the bias feature, which is written separately).
+constexpr uint32_t kBitAlways = 62;
+constexpr uint32_t kBitNever = 63;
 
-struct RowInfo { int off; int bit; };
+__device__ __forceinline__ uint32_t row_info(const DevSegment& s, int d, int i) {
+  if (i >= d || (s.has_bias && i == d - 1)) return kBitNever;
+  if (s.kind == KFB_SEG_NCHW) return ((uint32_t)(i * s.h * s.w) << 6) | kBitAlways;
+  int khw = s.kh * s.kw;
+  int ci = i / khw;
+  int q = i - ci * khw;
+  int ky = q / s.kw, kx = q - ky * s.kw;
+  return ((uint32_t)((ci * s.h + ky) * s.w + kx) << 6) | (uint32_t)q;
+}
 
-__device__ __forceinline__ RowInfo row_info(const DevSegment& s, int d, int i) {
-  RowInfo r;
-  r.off = 0;
-  if (i >= d) { r.bit = kBitNever; return r; }
-  if (s.has_bias && i == d - 1) { r.bit = kBitBias; return r; }
-  if (s.kind == KFB_SEG_NCHW) {
-    r.off = i * s.h * s.w;
-    r.bit = kBitAlways;
-  } else {
-    int khw = s.kh * s.kw;
-    int ci = i / khw;
-    int q = i - ci * khw;
-    int ky = q / s.kw, kx = q - ky * s.kw;
-    r.off = (ci * s.h + ky) * s.w + kx;
-    r.bit = q;
+// Does the feature described by `info` exist for the lane whose validity mask is (mlo, mhi)?
+// kWide = false: all bits the segment can use live in one 32-bit word (im2col windows of up to
+// 25 taps keep their bits in mlo; kBitAlways / kBitNever are bits 30 / 31 of mhi remapped by the
+// caller), so the test is one wrapping funnel shift.
+template <bool kWide>
+__device__ __forceinline__ bool row_valid(uint32_t info, uint32_t mlo, uint32_t mhi) {
+  if (kWide) {
+    uint32_t m = (info & 32u) ? mhi : mlo;
+    return (__funnelshift_r(m, 0u, info) & 1u) != 0;       // shift amount taken mod 32
   }
-  return r;
+  return (__funnelshift_r(mlo, 0u, info) & 1u) != 0;
 }
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
@@ -87,84 +94,139 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
   if (warp >= 5) {
     // ===================== producers =====================
     const int pw = warp - 5;
+    // byte offset of this lane inside any of this warp's tile rows: rows are pw + 16*j, so the
+    // swizzle term (row & 7) is the same for all of them
+    const uint32_t lane_off = (uint32_t)((((lane >> 2) ^ (pw & 7)) << 4) | ((lane & 3) << 2));
+    const uint32_t vec_kq = lane & 7, vec_rsub = lane >> 3;
     int stage = 0; uint32_t phase = 0;
     for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
       const TcItem item = items[it];
-      const DevJob& job = jobs[item.job];
       const DevSegment s = segs[item.seg];
-      const int d = job.d;
+      const int d = jobs[item.job].d;
       const bool diag = item.ti == item.tj;
-      // lane j holds the decode of tile row (pw + 8*j'): j' = j & 15, tile A for j < 16, B otherwise
-      const int my_row = pw + kProducerWarps * (lane & 15);
-      const RowInfo mine = row_info(s, d, (lane < 16 ? item.ti : item.tj) * TM + my_row);
-      const int S = s.oh * s.ow;
-      const bool vec4 = s.kind == KFB_SEG_NCHW && (S & 3) == 0 && (((uintptr_t)s.data) & 15) == 0;
       const int n_tiles = diag ? 1 : 2;
-
-      for (int64_t k0 = item.k_begin; k0 < item.k_end; k0 += BK) {
-        umma::mbar_wait(&empty[stage], phase ^ 1);
-        uint8_t* st = smem + stage * kStageBytes;
-        if (vec4) {
-          // 8 lanes x float4 cover one tile row (32 k); 4 rows per warp instruction
-          const int kq = lane & 7, rsub = lane >> 3;
-          const int64_t k = k0 + 4 * kq;
-          const bool kin = k < item.k_end;
-          int64_t base = 0;
-          if (kin) {
-            int64_t n = k / S;
-            base = n * (int64_t)s.c * S + (k - n * S);
-          }
-          for (int t = 0; t < n_tiles; ++t) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const int j = 4 * i + rsub;                       // which of this warp's 16 rows
-              const int off = __shfl_sync(0xffffffffu, mine.off, j + 16 * t);
-              const int bit = __shfl_sync(0xffffffffu, mine.bit, j + 16 * t);
-              float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (kin && bit == kBitAlways) v = __ldg(reinterpret_cast<const float4*>(s.data + base + off));
-              const int r = pw + kProducerWarps * j;
-              *reinterpret_cast<float4*>(st + t * kTileBytes + r * 128 + ((kq ^ (r & 7)) << 4)) = v;
-            }
-          }
-        } else {
-          const int64_t k = k0 + lane;
-          const bool kin = k < item.k_end;
-          int64_t base = 0;
-          uint64_t mask = 0;
-          if (kin) {
-            int64_t n = k / S;
-            int r = (int)(k - n * S);
-            if (s.kind == KFB_SEG_NCHW) {
-              base = n * (int64_t)s.c * S + r;
-              mask = (1ull << kBitAlways) | (1ull << kBitBias);
-            } else {
-              int oy = r / s.ow, ox = r - oy * s.ow;
-              int y0 = oy * s.sh - s.ph, x0 = ox * s.sw - s.pw;
-              base = n * (int64_t)s.c * s.h * s.w + (int64_t)y0 * s.w + x0;
-              int kx_lo = max(0, -x0), kx_hi = min(s.kw, s.w - x0);
-              int ky_lo = max(0, -y0), ky_hi = min(s.kh, s.h - y0);
-              uint64_t xm = kx_hi > kx_lo ? (((1ull << (kx_hi - kx_lo)) - 1) << kx_lo) : 0;
-              for (int ky = ky_lo; ky < ky_hi; ++ky) mask |= xm << (ky * s.kw);
-              mask |= 1ull << kBitBias;
-            }
-          }
-          for (int t = 0; t < n_tiles; ++t) {
-#pragma unroll 4
-            for (int j = 0; j < 16; ++j) {
-              const int off = __shfl_sync(0xffffffffu, mine.off, j + 16 * t);
-              const int bit = __shfl_sync(0xffffffffu, mine.bit, j + 16 * t);
-              float v = 0.f;
-              if ((mask >> bit) & 1ull) v = (bit == kBitBias) ? 1.f : __ldg(s.data + base + off);
-              const int r = pw + kProducerWarps * j;
-              *reinterpret_cast<float*>(st + t * kTileBytes + r * 128 + (((lane >> 2) ^ (r & 7)) << 4) +
-                                        ((lane & 3) << 2)) = v;
-            }
-          }
+      const int S = s.oh * s.ow;
+      const uint32_t uS = (uint32_t)S, uow = (uint32_t)s.ow;
+      const uint32_t k_end32 = (uint32_t)item.k_end;       // K < 2^31 (checked on the host)
+      const bool vec4 = s.kind == KFB_SEG_NCHW && (S & 3) == 0 && (((uintptr_t)s.data) & 15) == 0;
+      const bool wide = s.kind == KFB_SEG_IM2COL && s.kh * s.kw > 30;
+      // does this warp own the bias feature's row in tile A / tile B?
+      int bias_row[2] = {-1, -1};
+      if (s.has_bias) {
+        for (int t = 0; t < n_tiles; ++t) {
+          int local = (d - 1) - (t == 0 ? item.ti : item.tj) * TM;
+          if (local >= 0 && local < TM && (local % kProducerWarps) == pw) bias_row[t] = local;
         }
-        umma::fence_proxy_async_smem();      // generic-proxy stores -> visible to the tensor core
-        __syncwarp();
-        if (lane == 0) umma::mbar_arrive(&full[stage]);
-        if (++stage == kStages) { stage = 0; phase ^= 1; }
+      }
+
+      if (vec4) {
+        // ---- NCHW, 16B-alignable: 8 lanes x float4 = one tile row (32 k), 4 rows per instruction
+        uint32_t info[2][2];
+#pragma unroll
+        for (int t = 0; t < 2; ++t)
+#pragma unroll
+          for (int i = 0; i < 2; ++i)
+            info[t][i] = row_info(s, d, (t == 0 ? item.ti : item.tj) * TM + pw + kProducerWarps * (4 * i + vec_rsub));
+        for (uint32_t k0 = (uint32_t)item.k_begin; k0 < k_end32; k0 += BK) {
+          umma::mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* st = smem + stage * kStageBytes;
+          const uint32_t k = k0 + 4 * vec_kq;
+          const bool kin = k < k_end32;
+          const uint32_t n = k / uS;
+          const float* src = s.data + ((int64_t)n * s.c * S + (k - n * uS));
+          float4 v[2][2];
+#pragma unroll
+          for (int t = 0; t < 2; ++t)
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+              v[t][i] = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (t < n_tiles && kin && (info[t][i] & 63u) == kBitAlways)
+                v[t][i] = __ldg(reinterpret_cast<const float4*>(src + (info[t][i] >> 6)));
+            }
+#pragma unroll
+          for (int t = 0; t < 2; ++t)
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
+              if (t < n_tiles) {
+                const int r = pw + kProducerWarps * (4 * i + vec_rsub);
+                *reinterpret_cast<float4*>(st + t * kTileBytes + r * 128 + ((vec_kq ^ (r & 7)) << 4)) = v[t][i];
+              }
+          umma::fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) umma::mbar_arrive(&full[stage]);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      } else {
+        // ---- general gather: one X row per lane, this warp's 8 (+8) tile rows per stage
+        uint32_t info[2][kRowsPerWarp];
+#pragma unroll
+        for (int t = 0; t < 2; ++t)
+#pragma unroll
+          for (int j = 0; j < kRowsPerWarp; ++j)
+            info[t][j] = row_info(s, d, (t == 0 ? item.ti : item.tj) * TM + pw + kProducerWarps * j);
+        for (uint32_t k0 = (uint32_t)item.k_begin; k0 < k_end32; k0 += BK) {
+          umma::mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* st = smem + stage * kStageBytes + pw * 128 + lane_off;
+          const uint32_t k = k0 + lane;
+          const bool kin = k < k_end32;
+          const uint32_t n = k / uS;
+          const uint32_t r = k - n * uS;
+          const float* src;
+          uint32_t mlo = 0, mhi = 0;
+          if (s.kind == KFB_SEG_NCHW) {
+            src = s.data + ((int64_t)n * s.c * S + r);
+            if (kin) mhi = 1u << (kBitAlways - 32);
+          } else {
+            const int oy = (int)(r / uow), ox = (int)(r - (uint32_t)oy * uow);
+            const int y0 = oy * s.sh - s.ph, x0 = ox * s.sw - s.pw;
+            src = s.data + ((int64_t)n * s.c * s.h * s.w + (int64_t)y0 * s.w + x0);
+            if (kin) {
+              const int kx_lo = max(0, -x0), kx_hi = min(s.kw, s.w - x0);
+              const int ky_lo = max(0, -y0), ky_hi = min(s.kh, s.h - y0);
+              uint64_t m = 0;
+              const uint64_t xm = kx_hi > kx_lo ? (((1ull << (kx_hi - kx_lo)) - 1) << kx_lo) : 0;
+              for (int ky = ky_lo; ky < ky_hi; ++ky) m |= xm << (ky * s.kw);
+              mlo = (uint32_t)m;
+              mhi = (uint32_t)(m >> 32);
+            }
+          }
+          float v[2][kRowsPerWarp];
+          if (!wide) {
+            // narrow: (ky,kx) bits in mlo; move "always" to bit 30 so one word decides everything.
+            // row_info's bit field is 6 bits: 62 -> (62 & 31) = 30, 63 -> 31 (never set).
+            const uint32_t m = mlo | ((mhi >> (kBitAlways - 32)) << 30);
+#pragma unroll
+            for (int t = 0; t < 2; ++t)
+#pragma unroll
+              for (int j = 0; j < kRowsPerWarp; ++j) {
+                v[t][j] = 0.f;
+                if (t < n_tiles && row_valid<false>(info[t][j], m, 0u)) v[t][j] = __ldg(src + (info[t][j] >> 6));
+              }
+          } else {
+#pragma unroll
+            for (int t = 0; t < 2; ++t)
+#pragma unroll
+              for (int j = 0; j < kRowsPerWarp; ++j) {
+                v[t][j] = 0.f;
+                if (t < n_tiles && row_valid<true>(info[t][j], mlo, mhi)) v[t][j] = __ldg(src + (info[t][j] >> 6));
+              }
+          }
+#pragma unroll
+          for (int t = 0; t < 2; ++t)
+#pragma unroll
+            for (int j = 0; j < kRowsPerWarp; ++j)
+              if (t < n_tiles)
+                *reinterpret_cast<float*>(st + t * kTileBytes + j * (kProducerWarps * 128)) = v[t][j];
+          // the bias feature is the constant 1 wherever the X row exists
+          for (int t = 0; t < n_tiles; ++t)
+            if (bias_row[t] >= 0)
+              *reinterpret_cast<float*>(smem + stage * kStageBytes + t * kTileBytes + bias_row[t] * 128 + lane_off) =
+                  kin ? 1.f : 0.f;
+          umma::fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) umma::mbar_arrive(&full[stage]);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
       }
     }
   } else if (warp == 4) {
