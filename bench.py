@@ -253,7 +253,7 @@ def run_ours(args):
     work = algorithmic_work(pre, caps)
     t_factor = StageTimer(ops, 'factor_update')
     t_precond = StageTimer(ops, 'precondition')
-    t_syevd = StageTimer(ops, 'syevd')
+    t_syevd = StageTimer(ops, 'syevd_batch')
 
     def one_step():
         feed(pre, caps)

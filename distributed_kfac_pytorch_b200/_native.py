@@ -45,6 +45,12 @@ class CTriJob(C.Structure):
                 ('d', C.c_int32), ('reserved', C.c_int32)]
 
 
+class CSyevdJob(C.Structure):
+    _fields_ = [('factor', C.c_void_p), ('ld_factor', C.c_int64), ('E', C.c_void_p), ('ld_e', C.c_int64),
+                ('Q', C.c_void_p), ('ld_q', C.c_int64), ('w', C.c_void_p), ('dev_info', C.c_void_p),
+                ('d', C.c_int32), ('reserved', C.c_int32)]
+
+
 class CPrecondJob(C.Structure):
     _fields_ = [('da', C.c_int32), ('dg', C.c_int32), ('has_bias', C.c_int32),
                 ('reserved', C.c_int32), ('weight_grad', C.c_void_p), ('bias_grad', C.c_void_p),
@@ -78,6 +84,8 @@ _SIGNATURES = {
     'kfb_syevd_workspace_bytes': (C.c_size_t, [C.c_int32]),
     'kfb_syevd': (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p,
                             C.c_int64, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]),
+    'kfb_syevd_batch_workspace_bytes': (C.c_size_t, [C.POINTER(CSyevdJob), C.c_int32]),
+    'kfb_syevd_batch': (C.c_int, [C.POINTER(CSyevdJob), C.c_int32, C.c_void_p, C.c_size_t, C.c_void_p]),
     'kfb_transpose': (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
                                 C.c_int64, C.c_void_p]),
     'kfb_outer_recip': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_float,
@@ -302,6 +310,23 @@ class CudaOps(object):
         self._call('kfb_syevd', factor.data_ptr(), _pitch(factor), d, E.data_ptr(), _pitch(E),
                    Q.data_ptr(), _pitch(Q), w.data_ptr(), ws.data_ptr(), ws.numel(),
                    info.data_ptr(), stream)
+
+    def syevd_batch(self, jobs):
+        """jobs: list of (factor, E, Q, w, info) tensors; all decompositions run concurrently on
+        the library's worker lanes and are ordered after / before the current stream."""
+        if not jobs:
+            return
+        stream = self._enter(jobs[0][0])
+        cjobs = (CSyevdJob * len(jobs))()
+        for cj, (factor, E, Q, w, info) in zip(cjobs, jobs):
+            _check_cuda(factor, E, Q, w, info)
+            _check_f32(factor, E, Q, w)
+            cj.factor, cj.ld_factor = factor.data_ptr(), _pitch(factor)
+            cj.E, cj.ld_e, cj.Q, cj.ld_q = E.data_ptr(), _pitch(E), Q.data_ptr(), _pitch(Q)
+            cj.w, cj.dev_info, cj.d = w.data_ptr(), info.data_ptr(), factor.shape[0]
+        nbytes = self.lib.kfb_syevd_batch_workspace_bytes(cjobs, len(jobs))
+        ws = self.workspace(nbytes, jobs[0][0].device)
+        self._call('kfb_syevd_batch', cjobs, len(jobs), ws.data_ptr(), ws.numel(), stream)
 
     def transpose(self, src, dst):
         stream = self._enter(src)

@@ -286,7 +286,9 @@ class KFACLayer(object):
         if self._info is None:
             self._info = torch.zeros(2, device=dev, dtype=torch.int32)
 
-    def _compute_inv(self, key, damping, ignore_rank):
+    def _inv_job(self, key, ignore_rank=False):
+        """Checks and buffers for one factor's eigendecomposition; returns the syevd job
+        ``(factor, E, Q, w, info)`` if THIS rank computes it, else None."""
         self._check_inv_ready(key)
         mine = comm.backend.rank() == (self.compute_A_inv_rank if key == 'A'
                                        else self.compute_G_inv_rank)
@@ -294,25 +296,31 @@ class KFACLayer(object):
             self._ensure_inv_buffers(key)
         if ignore_rank or mine:
             info = self._info[0:1] if key == 'A' else self._info[1:2]
-            get_ops().syevd(self.state[key], self._E[key], self.state['Q' + key],
-                            self.state['d' + key], info)
-            return True
-        return False
+            return (self.state[key], self._E[key], self.state['Q' + key], self.state['d' + key], info)
+        return None
 
-    def compute_A_inv(self, damping=0.001, ignore_rank=False):
-        """Eigendecompose A on its assigned rank (kfac/layers/base.py:198-256)."""
-        self._compute_inv('A', damping, ignore_rank)
-
-    def compute_G_inv(self, damping=0.001, ignore_rank=False):
-        """Eigendecompose G on its assigned rank and, with prediv_eigenvalues, build
-        dGdA = 1/(dG dA^T + damping) there (kfac/layers/base.py:258-308)."""
-        if self._compute_inv('G', damping, ignore_rank) and self.prediv_eigenvalues:
+    def _finish_G_inv(self, damping):
+        """dGdA = 1/(dG dA^T + damping) on the rank that decomposed G (base.py:300-306)."""
+        if self.prediv_eigenvalues:
             if 'dA' not in self.state:
                 raise ValueError('compute_A_inv must be called before '
                                  'compute_G_inv if prediv_eigenvalues '
                                  'is True.')
-            get_ops().outer_recip(self.state['dG'], self.state['dA'], damping,
-                                  self.state['dGdA'])
+            get_ops().outer_recip(self.state['dG'], self.state['dA'], damping, self.state['dGdA'])
+
+    def compute_A_inv(self, damping=0.001, ignore_rank=False):
+        """Eigendecompose A on its assigned rank (kfac/layers/base.py:198-256)."""
+        job = self._inv_job('A', ignore_rank)
+        if job is not None:
+            get_ops().syevd(*job)
+
+    def compute_G_inv(self, damping=0.001, ignore_rank=False):
+        """Eigendecompose G on its assigned rank and, with prediv_eigenvalues, build
+        dGdA = 1/(dG dA^T + damping) there (kfac/layers/base.py:258-308)."""
+        job = self._inv_job('G', ignore_rank)
+        if job is not None:
+            get_ops().syevd(*job)
+            self._finish_G_inv(damping)
 
     def broadcast_inverses(self):
         """Ship QA, QG and dGdA (or dA, dG) over the inverse groups (base.py:129-171).

@@ -443,9 +443,19 @@ class KFAC(optim.Optimizer):
     def compute_inverses(self, damping=0.001):
         """Eigendecompose the factors assigned to this rank (preconditioner.py:555-564).
         A before G: G's pass builds dGdA from both spectra."""
+        jobs, g_done = [], []
         for layer in self.layers:
-            layer.compute_A_inv(damping=damping)
-            layer.compute_G_inv(damping=damping)
+            a_job = layer._inv_job('A')
+            g_job = layer._inv_job('G')
+            if a_job is not None:
+                jobs.append(a_job)
+            if g_job is not None:
+                jobs.append(g_job)
+                g_done.append(layer)
+        # all of this rank's decompositions in one call: they overlap on the library's lanes
+        get_ops().syevd_batch(jobs)
+        for layer in g_done:
+            layer._finish_G_inv(damping)
         if self.check_eig_info:
             infos = [l._info for l in self.layers if l._info is not None]
             if infos and bool(torch.stack(infos).ne(0).any()):

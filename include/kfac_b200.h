@@ -146,6 +146,23 @@ KFB_API size_t kfb_syevd_workspace_bytes(int32_t d);
 KFB_API int kfb_syevd(const float* factor, int64_t ld_factor, int32_t d,
               float* E, int64_t ld_e, float* Q, int64_t ld_q, float* w,
               void* workspace, size_t workspace_bytes, int32_t* dev_info, void* stream);
+/* Many eigendecompositions at once: the jobs are spread (longest first, by d^3) over a small pool
+ * of internal worker lanes - one host thread, CUDA stream and cuSOLVER handle each - so that the
+ * latency-bound small solves overlap each other and the few large ones.  All lanes start after the
+ * work already queued on `stream` and `stream` waits for all of them, so to the caller it behaves
+ * like one asynchronous call on `stream`.  Results are identical to kfb_syevd job by job. */
+typedef struct kfb_syevd_job {
+  const float* factor; int64_t ld_factor;
+  float* E; int64_t ld_e;
+  float* Q; int64_t ld_q;
+  float* w;
+  int32_t* dev_info;
+  int32_t d;
+  int32_t reserved;
+} kfb_syevd_job;
+KFB_API size_t kfb_syevd_batch_workspace_bytes(const kfb_syevd_job* jobs, int32_t n_jobs);
+KFB_API int kfb_syevd_batch(const kfb_syevd_job* jobs, int32_t n_jobs, void* workspace, size_t workspace_bytes,
+                            void* stream);
 /* out <- in^T  (receivers of a broadcast Q rebuild E) */
 KFB_API int kfb_transpose(const float* in, int64_t ld_in, int32_t rows, int32_t cols,
                   float* out, int64_t ld_out, void* stream);

@@ -79,6 +79,10 @@ class OracleOps(object):
         w.copy_(d)
         info.zero_()
 
+    def syevd_batch(self, jobs):
+        for job in jobs:
+            self.syevd(*job)
+
     def transpose(self, src, dst):
         dst.copy_(src.t())
 

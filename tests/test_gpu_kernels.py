@@ -212,6 +212,32 @@ def test_syevd(ops, d):
     torch.testing.assert_close(wc, ref_w, rtol=1e-3, atol=1e-5 * max(scale, 1e-6))
 
 
+def test_syevd_batch_matches_single(ops):
+    """The multi-lane batch gives the same decompositions as one-at-a-time calls."""
+    dims = [3, 64, 64, 147, 256, 33, 512, 64, 100, 8, 300, 1]
+    single, batch, factors = [], [], []
+    for i, d in enumerate(dims):
+        x = torch.randn(d + 3, d, generator=torch.Generator().manual_seed(50 + i))
+        f = (x.t() @ x / x.shape[0]).to(DEV)
+        _, F_ = alloc2d(d, d, DEV)
+        F_.copy_(f)
+        factors.append(F_)
+        for lst in (single, batch):
+            lst.append((F_, alloc2d(d, d, DEV)[1], alloc2d(d, d, DEV)[1], torch.empty(d, device=DEV),
+                        torch.ones(1, dtype=torch.int32, device=DEV)))
+    for job in single:
+        ops.syevd(*job)
+    ops.syevd_batch(batch)
+    torch.cuda.synchronize()
+    for (f, E1, Q1, w1, i1), (_, E2, Q2, w2, i2) in zip(single, batch):
+        assert i1.item() == 0 and i2.item() == 0
+        torch.testing.assert_close(w2, w1, rtol=1e-5, atol=1e-6 * w1.abs().max().item())
+        torch.testing.assert_close(E2, Q2.t(), rtol=0, atol=0)
+        d = f.shape[0]
+        recon = (Q2.double() * w2.double()) @ Q2.double().t()
+        assert (recon - f.double()).abs().max().item() <= 2e-4 * max(f.abs().max().item(), 1e-6)
+
+
 def test_transpose_and_outer_recip(ops):
     a = torch.randn(70, 45)
     _, src = alloc2d(70, 45, DEV)
