@@ -4,7 +4,7 @@
 //   warp 0      TMA producer: 128x32 (A) and 128x32 (B) fp32 boxes, 128B-swizzled, 6-stage ring
 //   warp 1      MMA issuer: 4 x tcgen05.mma.kind::tf32 (M=128, N=128, K=8) per stage, fp32
 //               accumulators in TMEM, double buffered (2 x 128 columns)
-//   warps 2-5   epilogue: tcgen05.ld -> registers -> (x dGdA) -> global, optional <D, Dot>
+//   warps 2-9   epilogue (two warps per TMEM lane quarter, alternating 32-column chunks): tcgen05.ld -> registers -> (x dGdA) -> global, optional <D, Dot>
 //               warp-shuffle reduction (the KL-clip inner product)
 // Operands are consumed as fp32 straight from HBM (kind::tf32 reads the top 19 bits), so there
 // is no conversion pass.
@@ -19,12 +19,17 @@
 namespace kfb {
 namespace {
 
-constexpr int BM = 128, BN = 128, BK = 32;          // BK floats = 128 bytes = one swizzle atom
+// Tile 128 x BN x 32 with BN = 256 when the problem is wide enough, else 128.  fp32 operands are
+// heavy on shared-memory bandwidth (TMA writes + tensor-core reads share 128 B/clk): a 128x128
+// tile needs 256 B/clk to run the MMA pipe flat out, a 128x256 tile 188 B/clk.
+constexpr int BM = 128, BN = 256, BK = 32;          // BK floats = 128 bytes = one swizzle atom
 constexpr int UMMA_K = 8;
-constexpr int kStages = 6;
-constexpr int kStageBytes = (BM + BN) * BK * 4;      // 32 KB
-constexpr int kThreads = 192;
-constexpr int kTmemCols = 2 * BN;                    // double-buffered accumulator
+constexpr int kStages = 4;
+constexpr int kStageBytes = (BM + BN) * BK * 4;      // 48 KB
+constexpr int kEpilogueWarps = 4;                      // one per TMEM lane quarter (8 spills registers and is slower)
+constexpr int kChunkStride = kEpilogueWarps / 4;       // warps sharing a lane quarter interleave chunks
+constexpr int kThreads = 32 * (2 + kEpilogueWarps);
+constexpr int kTmemCols = 2 * BN;                    // double-buffered accumulator: all 512 columns
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 constexpr int kTcBatch = 96;
 
@@ -34,7 +39,9 @@ struct alignas(64) TcProb {
   const float* Mul;
   const float* Dot;
   int64_t ldd, ldmul, lddot;
-  int M, N, K, tiles_n;
+  int M, N, K;
+  int bn;                     // N extent of this problem's tiles: 128 or 256
+  __host__ __device__ int tiles_n() const { return (N + bn - 1) / bn; }
 };
 struct TcBatch {
   int n;
@@ -66,7 +73,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < kStages; ++s) { umma::mbar_init(&full[s], 1); umma::mbar_init(&empty[s], 1); }
-    for (int s = 0; s < 2; ++s) { umma::mbar_init(&tfull[s], 1); umma::mbar_init(&tempty[s], 128); }
+    for (int s = 0; s < 2; ++s) { umma::mbar_init(&tfull[s], 1); umma::mbar_init(&tempty[s], 32 * kEpilogueWarps); }
     umma::fence_barrier_init();
   }
   if (warp == 1) umma::tmem_alloc<kTmemCols>(tmem_slot);
@@ -83,13 +90,14 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         const int p = find_prob(batch, tile);
         const TcProb& pr = batch.probs[p];
         const int local = tile - batch.start[p];
-        const int m0 = (local / pr.tiles_n) * BM, n0 = (local % pr.tiles_n) * BN;
+        const int m0 = (local / pr.tiles_n()) * BM, n0 = (local % pr.tiles_n()) * pr.bn;
         const int kblocks = (pr.K + BK - 1) / BK;
+        const uint32_t tx = (uint32_t)(BM + pr.bn) * BK * 4;
         for (int kb = 0; kb < kblocks; ++kb) {
           umma::mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sa = smem + stage * kStageBytes;
           uint8_t* sb = sa + BM * BK * 4;
-          umma::mbar_arrive_expect_tx(&full[stage], kStageBytes);
+          umma::mbar_arrive_expect_tx(&full[stage], tx);
           umma::tma_load_2d(sa, &pr.mapA, &full[stage], kb * BK, m0);
           umma::tma_load_2d(sb, &pr.mapB, &full[stage], kb * BK, n0);
           if (++stage == kStages) { stage = 0; phase ^= 1; }
@@ -99,12 +107,12 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
-      constexpr uint32_t idesc = umma::make_idesc_tf32(BM, BN);
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0;
       for (int tile = blockIdx.x; tile < batch.total_tiles; tile += gridDim.x) {
         const int p = find_prob(batch, tile);
         const int kblocks = (batch.probs[p].K + BK - 1) / BK;
+        const uint32_t idesc = umma::make_idesc_tf32(BM, batch.probs[p].bn);
         umma::mbar_wait(&tempty[acc], acc_phase ^ 1);      // epilogue drained this accumulator
         umma::tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
@@ -136,48 +144,72 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
       const int p = find_prob(batch, tile);
       const TcProb& pr = batch.probs[p];
       const int local = tile - batch.start[p];
-      const int m0 = (local / pr.tiles_n) * BM, n0 = (local % pr.tiles_n) * BN;
+      const int m0 = (local / pr.tiles_n()) * BM, n0 = (local % pr.tiles_n()) * pr.bn;
+      // Each thread owns one output row (TMEM lane) and walks it 32 columns at a time.  The
+      // epilogue operands (dGdA for the Hadamard stage, the gradient for <v,g>) are loaded one
+      // chunk AHEAD, the first chunk before the accumulator is even complete, so their HBM
+      // latency hides behind the MMAs instead of stalling the TMEM drain (which is what bounds
+      // the small-K stages).
       const int m = m0 + q * 32 + lane;
+      const bool row_ok = m < pr.M;
+      const float* mrow = (pr.Mul && row_ok) ? pr.Mul + (int64_t)m * pr.ldmul + n0 : nullptr;
+      const float* grow = (pr.Dot && row_ok) ? pr.Dot + (int64_t)m * pr.lddot + n0 : nullptr;
+      float* drow = pr.D + (int64_t)m * pr.ldd + n0;
+      const int ncols = min(pr.bn, pr.N - n0);          // valid columns of this tile
+      float4 mm[8], gg[8];
+      auto load_aux = [&](int c, float4 (&dm)[8], float4 (&dg)[8]) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          dm[j] = make_float4(1.f, 1.f, 1.f, 1.f);
+          dg[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+          const int col = c * 32 + 4 * j;
+          if (col + 3 < ncols) {
+            if (mrow) dm[j] = __ldg(reinterpret_cast<const float4*>(mrow + col));
+            if (grow) dg[j] = __ldg(reinterpret_cast<const float4*>(grow + col));
+          } else if (col < ncols) {
+            float tm[4] = {1.f, 1.f, 1.f, 1.f}, tg[4] = {0.f, 0.f, 0.f, 0.f};
+            for (int e = 0; e < 4; ++e)
+              if (col + e < ncols) {
+                if (mrow) tm[e] = mrow[col + e];
+                if (grow) tg[e] = grow[col + e];
+              }
+            dm[j] = make_float4(tm[0], tm[1], tm[2], tm[3]);
+            dg[j] = make_float4(tg[0], tg[1], tg[2], tg[3]);
+          }
+        }
+      };
+      const int half = (warp - 2) >> 2;                  // which of the two warps of this lane quarter
+      const int nchunks = (ncols + 31) / 32;
+      if (half < nchunks) load_aux(half, mm, gg);
       umma::mbar_wait(&tfull[acc], acc_phase);
       umma::tc_fence_after();
       const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
+      for (int c = half; c < nchunks; c += kChunkStride) {
         uint32_t r[32];
         umma::tmem_ld_32x32(taddr + c * 32, r);
+        float4 mm_next[8], gg_next[8];
+        if (c + kChunkStride < nchunks) load_aux(c + kChunkStride, mm_next, gg_next);
         umma::tmem_ld_wait();
-        const int nb = n0 + c * 32;
-        if (m < pr.M && nb < pr.N) {
-          float* drow = pr.D + (int64_t)m * pr.ldd + nb;
-          const float* mrow = pr.Mul ? pr.Mul + (int64_t)m * pr.ldmul + nb : nullptr;
-          const float* grow = pr.Dot ? pr.Dot + (int64_t)m * pr.lddot + nb : nullptr;
-          if (nb + 32 <= pr.N) {
+        if (row_ok) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              float4 v = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
-                                     __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
-              if (mrow) {
-                float4 mm = *reinterpret_cast<const float4*>(mrow + 4 * j);
-                v.x *= mm.x; v.y *= mm.y; v.z *= mm.z; v.w *= mm.w;
-              }
-              *reinterpret_cast<float4*>(drow + 4 * j) = v;
-              if (grow) {
-                float4 gg = *reinterpret_cast<const float4*>(grow + 4 * j);
-                dot = fmaf(v.x, gg.x, fmaf(v.y, gg.y, fmaf(v.z, gg.z, fmaf(v.w, gg.w, dot))));
-              }
+          for (int j = 0; j < 8; ++j) {
+            const int col = c * 32 + 4 * j;
+            float4 v = make_float4(__uint_as_float(r[4 * j]) * mm[j].x, __uint_as_float(r[4 * j + 1]) * mm[j].y,
+                                   __uint_as_float(r[4 * j + 2]) * mm[j].z, __uint_as_float(r[4 * j + 3]) * mm[j].w);
+            if (col + 3 < ncols) {
+              *reinterpret_cast<float4*>(drow + col) = v;
+            } else if (col < ncols) {
+              const float tv[4] = {v.x, v.y, v.z, v.w};
+              for (int e = 0; e < 4; ++e)
+                if (col + e < ncols) drow[col + e] = tv[e];
             }
-          } else {
-            const int lim = pr.N - nb;
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              if (j < lim) {
-                float v = __uint_as_float(r[j]);
-                if (mrow) v *= mrow[j];
-                drow[j] = v;
-                if (grow) dot = fmaf(v, grow[j], dot);
-              }
-            }
+            dot = fmaf(v.x, gg[j].x, fmaf(v.y, gg[j].y, fmaf(v.z, gg[j].z, fmaf(v.w, gg[j].w, dot))));
           }
+        }
+        if (c + kChunkStride < nchunks) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) { mm[j] = mm_next[j]; gg[j] = gg_next[j]; }
         }
       }
       umma::tc_fence_before();
@@ -262,6 +294,10 @@ int gemm_grouped_tc(Context* ctx, const GemmProb* probs, int n, float* dot_acc, 
     KFB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     attr_set = true;
   }
+  // longest tiles first: with the static round-robin tile schedule this is close to LPT
+  std::vector<GemmProb> sorted(probs, probs + n);
+  std::stable_sort(sorted.begin(), sorted.end(), [](const GemmProb& a, const GemmProb& b) { return a.K > b.K; });
+  probs = sorted.data();
   static TcBatch batch;   // 32 KB: too large for the stack of some callers; calls are serialised per process
   static std::mutex mu;
   std::lock_guard<std::mutex> lock(mu);
@@ -273,12 +309,13 @@ int gemm_grouped_tc(Context* ctx, const GemmProb* probs, int n, float* dot_acc, 
       TcProb& t = batch.probs[i];
       int rc = get_map(ctx, g.A, g.lda, g.M, g.K, BM, &t.mapA);
       if (rc) return rc;
-      rc = get_map(ctx, g.B, g.ldb, g.N, g.K, BN, &t.mapB);
+      t.bn = g.N > 128 ? 256 : 128;
+      rc = get_map(ctx, g.B, g.ldb, g.N, g.K, t.bn, &t.mapB);
       if (rc) return rc;
       t.D = g.D; t.Mul = g.Mul; t.Dot = g.Dot; t.ldd = g.ldd; t.ldmul = g.ldmul; t.lddot = g.lddot;
-      t.M = g.M; t.N = g.N; t.K = g.K; t.tiles_n = ceil_div(g.N, BN);
+      t.M = g.M; t.N = g.N; t.K = g.K;
       batch.start[i] = tiles;
-      tiles += ceil_div(g.M, BM) * t.tiles_n;
+      tiles += ceil_div(g.M, BM) * t.tiles_n();
     }
     batch.start[batch.n] = tiles;
     batch.total_tiles = tiles;

@@ -212,7 +212,8 @@ int kfb_precondition(const kfb_precond_job* jobs, int32_t n_jobs, float* vg_acc,
   KFB_REQUIRE(n_jobs >= 0 && (jobs || n_jobs == 0), "bad job array");
   if (n_jobs == 0) return KFB_OK;
   cudaStream_t stream = (cudaStream_t)stream_;
-  std::vector<GradJob> pack(n_jobs);
+  std::vector<GradJob> pack;
+  pack.reserve(n_jobs);
   std::vector<GemmProb> s1(n_jobs), s2(n_jobs), s3(n_jobs), s4(n_jobs);
   for (int i = 0; i < n_jobs; ++i) {
     const kfb_precond_job& j = jobs[i];
@@ -222,13 +223,23 @@ int kfb_precondition(const kfb_precond_job* jobs, int32_t n_jobs, float* vg_acc,
     KFB_REQUIRE(!j.has_bias || j.bias_grad, "precond job %d: has_bias without bias_grad", i);
     KFB_REQUIRE(j.ld_a >= j.da && j.ld_g >= j.dg && j.ld_dgda >= j.da && j.ld_v >= j.da && j.ld_t >= j.dg,
                 "precond job %d: pitch too small", i);
-    GradJob& g = pack[i];
-    g.wg = (float*)j.weight_grad; g.bg = (float*)j.bias_grad; g.v = j.gmat; g.ld = j.ld_v;
-    g.da = j.da; g.dg = j.dg; g.nw = j.da - (j.has_bias ? 1 : 0); g.pad_ = 0;
+    // Without a bias column the contiguous weight gradient already IS the [dg x da] matrix; if
+    // its rows are 16-byte aligned the GEMMs read it in place and nothing is packed.
+    const float* gm = j.gmat;
+    int64_t ld_gm = j.ld_v;
+    if (!j.has_bias && (j.da & 3) == 0 && (((uintptr_t)j.weight_grad) & 15) == 0) {
+      gm = j.weight_grad;
+      ld_gm = j.da;
+    } else {
+      GradJob g;
+      g.wg = (float*)j.weight_grad; g.bg = (float*)j.bias_grad; g.v = j.gmat; g.ld = j.ld_v;
+      g.da = j.da; g.dg = j.dg; g.nw = j.da - (j.has_bias ? 1 : 0); g.pad_ = 0;
+      pack.push_back(g);
+    }
     GemmProb z;
     memset(&z, 0, sizeof(z));
     // T = EA gmat^T
-    s1[i] = z; s1[i].A = j.EA; s1[i].lda = j.ld_a; s1[i].B = j.gmat; s1[i].ldb = j.ld_v;
+    s1[i] = z; s1[i].A = j.EA; s1[i].lda = j.ld_a; s1[i].B = gm; s1[i].ldb = ld_gm;
     s1[i].D = j.T; s1[i].ldd = j.ld_t; s1[i].M = j.da; s1[i].N = j.dg; s1[i].K = j.da;
     // V = (EG T^T) * dGdA
     s2[i] = z; s2[i].A = j.EG; s2[i].lda = j.ld_g; s2[i].B = j.T; s2[i].ldb = j.ld_t;
@@ -240,9 +251,9 @@ int kfb_precondition(const kfb_precond_job* jobs, int32_t n_jobs, float* vg_acc,
     // out = QG T^T, dot with gmat
     s4[i] = z; s4[i].A = j.QG; s4[i].lda = j.ld_g; s4[i].B = j.T; s4[i].ldb = j.ld_t;
     s4[i].D = j.out; s4[i].ldd = j.ld_v; s4[i].M = j.dg; s4[i].N = j.da; s4[i].K = j.dg;
-    if (vg_acc) { s4[i].Dot = j.gmat; s4[i].lddot = j.ld_v; }
+    if (vg_acc) { s4[i].Dot = gm; s4[i].lddot = ld_gm; }
   }
-  rc = run_grad<kPack>(pack.data(), n_jobs, nullptr, nullptr, 0.f, 0.f, 1.f, stream);
+  rc = run_grad<kPack>(pack.data(), (int)pack.size(), nullptr, nullptr, 0.f, 0.f, 1.f, stream);
   if (rc) return rc;
   if ((rc = run_stage(ctx, s1, nullptr, stream))) return rc;
   if ((rc = run_stage(ctx, s2, nullptr, stream))) return rc;
