@@ -144,7 +144,7 @@ def capture(model, pre, x, y):
     return caps, grads
 
 
-def algorithmic_work(pre, caps):
+def algorithmic_work(pre, caps, rank=0):
     """FLOPs per stage from the layer shapes: SYRK on the upper triangle
     K*d*(d+1); precondition 4*dg*da*(da+dg); plus minimum bytes of the factor stage."""
     syrk = precond = 0
@@ -160,7 +160,8 @@ def algorithmic_work(pre, caps):
             ka = a.numel() // a.shape[-1]
             kg = g.numel() // g.shape[-1]
         syrk += ka * da * (da + 1) + kg * dg * (dg + 1)
-        precond += 4 * dg * da * (da + dg)
+        if l.compute_grad_ranks is None or rank in l.compute_grad_ranks:
+            precond += 4 * dg * da * (da + dg)      # only the layers THIS rank preconditions
         in_bytes += (a.numel() + g.numel()) * 4
         state_bytes += 2 * 4 * (da * (da + 1) // 2 + dg * (dg + 1) // 2)   # read + write the triangle
     return dict(syrk_flops=syrk, precond_flops=precond, factor_bytes=in_bytes + state_bytes)
@@ -232,7 +233,18 @@ def run_ours(args):
     torch.cuda.set_device(local)
     device = torch.device('cuda', local)
     if dist_on:
-        torch.distributed.init_process_group('nccl', device_id=device)
+        # NCCL prints its version banner on stdout at the first collective; keep stdout for the
+        # one JSON line by pointing fd 1 at stderr until the communicator is up
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            torch.distributed.init_process_group('nccl', device_id=device)
+            torch.distributed.all_reduce(torch.zeros(1, device=device))
+            torch.cuda.synchronize()
+        finally:
+            os.dup2(saved, 1)
+            os.close(saved)
     ops = _native.get_ops()
     ops._enter(torch.zeros(1, device=device))
     ops.set_mma_mode(args.mma_mode)
@@ -250,7 +262,6 @@ def run_ours(args):
             if b is not None:
                 torch.distributed.all_reduce(b)
                 b /= world
-    work = algorithmic_work(pre, caps)
     t_factor = StageTimer(ops, 'factor_update')
     t_precond = StageTimer(ops, 'precondition')
     t_syevd = StageTimer(ops, 'syevd_batch')
@@ -262,6 +273,7 @@ def run_ours(args):
 
     for _ in range(args.warmup):
         one_step()
+    work = algorithmic_work(pre, caps, rank)     # after the warm-up: the worker assignment exists
     sampler = ClockSampler(local)
     for t in (t_factor, t_precond, t_syevd):
         t.reset(True)

@@ -1,0 +1,41 @@
+"""Summarise an .ncu-rep (ncu --set full) into a small text table for profiles/.
+Usage: python tools/ncu_summary.py report.ncu-rep > profiles/xxx.txt"""
+import csv
+import io
+import subprocess
+import sys
+
+METRICS = [
+    'gpu__time_duration.sum', 'sm__cycles_elapsed.max', 'launch__registers_per_thread', 'launch__grid_size',
+    'launch__block_size', 'dram__bytes_read.sum', 'dram__bytes_write.sum',
+    'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed',
+    'sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed',
+    'sm__pipe_tensor_cycles_active.max.pct_of_peak_sustained_elapsed',
+    'sm__ops_path_tensor_op_utchmma_src_tf32_dst_fp32_sparsity_off.avg.pct_of_peak_sustained_elapsed',
+    'l1tex__data_pipe_tc_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed',
+    'l1tex__m_xbar2l1tex_read_bytes.sum', 'lts__t_sector_hit_rate.pct', 'l1tex__t_sector_hit_rate.pct',
+    'lts__throughput.avg.pct_of_peak_sustained_elapsed', 'sm__throughput.avg.pct_of_peak_sustained_elapsed',
+    'sm__warps_active.avg.pct_of_peak_sustained_active', 'smsp__inst_executed.sum',
+    'sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_elapsed',
+    'l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum',
+    'smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio',
+    'smsp__average_warps_issue_stalled_wait_per_issue_active.ratio',
+]
+
+
+def main():
+    rep = sys.argv[1]
+    raw = subprocess.run(['ncu', '-i', rep, '--page', 'raw', '--csv'], stdout=subprocess.PIPE, text=True).stdout
+    rows = list(csv.reader(io.StringIO(raw)))
+    hdr, units = rows[0], rows[1]
+    name_i = hdr.index('Kernel Name')
+    print('# %s' % rep)
+    print('# kernels: %s' % ', '.join(sorted({r[name_i].split('(')[0] for r in rows[2:]})))
+    for m in METRICS:
+        if m in hdr:
+            i = hdr.index(m)
+            print('%-100s %-10s %s' % (m, units[i], '  '.join(r[i] for r in rows[2:])))
+
+
+if __name__ == '__main__':
+    main()
