@@ -37,9 +37,11 @@ struct DevJob {
   int use_tc;            // 1: handled by the tcgen05 SYRK
 };
 
-struct TcItem {            // one unit of tensor-core SYRK work
-  int job, seg, ti, tj;    // 128-wide tile pair (ti <= tj) of one segment of one job
-  int64_t k_begin, k_end;  // rows of X
+struct TcItem {            // one unit of tensor-core SYRK work: a 2x2 block of 128-wide tiles
+  int job, seg;
+  int a0, b0;              // first row tile / first column tile (a0 <= b0; equal on the diagonal)
+  int mi, nj;              // tiles in the block's rows / columns (1 or 2)
+  uint32_t k_begin, k_end; // rows of X
 };
 
 struct FactorPlan {

@@ -1,11 +1,14 @@
-// Factor SYRK on the 5th-generation tensor cores:  F += w * X^T X  for one 128x128 upper-triangle
-// tile pair and one K chunk per work item, X read IN PLACE from the captured NCHW tensors
-// (implicit im2col: the unfolded matrix of kfac/layers/conv.py:50-70 is never materialised).
+// Factor SYRK on the 5th-generation tensor cores:  F += w * X^T X  for one 256x256 block (2x2
+// tiles of 128) of the upper triangle and one K chunk per work item, X read IN PLACE from the
+// captured NCHW tensors (implicit im2col: the unfolded matrix of kfac/layers/conv.py:50-70 is
+// never materialised).  Blocking 2x2 halves the operand gathering per FLOP (4 tiles feed 4
+// tile products instead of 2 tiles per product) and the shared-memory traffic per MMA.
 //
 //   warps 0-3   epilogue: tcgen05.ld -> x weight -> red.global.add.v4.f32 into the job's scratch
-//   warp  4     MMA issuer: tcgen05.mma.kind::tf32, M=128 N=128 K=8, fp32 accumulators in TMEM
-//               (double buffered); a diagonal tile pair uses ONE smem tile for both operands
-//   warps 5-12  producers: gather X^T tiles (128 features x 32 rows of X, K-major) from global
+//   warp  4     MMA issuer: tcgen05.mma.kind::tf32, M=128, N=256 (or 128), K=8; the block's four
+//               fp32 accumulators fill all 512 TMEM columns; a diagonal block loads its two
+//               tiles once for both operands and skips the lower-left product
+//   warps 5-20  producers: gather X^T tiles (128 features x 32 rows of X, K-major) from global
 //               memory straight into the 128B-swizzled UMMA shared-memory layout
 //               - NCHW operands with 16-byte alignable rows: 128-bit loads/stores
 //               - im2col operands: one 32-bit load per element with a per-lane validity bitmask
@@ -23,13 +26,13 @@ namespace {
 constexpr int TM = 128;                 // tile side (features)
 constexpr int BK = 32;                  // rows of X per stage = one 128-byte swizzle row
 constexpr int UMMA_K = 8;
-constexpr int kStages = 5;
+constexpr int kStages = 3;
 constexpr int kTileBytes = TM * BK * 4; // 16 KB
-constexpr int kStageBytes = 2 * kTileBytes;
+constexpr int kStageBytes = 4 * kTileBytes;          // slots 0,1: the block's row tiles; 2,3: column tiles
 constexpr int kProducerWarps = 16;
 constexpr int kRowsPerWarp = TM / kProducerWarps;   // 8 rows of each tile per producer warp
 constexpr int kThreads = 32 * (4 + 1 + kProducerWarps);
-constexpr int kTmemCols = 256;
+constexpr int kTmemCols = 512;
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256;
 
 // A tile row (= one feature of X) is described by ONE packed word: (element offset << 6) | bit,
@@ -75,14 +78,15 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
   uint64_t* full = (uint64_t*)(smem + kStages * kStageBytes);
   uint64_t* empty = full + kStages;
   uint64_t* tfull = empty + kStages;
-  uint64_t* tempty = tfull + 2;
-  uint32_t* tmem_slot = (uint32_t*)(tempty + 2);
+  uint64_t* tempty = tfull + 1;
+  uint32_t* tmem_slot = (uint32_t*)(tempty + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) { umma::mbar_init(&full[s], kProducerWarps); umma::mbar_init(&empty[s], 1); }
-    for (int s = 0; s < 2; ++s) { umma::mbar_init(&tfull[s], 1); umma::mbar_init(&tempty[s], 128); }
+    umma::mbar_init(tfull, 1);
+    umma::mbar_init(tempty, 128);
     umma::fence_barrier_init();
   }
   if (warp == 4) umma::tmem_alloc<kTmemCols>(tmem_slot);
@@ -103,53 +107,66 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
       const TcItem item = items[it];
       const DevSegment s = segs[item.seg];
       const int d = jobs[item.job].d;
-      const bool diag = item.ti == item.tj;
-      const int n_tiles = diag ? 1 : 2;
+      const bool diag = item.a0 == item.b0;
+      // smem slots to fill: row tiles a0.. (slots 0..mi-1) and, off the diagonal, column tiles
+      // b0.. (slots 2..2+nj-1)
+      const int n_slots = diag ? item.mi : item.mi + item.nj;
+      int slot_of[4], tile_of[4];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const bool is_a = t < item.mi;
+        slot_of[t] = is_a ? t : 2 + (t - item.mi);
+        tile_of[t] = is_a ? item.a0 + t : item.b0 + (t - item.mi);
+      }
       const int S = s.oh * s.ow;
       const uint32_t uS = (uint32_t)S, uow = (uint32_t)s.ow;
-      const uint32_t k_end32 = (uint32_t)item.k_end;       // K < 2^31 (checked on the host)
+      const uint32_t k_end32 = item.k_end;       // K < 2^31 (checked on the host)
       const bool vec4 = s.kind == KFB_SEG_NCHW && (S & 3) == 0 && (((uintptr_t)s.data) & 15) == 0;
       const bool wide = s.kind == KFB_SEG_IM2COL && s.kh * s.kw > 30;
-      // does this warp own the bias feature's row in tile A / tile B?
-      int bias_row[2] = {-1, -1};
+      // does this warp own the bias feature's row in one of the tiles?
+      int bias_slot = -1, bias_row = 0;
       if (s.has_bias) {
-        for (int t = 0; t < n_tiles; ++t) {
-          int local = (d - 1) - (t == 0 ? item.ti : item.tj) * TM;
-          if (local >= 0 && local < TM && (local % kProducerWarps) == pw) bias_row[t] = local;
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          int local = (d - 1) - tile_of[t] * TM;
+          if (t < n_slots && local >= 0 && local < TM && (local % kProducerWarps) == pw) {
+            bias_slot = slot_of[t];
+            bias_row = local;
+          }
         }
       }
 
       if (vec4) {
         // ---- NCHW, 16B-alignable: 8 lanes x float4 = one tile row (32 k), 4 rows per instruction
-        uint32_t info[2][2];
+        uint32_t info[4][2];
 #pragma unroll
-        for (int t = 0; t < 2; ++t)
+        for (int t = 0; t < 4; ++t)
 #pragma unroll
           for (int i = 0; i < 2; ++i)
-            info[t][i] = row_info(s, d, (t == 0 ? item.ti : item.tj) * TM + pw + kProducerWarps * (4 * i + vec_rsub));
-        for (uint32_t k0 = (uint32_t)item.k_begin; k0 < k_end32; k0 += BK) {
+            info[t][i] = t < n_slots ? row_info(s, d, tile_of[t] * TM + pw + kProducerWarps * (4 * i + vec_rsub)) : kBitNever;
+        for (uint32_t k0 = item.k_begin; k0 < k_end32; k0 += BK) {
           umma::mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* st = smem + stage * kStageBytes;
           const uint32_t k = k0 + 4 * vec_kq;
           const bool kin = k < k_end32;
           const uint32_t n = k / uS;
           const float* src = s.data + ((int64_t)n * s.c * S + (k - n * uS));
-          float4 v[2][2];
+          float4 v[4][2];
 #pragma unroll
-          for (int t = 0; t < 2; ++t)
+          for (int t = 0; t < 4; ++t)
 #pragma unroll
             for (int i = 0; i < 2; ++i) {
               v[t][i] = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (t < n_tiles && kin && (info[t][i] & 63u) == kBitAlways)
+              if (kin && (info[t][i] & 63u) == kBitAlways)
                 v[t][i] = __ldg(reinterpret_cast<const float4*>(src + (info[t][i] >> 6)));
             }
 #pragma unroll
-          for (int t = 0; t < 2; ++t)
+          for (int t = 0; t < 4; ++t)
 #pragma unroll
             for (int i = 0; i < 2; ++i)
-              if (t < n_tiles) {
+              if (t < n_slots) {
                 const int r = pw + kProducerWarps * (4 * i + vec_rsub);
-                *reinterpret_cast<float4*>(st + t * kTileBytes + r * 128 + ((vec_kq ^ (r & 7)) << 4)) = v[t][i];
+                *reinterpret_cast<float4*>(st + slot_of[t] * kTileBytes + r * 128 + ((vec_kq ^ (r & 7)) << 4)) = v[t][i];
               }
           umma::fence_proxy_async_smem();
           __syncwarp();
@@ -157,14 +174,14 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       } else {
-        // ---- general gather: one X row per lane, this warp's 8 (+8) tile rows per stage
-        uint32_t info[2][kRowsPerWarp];
+        // ---- general gather: one X row per lane, this warp's 8 rows of every tile per stage
+        uint32_t info[4][kRowsPerWarp];
 #pragma unroll
-        for (int t = 0; t < 2; ++t)
+        for (int t = 0; t < 4; ++t)
 #pragma unroll
           for (int j = 0; j < kRowsPerWarp; ++j)
-            info[t][j] = row_info(s, d, (t == 0 ? item.ti : item.tj) * TM + pw + kProducerWarps * j);
-        for (uint32_t k0 = (uint32_t)item.k_begin; k0 < k_end32; k0 += BK) {
+            info[t][j] = t < n_slots ? row_info(s, d, tile_of[t] * TM + pw + kProducerWarps * j) : kBitNever;
+        for (uint32_t k0 = item.k_begin; k0 < k_end32; k0 += BK) {
           umma::mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* st = smem + stage * kStageBytes + pw * 128 + lane_off;
           const uint32_t k = k0 + lane;
@@ -190,38 +207,34 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
               mhi = (uint32_t)(m >> 32);
             }
           }
-          float v[2][kRowsPerWarp];
-          if (!wide) {
-            // narrow: (ky,kx) bits in mlo; move "always" to bit 30 so one word decides everything.
-            // row_info's bit field is 6 bits: 62 -> (62 & 31) = 30, 63 -> 31 (never set).
-            const uint32_t m = mlo | ((mhi >> (kBitAlways - 32)) << 30);
+          // narrow: (ky,kx) bits in mlo; "always" moves to bit 30 so one word decides everything
+          // (row_info's 6-bit field: 62 & 31 = 30, 63 & 31 = 31 which is never set)
+          const uint32_t mnarrow = mlo | ((mhi >> (kBitAlways - 32)) << 30);
+          // two tiles (16 independent loads per lane) in flight at a time
 #pragma unroll
-            for (int t = 0; t < 2; ++t)
+          for (int tp = 0; tp < 2; ++tp) {
+            if (2 * tp >= n_slots) break;
+            float v[2][kRowsPerWarp];
 #pragma unroll
-              for (int j = 0; j < kRowsPerWarp; ++j) {
-                v[t][j] = 0.f;
-                if (t < n_tiles && row_valid<false>(info[t][j], m, 0u)) v[t][j] = __ldg(src + (info[t][j] >> 6));
-              }
-          } else {
-#pragma unroll
-            for (int t = 0; t < 2; ++t)
+            for (int u = 0; u < 2; ++u)
 #pragma unroll
               for (int j = 0; j < kRowsPerWarp; ++j) {
-                v[t][j] = 0.f;
-                if (t < n_tiles && row_valid<true>(info[t][j], mlo, mhi)) v[t][j] = __ldg(src + (info[t][j] >> 6));
+                const uint32_t inf = info[2 * tp + u][j];
+                const bool ok = wide ? row_valid<true>(inf, mlo, mhi) : row_valid<false>(inf, mnarrow, 0u);
+                v[u][j] = 0.f;
+                if (ok) v[u][j] = __ldg(src + (inf >> 6));
               }
+#pragma unroll
+            for (int u = 0; u < 2; ++u)
+#pragma unroll
+              for (int j = 0; j < kRowsPerWarp; ++j)
+                if (2 * tp + u < n_slots)
+                  *reinterpret_cast<float*>(st + slot_of[2 * tp + u] * kTileBytes + j * (kProducerWarps * 128)) = v[u][j];
           }
-#pragma unroll
-          for (int t = 0; t < 2; ++t)
-#pragma unroll
-            for (int j = 0; j < kRowsPerWarp; ++j)
-              if (t < n_tiles)
-                *reinterpret_cast<float*>(st + t * kTileBytes + j * (kProducerWarps * 128)) = v[t][j];
           // the bias feature is the constant 1 wherever the X row exists
-          for (int t = 0; t < n_tiles; ++t)
-            if (bias_row[t] >= 0)
-              *reinterpret_cast<float*>(smem + stage * kStageBytes + t * kTileBytes + bias_row[t] * 128 + lane_off) =
-                  kin ? 1.f : 0.f;
+          if (bias_slot >= 0)
+            *reinterpret_cast<float*>(smem + stage * kStageBytes + bias_slot * kTileBytes + bias_row * 128 + lane_off) =
+                kin ? 1.f : 0.f;
           umma::fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) umma::mbar_arrive(&full[stage]);
@@ -232,73 +245,84 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
   } else if (warp == 4) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
-      constexpr uint32_t idesc = umma::make_idesc_tf32(TM, TM);
       int stage = 0; uint32_t phase = 0;
-      int acc = 0; uint32_t acc_phase = 0;
+      uint32_t acc_phase = 0;
       for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
         const TcItem item = items[it];
-        const bool diag = item.ti == item.tj;
-        umma::mbar_wait(&tempty[acc], acc_phase ^ 1);
+        const bool diag = item.a0 == item.b0;
+        umma::mbar_wait(tempty, acc_phase ^ 1);            // the epilogue has drained TMEM
         umma::tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * TM;
         bool first = true;
-        for (int64_t k0 = item.k_begin; k0 < item.k_end; k0 += BK) {
+        for (uint32_t k0 = item.k_begin; k0 < item.k_end; k0 += BK) {
           umma::mbar_wait(&full[stage], phase);
           umma::tc_fence_after();
-          const uint32_t sa = umma::smem_u32(smem + stage * kStageBytes);
-          const uint64_t da = umma::make_kmajor_sw128_desc(sa);
-          const uint64_t db = diag ? da : umma::make_kmajor_sw128_desc(sa + kTileBytes);
+          const uint32_t sbase = umma::smem_u32(smem + stage * kStageBytes);
+          for (int m = 0; m < item.mi; ++m) {
+            // row tile m against column tiles n0..nj-1 in ONE instruction (N = 128 or 256); on the
+            // diagonal the column tiles are the row tiles and products below the diagonal are skipped
+            const int n0 = diag ? m : 0;
+            const int ncols = (item.nj - n0) * TM;
+            const uint64_t da = umma::make_kmajor_sw128_desc(sbase + m * kTileBytes);
+            const uint64_t db = umma::make_kmajor_sw128_desc(sbase + ((diag ? 0 : 2) + n0) * kTileBytes);
+            const uint32_t idesc = umma::make_idesc_tf32(TM, ncols);
+            const uint32_t d_tmem = tmem_base + m * 256 + n0 * TM;
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k) {
-            umma::mma_tf32_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, (first && k == 0) ? 0u : 1u);
+            for (int k = 0; k < BK / UMMA_K; ++k)
+              umma::mma_tf32_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, (first && k == 0) ? 0u : 1u);
           }
           first = false;
           umma::tc_commit(&empty[stage]);
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
-        umma::tc_commit(&tfull[acc]);
-        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        umma::tc_commit(tfull);
+        acc_phase ^= 1;
       }
     }
   } else {
     // ===================== epilogue (warps 0..3) =====================
     const int q = warp;
-    int acc = 0; uint32_t acc_phase = 0;
+    uint32_t acc_phase = 0;
     for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
       const TcItem item = items[it];
       const DevJob& job = jobs[item.job];
       const float weight = segs[item.seg].weight;
       const int d = job.d;
-      const int i = item.ti * TM + q * 32 + lane;
-      const int j0 = item.tj * TM;
-      umma::mbar_wait(&tfull[acc], acc_phase);
+      const bool diag = item.a0 == item.b0;
+      umma::mbar_wait(tfull, acc_phase);
       umma::tc_fence_after();
-      const uint32_t taddr = tmem_base + acc * TM + ((uint32_t)(q * 32) << 16);
+      for (int m = 0; m < item.mi; ++m) {
+        const int i = (item.a0 + m) * TM + q * 32 + lane;
+        for (int nn = diag ? m : 0; nn < item.nj; ++nn) {
+          const int j0 = (item.b0 + nn) * TM;
+          const uint32_t taddr = tmem_base + m * 256 + nn * TM + ((uint32_t)(q * 32) << 16);
 #pragma unroll 1
-      for (int c = 0; c < TM / 32; ++c) {
-        uint32_t r[32];
-        umma::tmem_ld_32x32(taddr + c * 32, r);
-        umma::tmem_ld_wait();
-        const int jb = j0 + c * 32;
-        if (i < d && jb < d && jb + 31 >= i) {
-          float* row = job.scratch + (int64_t)i * job.ld_scratch + jb;
+          for (int c = 0; c < TM / 32; ++c) {
+            const int jb = j0 + c * 32;
+            if (jb >= d) break;                               // warp-uniform
+            uint32_t r[32];
+            umma::tmem_ld_32x32(taddr + c * 32, r);
+            umma::tmem_ld_wait();
+            if (i < d && jb + 31 >= i) {
+              float* row = job.scratch + (int64_t)i * job.ld_scratch + jb;
 #pragma unroll
-          for (int g = 0; g < 8; ++g) {
-            const int j = jb + 4 * g;
-            if (j + 3 < d && j >= i) {
-              red_add_v4(row + 4 * g, __uint_as_float(r[4 * g]) * weight, __uint_as_float(r[4 * g + 1]) * weight,
-                         __uint_as_float(r[4 * g + 2]) * weight, __uint_as_float(r[4 * g + 3]) * weight);
-            } else {
+              for (int g = 0; g < 8; ++g) {
+                const int j = jb + 4 * g;
+                if (j + 3 < d && j >= i) {
+                  red_add_v4(row + 4 * g, __uint_as_float(r[4 * g]) * weight, __uint_as_float(r[4 * g + 1]) * weight,
+                             __uint_as_float(r[4 * g + 2]) * weight, __uint_as_float(r[4 * g + 3]) * weight);
+                } else {
 #pragma unroll
-              for (int e = 0; e < 4; ++e)
-                if (j + e < d && j + e >= i) atomicAdd(row + 4 * g + e, __uint_as_float(r[4 * g + e]) * weight);
+                  for (int e = 0; e < 4; ++e)
+                    if (j + e < d && j + e >= i) atomicAdd(row + 4 * g + e, __uint_as_float(r[4 * g + e]) * weight);
+                }
+              }
             }
           }
         }
       }
       umma::tc_fence_before();
-      umma::mbar_arrive(&tempty[acc]);
-      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      umma::mbar_arrive(tempty);
+      acc_phase ^= 1;
     }
   }
 
@@ -314,30 +338,35 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
 
 // Build the tensor-core work list for the jobs marked use_tc: (tile pair, K chunk) items, longest first.
 void plan_syrk_tc(FactorPlan* plan) {
-  constexpr int64_t kChunk = 4096;
+  constexpr int64_t kChunk = 2048;     // rows of X per item: ~64 stages of 4 tile products
   plan->tc_items.clear();
   for (size_t ji = 0; ji < plan->jobs.size(); ++ji) {
     const DevJob& j = plan->jobs[ji];
     if (!j.use_tc) continue;
-    const int T = ceil_div(j.d, TM);
+    const int T = ceil_div(j.d, TM);          // 128-wide tiles per side
+    const int TB = ceil_div(T, 2);            // 256-wide blocks per side
     for (int si = 0; si < j.n_segments; ++si) {
       const DevSegment& s = plan->segs[j.seg_start + si];
       const int64_t nch = std::max<int64_t>(1, ceil_div64(s.K, kChunk));
       const int64_t len = ceil_div64(ceil_div64(s.K, nch), BK) * BK;
       for (int64_t k = 0; k < s.K; k += len)
-        for (int ti = 0; ti < T; ++ti)
-          for (int tj = ti; tj < T; ++tj) {
+        for (int bi = 0; bi < TB; ++bi)
+          for (int bj = bi; bj < TB; ++bj) {
             TcItem it;
-            it.job = (int)ji; it.seg = j.seg_start + si; it.ti = ti; it.tj = tj;
-            it.k_begin = k; it.k_end = std::min<int64_t>(s.K, k + len);
+            it.job = (int)ji; it.seg = j.seg_start + si;
+            it.a0 = 2 * bi; it.b0 = 2 * bj;
+            it.mi = std::min(2, T - it.a0); it.nj = std::min(2, T - it.b0);
+            it.k_begin = (uint32_t)k; it.k_end = (uint32_t)std::min<int64_t>(s.K, k + len);
             plan->tc_items.push_back(it);
           }
     }
   }
-  std::stable_sort(plan->tc_items.begin(), plan->tc_items.end(), [](const TcItem& a, const TcItem& b) {
-    int64_t ca = (a.k_end - a.k_begin) * (a.ti == a.tj ? 1 : 2), cb = (b.k_end - b.k_begin) * (b.ti == b.tj ? 1 : 2);
-    return ca > cb;
-  });
+  auto cost = [](const TcItem& a) {
+    int64_t units = a.a0 == a.b0 ? (a.mi * (a.mi + 1)) / 2 : a.mi * a.nj;
+    return (int64_t)(a.k_end - a.k_begin) * units;
+  };
+  std::stable_sort(plan->tc_items.begin(), plan->tc_items.end(),
+                   [&](const TcItem& a, const TcItem& b) { return cost(a) > cost(b); });
 }
 
 int launch_syrk_tc(const FactorPlan& plan, void* workspace, Context* ctx, cudaStream_t stream) {
