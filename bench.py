@@ -271,10 +271,10 @@ def run_ours(args):
         restore_grads(pre, grads)
         pre.step()
 
+    sampler = ClockSampler(local)                # started early: nvidia-smi takes a while to come up
     for _ in range(args.warmup):
         one_step()
     work = algorithmic_work(pre, caps, rank)     # after the warm-up: the worker assignment exists
-    sampler = ClockSampler(local)
     for t in (t_factor, t_precond, t_syevd):
         t.reset(True)
     launches0 = ops.launch_count()
