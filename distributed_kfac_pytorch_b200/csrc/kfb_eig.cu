@@ -2,6 +2,8 @@
 // kernels around it: eigenvalue clip, transpose, outer-product reciprocal.
 #include <cusolverDn.h>
 
+#include <stdlib.h>
+
 #include <algorithm>
 #include <mutex>
 #include <string>
@@ -108,7 +110,12 @@ int kfb_syevd(const float* factor, int64_t ld_factor, int32_t d, float* E, int64
                    workspace_bytes, dev_info, (cudaStream_t)stream_);
 }
 
-// ---- batched: worker lanes -------------------------------------------------------------------------
+// ---- many decompositions at once ---------------------------------------------------------------
+// Two mechanisms, both cuSOLVER:
+//  * same-size groups of small/medium factors go through cusolverDnXsyevBatched (one launch
+//    sequence for the whole group: 22 64x64 solves take 0.4 ms instead of 20 ms);
+//  * the remaining (large or one-of-a-kind) factors run syevd on worker lanes, one host thread +
+//    stream + handle each, longest first.
 namespace {
 constexpr int kMaxLanes = 8;
 struct Lane {
@@ -118,6 +125,8 @@ struct Lane {
 };
 struct LanePool {
   Lane lanes[kMaxLanes];
+  Lane grouped;                 // stream/handle for the XsyevBatched groups
+  cusolverDnParams_t params = nullptr;
   cudaEvent_t start = nullptr;
   bool ready = false;
 };
@@ -129,57 +138,161 @@ int get_pool(kfb::Context* ctx, LanePool** out) {
   LanePool& p = g_pools[ctx->device];
   if (!p.ready) {
     KFB_CUDA(cudaEventCreateWithFlags(&p.start, cudaEventDisableTiming));
-    for (int i = 0; i < kMaxLanes; ++i) {
-      KFB_CUDA(cudaStreamCreateWithFlags(&p.lanes[i].stream, cudaStreamNonBlocking));
-      KFB_CUDA(cudaEventCreateWithFlags(&p.lanes[i].done, cudaEventDisableTiming));
-      if (cusolverDnCreate(&p.lanes[i].handle) != CUSOLVER_STATUS_SUCCESS)
+    for (int i = 0; i <= kMaxLanes; ++i) {
+      Lane& l = i < kMaxLanes ? p.lanes[i] : p.grouped;
+      KFB_CUDA(cudaStreamCreateWithFlags(&l.stream, cudaStreamNonBlocking));
+      KFB_CUDA(cudaEventCreateWithFlags(&l.done, cudaEventDisableTiming));
+      if (cusolverDnCreate(&l.handle) != CUSOLVER_STATUS_SUCCESS)
         KFB_FAIL(KFB_ERR_CUSOLVER, "cusolverDnCreate failed for worker lane %d", i);
     }
+    if (cusolverDnCreateParams(&p.params) != CUSOLVER_STATUS_SUCCESS)
+      KFB_FAIL(KFB_ERR_CUSOLVER, "cusolverDnCreateParams failed");
     p.ready = true;
   }
   *out = &p;
   return KFB_OK;
 }
 
-// longest-processing-time placement of the jobs on the lanes; returns per-lane job lists
-void place_jobs(const kfb_syevd_job* jobs, int n, std::vector<std::vector<int>>* lanes) {
-  int n_lanes = std::min(kMaxLanes, std::max(1, n));
-  lanes->assign(n_lanes, {});
-  std::vector<int> order(n);
-  for (int i = 0; i < n; ++i) order[i] = i;
-  std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return jobs[a].d > jobs[b].d; });
-  std::vector<double> load(n_lanes, 0.0);
-  for (int i : order) {
-    int best = 0;
-    for (int l = 1; l < n_lanes; ++l)
-      if (load[l] < load[best]) best = l;
-    double d = jobs[i].d;
-    load[best] += d * d * d + 2e6;      // + a constant: tiny solves are pure launch latency
-    (*lanes)[best].push_back(i);
-  }
-}
+size_t align256(size_t x) { return (x + 255) / 256 * 256; }
 
 size_t lwork_bytes(cusolverDnHandle_t h, int d) {
   int lwork = 0;
   if (cusolverDnSsyevd_bufferSize(h, CUSOLVER_EIG_MODE_VECTOR, CUBLAS_FILL_MODE_UPPER, d, nullptr, (d + 3) / 4 * 4, nullptr,
                                   &lwork) != CUSOLVER_STATUS_SUCCESS)
     return 0;
-  return ((size_t)lwork * sizeof(float) + 255) / 256 * 256 + 256;
+  return align256((size_t)lwork * sizeof(float)) + 256;
+}
+
+struct Group {
+  int d;
+  std::vector<int> idx;
+  size_t dev_ws = 0, host_ws = 0;
+  size_t off_A = 0, off_W = 0, off_info = 0, off_ws = 0, bytes = 0;   // inside the group region
+};
+struct BatchPlan {
+  std::vector<Group> groups;
+  std::vector<std::vector<int>> lanes;   // job indices per worker lane
+  std::vector<size_t> lane_off;          // workspace offset per lane (+ end)
+  size_t group_off = 0, total = 0;
+};
+
+// measured on B200 (tools/try_syev_batched.py): the batched solver wins for n <= 512 and, with
+// enough matrices to amortise over, up to n = 1024; above that syevd per matrix is faster
+bool batched_wins(int d, size_t count) { return count >= 2 && (d <= 512 || (d <= 1024 && count >= 8)); }
+
+int make_plan(kfb::Context* ctx, LanePool* pool, const kfb_syevd_job* jobs, int n, BatchPlan* plan) {
+  std::vector<int> order(n);
+  for (int i = 0; i < n; ++i) {
+    KFB_REQUIRE(jobs[i].factor && jobs[i].E && jobs[i].Q && jobs[i].w && jobs[i].dev_info && jobs[i].d > 0,
+                "syevd job %d: null argument", i);
+    KFB_REQUIRE(jobs[i].ld_factor >= jobs[i].d && jobs[i].ld_e >= jobs[i].d && jobs[i].ld_q >= jobs[i].d,
+                "syevd job %d: pitch smaller than d", i);
+    order[i] = i;
+  }
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return jobs[a].d > jobs[b].d; });
+  std::vector<int> singles;
+  for (size_t i = 0; i < order.size();) {
+    size_t j = i;
+    while (j < order.size() && jobs[order[j]].d == jobs[order[i]].d) ++j;
+    const int d = jobs[order[i]].d;
+    if (batched_wins(d, j - i)) {
+      Group g;
+      g.d = d;
+      g.idx.assign(order.begin() + i, order.begin() + j);
+      const int64_t cnt = (int64_t)g.idx.size();
+      if (cusolverDnXsyevBatched_bufferSize(pool->grouped.handle, pool->params, CUSOLVER_EIG_MODE_VECTOR,
+                                            CUBLAS_FILL_MODE_UPPER, d, CUDA_R_32F, nullptr, d, CUDA_R_32F, nullptr,
+                                            CUDA_R_32F, &g.dev_ws, &g.host_ws, cnt) != CUSOLVER_STATUS_SUCCESS)
+        KFB_FAIL(KFB_ERR_CUSOLVER, "XsyevBatched bufferSize failed for d=%d batch=%lld", d, (long long)cnt);
+      size_t off = 0;
+      g.off_A = off;    off = align256(off + (size_t)cnt * d * d * sizeof(float));
+      g.off_W = off;    off = align256(off + (size_t)cnt * d * sizeof(float));
+      g.off_info = off; off = align256(off + (size_t)cnt * sizeof(int));
+      g.off_ws = off;   off = align256(off + g.dev_ws);
+      g.bytes = off;
+      plan->groups.push_back(g);
+    } else {
+      singles.insert(singles.end(), order.begin() + i, order.begin() + j);
+    }
+    i = j;
+  }
+  // longest-processing-time placement of the single solves on the lanes (descending d already)
+  static const int lane_cap = []() {
+    const char* e = getenv("KFB_SYEVD_LANES");     // tuning knob; default = all lanes
+    int v = e ? atoi(e) : kMaxLanes;
+    return std::min(kMaxLanes, std::max(1, v));
+  }();
+  const int n_lanes = std::min<int>(lane_cap, std::max<size_t>(1, singles.size()));
+  plan->lanes.assign(n_lanes, {});
+  std::vector<double> load(n_lanes, 0.0);
+  for (int i : singles) {
+    int best = 0;
+    for (int l = 1; l < n_lanes; ++l)
+      if (load[l] < load[best]) best = l;
+    load[best] += (double)jobs[i].d;          // syevd time is ~linear in d on this GPU (launch-bound panels)
+    plan->lanes[best].push_back(i);
+  }
+  plan->lane_off.assign(n_lanes + 1, 0);
+  for (int l = 0; l < n_lanes; ++l) {
+    size_t mx = 0;
+    for (int i : plan->lanes[l]) mx = std::max(mx, lwork_bytes((cusolverDnHandle_t)ctx->cusolver, jobs[i].d));
+    plan->lane_off[l + 1] = plan->lane_off[l] + mx;
+  }
+  plan->group_off = plan->lane_off[n_lanes];
+  size_t gmax = 0;
+  for (auto& g : plan->groups) gmax = std::max(gmax, g.bytes);   // groups run one after another
+  plan->total = plan->group_off + gmax;
+  return KFB_OK;
+}
+
+// W (ascending, may be slightly negative) -> w = max(W, 0)
+__global__ void clip_copy_kernel(const float* __restrict__ src, float* __restrict__ dst, int d) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < d) dst[i] = fmaxf(src[i], 0.f);
+}
+
+int run_group(LanePool* pool, const Group& g, const kfb_syevd_job* jobs, char* region) {
+  cudaStream_t st = pool->grouped.stream;
+  cusolverDnHandle_t h = pool->grouped.handle;
+  if (cusolverDnSetStream(h, st) != CUSOLVER_STATUS_SUCCESS) KFB_FAIL(KFB_ERR_CUSOLVER, "cusolverDnSetStream failed");
+  const int d = g.d;
+  const int64_t cnt = (int64_t)g.idx.size();
+  float* A = (float*)(region + g.off_A);
+  float* W = (float*)(region + g.off_W);
+  int* info = (int*)(region + g.off_info);
+  for (int64_t b = 0; b < cnt; ++b) {
+    const kfb_syevd_job& j = jobs[g.idx[b]];
+    KFB_CUDA(cudaMemcpy2DAsync(A + b * d * d, (size_t)d * sizeof(float), j.factor, j.ld_factor * sizeof(float),
+                               (size_t)d * sizeof(float), d, cudaMemcpyDeviceToDevice, st));
+  }
+  std::vector<char> host(std::max<size_t>(g.host_ws, 1));
+  cusolverStatus_t rc = cusolverDnXsyevBatched(h, pool->params, CUSOLVER_EIG_MODE_VECTOR, CUBLAS_FILL_MODE_UPPER, d,
+                                               CUDA_R_32F, A, d, CUDA_R_32F, W, CUDA_R_32F, region + g.off_ws,
+                                               g.dev_ws, host.data(), g.host_ws, info, cnt);
+  if (rc != CUSOLVER_STATUS_SUCCESS) KFB_FAIL(KFB_ERR_CUSOLVER, "cusolverDnXsyevBatched failed (%d) for d=%d", (int)rc, d);
+  for (int64_t b = 0; b < cnt; ++b) {
+    const kfb_syevd_job& j = jobs[g.idx[b]];
+    // column-major eigenvectors = rows of the row-major view: that is E; Q is its transpose
+    KFB_CUDA(cudaMemcpy2DAsync(j.E, j.ld_e * sizeof(float), A + b * d * d, (size_t)d * sizeof(float),
+                               (size_t)d * sizeof(float), d, cudaMemcpyDeviceToDevice, st));
+    clip_copy_kernel<<<kfb::ceil_div(d, 256), 256, 0, st>>>(W + b * d, j.w, d);
+    KFB_CHECK_LAUNCH();
+    int r = kfb::launch_transpose(A + b * d * d, d, d, d, j.Q, j.ld_q, st);
+    if (r) return r;
+    KFB_CUDA(cudaMemcpyAsync(j.dev_info, info + b, sizeof(int), cudaMemcpyDeviceToDevice, st));
+  }
+  return KFB_OK;
 }
 }  // namespace
 
 size_t kfb_syevd_batch_workspace_bytes(const kfb_syevd_job* jobs, int32_t n_jobs) {
   kfb::Context* ctx = kfb::current_context();
   if (!ctx || !jobs || n_jobs <= 0) return 0;
-  std::vector<std::vector<int>> lanes;
-  place_jobs(jobs, n_jobs, &lanes);
-  size_t total = 0;
-  for (auto& l : lanes) {
-    size_t mx = 0;
-    for (int i : l) mx = std::max(mx, lwork_bytes((cusolverDnHandle_t)ctx->cusolver, jobs[i].d));
-    total += mx;
-  }
-  return total;
+  LanePool* pool;
+  if (get_pool(ctx, &pool)) return 0;
+  BatchPlan plan;
+  if (make_plan(ctx, pool, jobs, n_jobs, &plan)) return 0;
+  return plan.total;
 }
 
 int kfb_syevd_batch(const kfb_syevd_job* jobs, int32_t n_jobs, void* workspace, size_t workspace_bytes,
@@ -192,18 +305,12 @@ int kfb_syevd_batch(const kfb_syevd_job* jobs, int32_t n_jobs, void* workspace, 
   cudaStream_t stream = (cudaStream_t)stream_;
   LanePool* pool;
   if ((rc = get_pool(ctx, &pool))) return rc;
-  std::vector<std::vector<int>> lanes;
-  place_jobs(jobs, n_jobs, &lanes);
-  const int n_lanes = (int)lanes.size();
-  std::vector<size_t> off(n_lanes + 1, 0);
-  for (int l = 0; l < n_lanes; ++l) {
-    size_t mx = 0;
-    for (int i : lanes[l]) mx = std::max(mx, lwork_bytes((cusolverDnHandle_t)ctx->cusolver, jobs[i].d));
-    off[l + 1] = off[l] + mx;
-  }
-  if (!workspace || workspace_bytes < off[n_lanes])
-    KFB_FAIL(KFB_ERR_WORKSPACE, "syevd batch workspace: need %zu bytes, got %zu", off[n_lanes], workspace_bytes);
+  BatchPlan plan;
+  if ((rc = make_plan(ctx, pool, jobs, n_jobs, &plan))) return rc;
+  if (!workspace || workspace_bytes < plan.total)
+    KFB_FAIL(KFB_ERR_WORKSPACE, "syevd batch workspace: need %zu bytes, got %zu", plan.total, workspace_bytes);
   KFB_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+  const int n_lanes = (int)plan.lanes.size();
   // fork: every lane starts after what is already queued on the caller's stream
   KFB_CUDA(cudaEventRecord(pool->start, stream));
   std::vector<int> status(n_lanes, KFB_OK);
@@ -211,25 +318,37 @@ int kfb_syevd_batch(const kfb_syevd_job* jobs, int32_t n_jobs, void* workspace, 
   std::vector<std::thread> threads;
   const int device = ctx->device;
   for (int l = 0; l < n_lanes; ++l) {
+    if (plan.lanes[l].empty()) continue;
     threads.emplace_back([&, l]() {
-      // cuSOLVER's syevd synchronises with the host internally, so each lane needs its own thread
-      // for the lanes to overlap at all
+      // syevd's host-side panel loop is what takes the time: one thread per lane lets them overlap
       cudaSetDevice(device);
       kfb_init(device);
       Lane& lane = pool->lanes[l];
       if (cudaStreamWaitEvent(lane.stream, pool->start, 0) != cudaSuccess) { status[l] = KFB_ERR_CUDA; return; }
-      for (int i : lanes[l]) {
+      for (int i : plan.lanes[l]) {
         const kfb_syevd_job& j = jobs[i];
         int r = syevd_one(lane.handle, j.factor, j.ld_factor, j.d, j.E, j.ld_e, j.Q, j.ld_q, j.w,
-                          (char*)workspace + off[l], off[l + 1] - off[l], j.dev_info, lane.stream);
+                          (char*)workspace + plan.lane_off[l], plan.lane_off[l + 1] - plan.lane_off[l], j.dev_info,
+                          lane.stream);
         if (r) { status[l] = r; errors[l] = kfb::get_error(); break; }
       }
       if (cudaEventRecord(lane.done, lane.stream) != cudaSuccess) status[l] = KFB_ERR_CUDA;
     });
   }
+  // meanwhile, on this thread: the same-size groups through the batched solver
+  int grc = KFB_OK;
+  if (!plan.groups.empty()) {
+    grc = cudaStreamWaitEvent(pool->grouped.stream, pool->start, 0) == cudaSuccess ? KFB_OK : KFB_ERR_CUDA;
+    for (size_t gi = 0; gi < plan.groups.size() && grc == KFB_OK; ++gi)
+      grc = run_group(pool, plan.groups[gi], jobs, (char*)workspace + plan.group_off);
+    if (grc == KFB_OK && cudaEventRecord(pool->grouped.done, pool->grouped.stream) != cudaSuccess) grc = KFB_ERR_CUDA;
+  }
   for (auto& t : threads) t.join();
-  // join: the caller's stream continues after every lane
-  for (int l = 0; l < n_lanes; ++l) KFB_CUDA(cudaStreamWaitEvent(stream, pool->lanes[l].done, 0));
+  // join: the caller's stream continues after every lane and the grouped stream
+  for (int l = 0; l < n_lanes; ++l)
+    if (!plan.lanes[l].empty()) KFB_CUDA(cudaStreamWaitEvent(stream, pool->lanes[l].done, 0));
+  if (!plan.groups.empty() && grc == KFB_OK) KFB_CUDA(cudaStreamWaitEvent(stream, pool->grouped.done, 0));
+  if (grc) return grc;
   for (int l = 0; l < n_lanes; ++l)
     if (status[l]) KFB_FAIL(status[l], "syevd batch lane %d failed: %s", l, errors[l].c_str());
   return KFB_OK;

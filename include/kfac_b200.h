@@ -146,11 +146,13 @@ KFB_API size_t kfb_syevd_workspace_bytes(int32_t d);
 KFB_API int kfb_syevd(const float* factor, int64_t ld_factor, int32_t d,
               float* E, int64_t ld_e, float* Q, int64_t ld_q, float* w,
               void* workspace, size_t workspace_bytes, int32_t* dev_info, void* stream);
-/* Many eigendecompositions at once: the jobs are spread (longest first, by d^3) over a small pool
- * of internal worker lanes - one host thread, CUDA stream and cuSOLVER handle each - so that the
- * latency-bound small solves overlap each other and the few large ones.  All lanes start after the
- * work already queued on `stream` and `stream` waits for all of them, so to the caller it behaves
- * like one asynchronous call on `stream`.  Results are identical to kfb_syevd job by job. */
+/* Many eigendecompositions at once, still all cuSOLVER: factors of the same size (small and medium
+ * ones, where it measures faster) are solved together by cusolverDnXsyevBatched; the rest are
+ * spread, longest first, over a small pool of internal worker lanes - one host thread, CUDA stream
+ * and cuSOLVER handle each - so that their host-driven panel loops overlap.  Everything starts after
+ * the work already queued on `stream` and `stream` waits for all of it, so to the caller it behaves
+ * like one asynchronous call on `stream`.  Results match kfb_syevd job by job (eigenvectors up to
+ * sign). */
 typedef struct kfb_syevd_job {
   const float* factor; int64_t ld_factor;
   float* E; int64_t ld_e;
