@@ -218,8 +218,8 @@ int make_plan(kfb::Context* ctx, LanePool* pool, const kfb_syevd_job* jobs, int 
   }
   // longest-processing-time placement of the single solves on the lanes (descending d already)
   static const int lane_cap = []() {
-    const char* e = getenv("KFB_SYEVD_LANES");     // tuning knob; default = all lanes
-    int v = e ? atoi(e) : kMaxLanes;
+    const char* e = getenv("KFB_SYEVD_LANES");     // tuning knob
+    int v = e ? atoi(e) : 2;              // measured: no gain beyond 2 (the launch path serialises)
     return std::min(kMaxLanes, std::max(1, v));
   }();
   const int n_lanes = std::min<int>(lane_cap, std::max<size_t>(1, singles.size()));
