@@ -50,6 +50,14 @@ struct TcBatch {
   TcProb probs[kTcBatch];
 };
 
+// Tiles are sorted longest first; handing them out boustrophedon (CTA 0..G-1, then G-1..0, ...)
+// instead of round-robin evens out the per-CTA totals without a dynamic scheduler.
+__device__ __forceinline__ int snake_tile(int round, int total) {
+  const int g = gridDim.x, c = blockIdx.x;
+  const int t = round * g + ((round & 1) ? g - 1 - c : c);
+  return t < total ? t : -1;      // only the last round can be partial, so -1 also ends the walk
+}
+
 __device__ __forceinline__ int find_prob(const TcBatch& b, int tile) {
   int lo = 0, hi = b.n;
   while (hi - lo > 1) {
@@ -86,7 +94,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
     // ===================== TMA producer =====================
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < batch.total_tiles; tile += gridDim.x) {
+      for (int round = 0, tile; (tile = snake_tile(round, batch.total_tiles)) >= 0; ++round) {
         const int p = find_prob(batch, tile);
         const TcProb& pr = batch.probs[p];
         const int local = tile - batch.start[p];
@@ -109,7 +117,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < batch.total_tiles; tile += gridDim.x) {
+      for (int round = 0, tile; (tile = snake_tile(round, batch.total_tiles)) >= 0; ++round) {
         const int p = find_prob(batch, tile);
         const int kblocks = (batch.probs[p].K + BK - 1) / BK;
         const uint32_t idesc = umma::make_idesc_tf32(BM, batch.probs[p].bn);
@@ -140,7 +148,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
     const int q = warp & 3;                                // TMEM lane quarter this warp may read
     int acc = 0; uint32_t acc_phase = 0;
     float dot = 0.f;
-    for (int tile = blockIdx.x; tile < batch.total_tiles; tile += gridDim.x) {
+    for (int round = 0, tile; (tile = snake_tile(round, batch.total_tiles)) >= 0; ++round) {
       const int p = find_prob(batch, tile);
       const TcProb& pr = batch.probs[p];
       const int local = tile - batch.start[p];

@@ -66,6 +66,14 @@ __device__ __forceinline__ bool row_valid(uint32_t info, uint32_t mlo, uint32_t 
   return (__funnelshift_r(mlo, 0u, info) & 1u) != 0;
 }
 
+// Items are sorted longest first; hand them out boustrophedon (CTA 0..G-1, then G-1..0, ...) so the
+// per-CTA totals even out without a dynamic scheduler.
+__device__ __forceinline__ int snake_item(int round, int total) {
+  const int g = gridDim.x, c = blockIdx.x;
+  const int t = round * g + ((round & 1) ? g - 1 - c : c);
+  return t < total ? t : -1;
+}
+
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
@@ -103,7 +111,7 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
     const uint32_t lane_off = (uint32_t)((((lane >> 2) ^ (pw & 7)) << 4) | ((lane & 3) << 2));
     const uint32_t vec_kq = lane & 7, vec_rsub = lane >> 3;
     int stage = 0; uint32_t phase = 0;
-    for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+    for (int round = 0, it; (it = snake_item(round, n_items)) >= 0; ++round) {
       const TcItem item = items[it];
       const DevSegment s = segs[item.seg];
       const int d = jobs[item.job].d;
@@ -247,7 +255,7 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
       uint32_t acc_phase = 0;
-      for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+      for (int round = 0, it; (it = snake_item(round, n_items)) >= 0; ++round) {
         const TcItem item = items[it];
         const bool diag = item.a0 == item.b0;
         umma::mbar_wait(tempty, acc_phase ^ 1);            // the epilogue has drained TMEM
@@ -282,7 +290,7 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
     // ===================== epilogue (warps 0..3) =====================
     const int q = warp;
     uint32_t acc_phase = 0;
-    for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+    for (int round = 0, it; (it = snake_item(round, n_items)) >= 0; ++round) {
       const TcItem item = items[it];
       const DevJob& job = jobs[item.job];
       const float weight = segs[item.seg].weight;
