@@ -12,6 +12,7 @@ the API used at kfac/layers/utils.py:63), and writes
     tests/golden/lstm_single.pt  single-process LSTM (LinearMultiLayer), 2 steps
     tests/golden/cnn_world2.pt   2-rank gloo, COMM_OPT / MEM_OPT / HYBRID_OPT
     tests/golden/allocator.json  worker assignments for ResNet-50/152, W = 2, 4, 8
+    tests/golden/resnet32_single.pt  BASELINE configs[0]: CIFAR ResNet-32, batch 128, 2 steps
 
 Nothing here is imported by the product or by the tests; the tests only read the
 files it wrote.
@@ -92,6 +93,37 @@ def gen_cnn_single():
     rec = run_single(model, models.cnn_batch, F.cross_entropy, 4, KFAC_ARGS)
     torch.save(rec, os.path.join(HERE, 'cnn_single.pt'))
     print('cnn_single: losses', [round(s['loss'], 4) for s in rec['steps']])
+
+
+def gen_resnet32():
+    """BASELINE configs[0]: ResNet-32, 32x32, batch 128, single process, COMM_OPT, CIFAR defaults
+    (factor_update_freq 1, inv_update_freq 10, damping 0.003).  Only what the parity test needs
+    is stored: the final gradients of each step and two factors, in fp16-safe fp32."""
+    torch.set_num_threads(8)
+    model = models.make_resnet32()
+    # the weights are reproducible from the seed (make_resnet32); only a checksum is stored
+    init_checksum = float(sum(p.double().abs().sum() for p in model.parameters()))
+    opt = torch.optim.SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=5e-4)
+    kw = dict(damping=0.003, factor_decay=0.95, factor_update_freq=1, inv_update_freq=10, kl_clip=0.001, lr=0.1)
+    pre = kfac.KFAC(model, **kw)
+    steps = []
+    for s in range(2):
+        x, y = models.cifar_batch(s)
+        opt.zero_grad()
+        loss = F.cross_entropy(model(x), y)
+        loss.backward()
+        pre.step()
+        steps.append({'loss': loss.item(),
+                      'grads_out': [l.module.weight.grad.detach().half() for l in pre.layers],   # fp16: 5e-4 relative
+                      'bias_out': pre.layers[-1].module.bias.grad.detach().clone(),
+                      'A_first': pre.layers[0].state['A'].clone(), 'G_first': pre.layers[0].state['G'].clone(),
+                      'A_last': pre.layers[-1].state['A'].clone(), 'G_last': pre.layers[-1].state['G'].clone(),
+                      'A_trace': [l.state['A'].diagonal().sum().item() for l in pre.layers],
+                      'G_trace': [l.state['G'].diagonal().sum().item() for l in pre.layers]})
+        opt.step()
+    torch.save({'init_checksum': init_checksum, 'kfac_kwargs': kw, 'steps': steps, 'n_layers': len(pre.layers)},
+               os.path.join(HERE, 'resnet32_single.pt'))
+    print('resnet32: layers', len(pre.layers), 'losses', [round(s['loss'], 4) for s in steps])
 
 
 def gen_lstm_single():
@@ -197,7 +229,9 @@ def gen_allocator():
 
 
 if __name__ == '__main__':
-    which = sys.argv[1:] or ['cnn', 'lstm', 'world2', 'alloc']
+    which = sys.argv[1:] or ['cnn', 'lstm', 'world2', 'alloc', 'resnet32']
+    if 'resnet32' in which:
+        gen_resnet32()
     if 'cnn' in which:
         gen_cnn_single()
     if 'lstm' in which:

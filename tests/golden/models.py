@@ -31,6 +31,61 @@ class SmallCNN(nn.Module):
         return self.fc(x)
 
 
+class _BasicBlock(nn.Module):
+    def __init__(self, cin, cout, stride):
+        super().__init__()
+        self.conv1 = nn.Conv2d(cin, cout, 3, stride=stride, padding=1, bias=False)
+        self.bn1 = nn.BatchNorm2d(cout)
+        self.conv2 = nn.Conv2d(cout, cout, 3, stride=1, padding=1, bias=False)
+        self.bn2 = nn.BatchNorm2d(cout)
+        self.pad = (cout - cin) // 2 if (stride != 1 or cin != cout) else None
+        self.stride = stride
+
+    def forward(self, x):
+        out = F.relu(self.bn1(self.conv1(x)))
+        out = self.bn2(self.conv2(out))
+        if self.pad is not None:      # option-A shortcut: subsample and zero-pad channels
+            x = F.pad(x[:, :, ::self.stride, ::self.stride], (0, 0, 0, 0, self.pad, self.pad))
+        return F.relu(out + x)
+
+
+class CifarResNet32(nn.Module):
+    """The standard 32-layer CIFAR ResNet (He et al. 2015, 3 stages of 5 basic blocks, 16/32/64
+    channels, option-A shortcuts, 0.46 M parameters): BASELINE.json configs[0].  32 K-FAC layers
+    (31 convs without bias + the biased classifier), factor dims from (27,16) to (576,64)+(65,10)."""
+
+    def __init__(self, num_classes=10):
+        super().__init__()
+        self.conv1 = nn.Conv2d(3, 16, 3, stride=1, padding=1, bias=False)
+        self.bn1 = nn.BatchNorm2d(16)
+        blocks, cin = [], 16
+        for cout, stride in ((16, 1), (32, 2), (64, 2)):
+            for i in range(5):
+                blocks.append(_BasicBlock(cin, cout, stride if i == 0 else 1))
+                cin = cout
+        self.blocks = nn.Sequential(*blocks)
+        self.linear = nn.Linear(64, num_classes)
+        for m in self.modules():
+            if isinstance(m, (nn.Conv2d, nn.Linear)):
+                nn.init.kaiming_normal_(m.weight)
+
+    def forward(self, x):
+        x = F.relu(self.bn1(self.conv1(x)))
+        x = self.blocks(x)
+        x = F.adaptive_avg_pool2d(x, 1).flatten(1)
+        return self.linear(x)
+
+
+def make_resnet32(seed=0):
+    torch.manual_seed(seed)
+    return CifarResNet32()
+
+
+def cifar_batch(step, n=128):
+    g = torch.Generator().manual_seed(3000 + step)
+    return torch.randn(n, 3, 32, 32, generator=g), torch.randint(0, 10, (n,), generator=g)
+
+
 CNN_INPUT = (6, 3, 24, 20)      # N, C, H, W
 CNN_CLASSES = 10
 
