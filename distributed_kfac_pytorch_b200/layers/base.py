@@ -152,6 +152,19 @@ class KFACLayer(object):
         self.state[key] = view
         return view
 
+    def _inject2d(self, key, buf, cols):
+        """Back ``state[key]`` (or the preconditioned gradient for key 'out') with a buffer
+        owned by somebody else: KFAC lays the buffers of all layers that share a broadcast
+        source out in one slab so that the whole exchange is a single collective."""
+        self._buf[key] = buf
+        view = buf[:, :cols]
+        if key == 'out':
+            self._out = None
+            self._set_out(view)
+        else:
+            self.state[key] = view
+        return view
+
     def _alloc_E(self, key, d, device):
         buf, view = alloc2d(d, d, device)
         self._buf['E' + key] = buf
@@ -377,18 +390,21 @@ class KFACLayer(object):
     def _dims(self):
         return self.state['A'].shape[0], self.state['G'].shape[0]
 
+    def _set_out(self, view):
+        w = self.module.weight
+        n_w = view.shape[1] - int(self.has_bias)
+        self._out = view
+        self.preconditioned_gradient = [view[:, :n_w].unflatten(1, tuple(w.shape[1:]))
+                                        if w.dim() > 2 else view[:, :n_w]]
+        if self.has_bias:
+            self.preconditioned_gradient.append(view[:, n_w])
+
     def _ensure_out(self):
         if self._out is None:
             da, dg = self._weight_dims()
-            w = self.module.weight
-            buf, view = alloc2d(dg, da, w.device, zero=True)
+            buf, view = alloc2d(dg, da, self.module.weight.device, zero=True)
             self._buf['out'] = buf
-            self._out = view
-            n_w = da - int(self.has_bias)
-            self.preconditioned_gradient = [view[:, :n_w].unflatten(1, tuple(w.shape[1:]))
-                                            if w.dim() > 2 else view[:, :n_w]]
-            if self.has_bias:
-                self.preconditioned_gradient.append(view[:, n_w])
+            self._set_out(view)
         return self._out
 
     def _weight_dims(self):

@@ -171,6 +171,8 @@ class KFAC(optim.Optimizer):
 
         self.layers = []
         self.hook_layers = {}  # key: nn.Module, value: KFACLayer
+        self._inv_slabs = None     # [(src, CommGroup, slab)]: fused inverse broadcast
+        self._grad_slabs = None    # [(src, CommGroup, slab)]: fused gradient broadcast
         self._tri_slab = None      # packed-triangle allreduce fusion buffer
         self._tri_views = None     # per layer {'A': view, 'G': view}
         self._vg_acc = None        # device scalar: sum(v * g) over layers
@@ -465,9 +467,13 @@ class KFAC(optim.Optimizer):
         """preconditioner.py:535-543."""
         if comm.backend.size() == 1:
             return
-        handles = []
-        for layer in self.layers:
-            handles.extend(layer.broadcast_inverses())
+        if self._inv_slabs is not None:
+            handles = [comm.backend.broadcast(slab, src=src, group=group)
+                       for src, group, slab in self._inv_slabs]
+        else:
+            handles = []
+            for layer in self.layers:
+                handles.extend(layer.broadcast_inverses())
         comm.backend.sync(handles)
         for layer in self.layers:
             layer.finish_inverse_broadcast()
@@ -491,9 +497,13 @@ class KFAC(optim.Optimizer):
         """preconditioner.py:545-553."""
         if comm.backend.size() == 1:
             return
-        handles = []
-        for layer in self.layers:
-            handles.extend(layer.broadcast_gradient())
+        if self._grad_slabs is not None:
+            handles = [comm.backend.broadcast(slab, src=src, group=group)
+                       for src, group, slab in self._grad_slabs]
+        else:
+            handles = []
+            for layer in self.layers:
+                handles.extend(layer.broadcast_gradient())
         comm.backend.sync(handles)
 
     def _write_back(self, vg, lr, kl_clip, fixed_scale):
@@ -564,6 +574,70 @@ class KFAC(optim.Optimizer):
                                          allocator.get_inv_group(g_locs[i]))
             src_ranks = allocator.get_inv_ranks(a_locs[i])
             layer.assign_gradient_workers(src_ranks, allocator.get_grad_groups(src_ranks))
+        self._build_comm_slabs()
+
+    def _build_comm_slabs(self):
+        """Fuse the per-layer broadcasts: every buffer that travels from the same source rank over
+        the same group is carved out of ONE slab, so `broadcast_inverses` is one collective per
+        inverse rank (instead of three per layer: preconditioner.py:535-543, base.py:129-171) and
+        `broadcast_gradients` one per source in this rank's gradient group (instead of one or two
+        per layer every step: base.py:173-196).  Zero copies: the layers' tensors ARE the slab."""
+        from .layers.base import _round4
+        self._inv_slabs, self._grad_slabs = None, None
+        if comm.backend.size() == 1 or len(self.layers) == 0:
+            return
+        rank = comm.backend.rank()
+        dev = self.layers[0].state['A'].device
+
+        def carve(plan):
+            slabs = []
+            for (src, gid), entries in plan.items():
+                total = sum(r * _round4(c) for _, _, r, c in entries)
+                slab = torch.zeros(total, device=dev, dtype=torch.float32)
+                off = 0
+                for layer, key, r, c in entries:
+                    n = r * _round4(c)
+                    if c == 0:       # 1-D vector stored as one row
+                        layer.state[key] = slab[off:off + _round4(r)][:r]
+                        n = _round4(r)
+                    else:
+                        layer._inject2d(key, slab[off:off + n].view(r, _round4(c)), c)
+                    off += n
+                slabs.append((src, entries[0][0]._slab_groups[gid], slab))
+            return slabs
+
+        fused_inv = (self.comm_method in (CommMethod.COMM_OPT, CommMethod.HYBRID_OPT)
+                     and not self.distribute_layer_factors
+                     and not any('QA' in l.state or 'QG' in l.state for l in self.layers))
+        if fused_inv:
+            plan = {}
+            for l in self.layers:
+                l._slab_groups = {id(l.broadcast_A_inv_group): l.broadcast_A_inv_group}
+                if not l.keep_inv_copy or l.broadcast_A_inv_group.size <= 1:
+                    continue
+                da, dg = l.state['A'].shape[0], l.state['G'].shape[0]
+                e = plan.setdefault((l.compute_A_inv_rank, id(l.broadcast_A_inv_group)), [])
+                e += [(l, 'QA', da, da), (l, 'QG', dg, dg)]
+                if self.precompute_outer_eigen:
+                    e.append((l, 'dGdA', dg, da))
+                else:
+                    e += [(l, 'dA', da, 0), (l, 'dG', dg, 0)]
+            self._inv_slabs = carve(plan)
+            for l in self.layers:
+                if l.keep_inv_copy and l.broadcast_A_inv_group.size > 1:
+                    for key in ('A', 'G'):
+                        l._alloc_E(key, l.state[key].shape[0], dev)
+        if self.comm_method in (CommMethod.MEM_OPT, CommMethod.HYBRID_OPT):
+            plan = {}
+            for l in self.layers:
+                src, group = l.broadcast_grad_groups[rank]
+                l._slab_groups = getattr(l, '_slab_groups', {})
+                l._slab_groups[id(group)] = group
+                if group.size <= 1:
+                    continue
+                da, dg = l._weight_dims()
+                plan.setdefault((src, id(group)), []).append((l, 'out', dg, da))
+            self._grad_slabs = carve(plan)
 
     # ------------------------------------------------------------------ hooks
     def _periodic_hook(grad_enabled=True):
