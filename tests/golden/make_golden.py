@@ -12,6 +12,7 @@ the API used at kfac/layers/utils.py:63), and writes
     tests/golden/lstm_single.pt  single-process LSTM (LinearMultiLayer), 2 steps
     tests/golden/cnn_world2.pt   2-rank gloo, COMM_OPT / MEM_OPT / HYBRID_OPT
     tests/golden/allocator.json  worker assignments for ResNet-50/152, W = 2, 4, 8
+    tests/golden/cnn_variants.pt  SmallCNN with compute_factor_in_hook / accumulate_data / no prediv
     tests/golden/resnet32_single.pt  BASELINE configs[0]: CIFAR ResNet-32, batch 128, 2 steps
 
 Nothing here is imported by the product or by the tests; the tests only read the
@@ -93,6 +94,39 @@ def gen_cnn_single():
     rec = run_single(model, models.cnn_batch, F.cross_entropy, 4, KFAC_ARGS)
     torch.save(rec, os.path.join(HERE, 'cnn_single.pt'))
     print('cnn_single: losses', [round(s['loss'], 4) for s in rec['steps']])
+
+
+def gen_cnn_variants():
+    """compute_factor_in_hook=True, and accumulate_data=True over two
+    micro-batches per optimisation step (gradient accumulation, examples/cnn_utils/engine.py:33-65)."""
+    torch.set_num_threads(1)
+    out = {}
+    for name, kw, micro in (('in_hook', dict(compute_factor_in_hook=True), 1),
+                            ('accumulate', dict(accumulate_data=True), 2),
+                            ('no_prediv', dict(precompute_outer_eigen=False), 1),
+                            ('grad_scaler', dict(grad_scaler=models.FixedScaler(1024.0)), 1)):
+        model = models.make_cnn()
+        opt = torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.9)
+        pre = kfac.KFAC(model, **dict(KFAC_ARGS, **kw))
+        scale = kw['grad_scaler'].get_scale() if 'grad_scaler' in kw else 1.0
+        steps = []
+        for s in range(3):
+            opt.zero_grad()
+            for m in range(micro):
+                x, y = models.cnn_batch(10 * s + m)
+                (F.cross_entropy(model(x), y) * scale / micro).backward()
+            if scale != 1.0:       # what GradScaler.unscale_(optimizer) does before preconditioner.step()
+                for p in model.parameters():
+                    p.grad.div_(scale)
+            pre.step()
+            steps.append({'grads_out': [_grads(l) for l in pre.layers],
+                          'A': [l.state['A'].clone() for l in pre.layers],
+                          'G': [l.state['G'].clone() for l in pre.layers]})
+            opt.step()
+        out[name] = {'kwargs': {k: v for k, v in kw.items() if k != 'grad_scaler'}, 'micro': micro,
+                     'scale': scale, 'steps': steps}
+    torch.save(out, os.path.join(HERE, 'cnn_variants.pt'))
+    print('cnn_variants: ok')
 
 
 def gen_resnet32():
@@ -229,9 +263,11 @@ def gen_allocator():
 
 
 if __name__ == '__main__':
-    which = sys.argv[1:] or ['cnn', 'lstm', 'world2', 'alloc', 'resnet32']
+    which = sys.argv[1:] or ['cnn', 'lstm', 'world2', 'alloc', 'resnet32', 'variants']
     if 'resnet32' in which:
         gen_resnet32()
+    if 'variants' in which:
+        gen_cnn_variants()
     if 'cnn' in which:
         gen_cnn_single()
     if 'lstm' in which:

@@ -110,6 +110,17 @@ class SmallLSTMModel(nn.Module):
 LSTM_SEQ, LSTM_BATCH, LSTM_NTOKEN = 5, 4, 30
 
 
+class FixedScaler(object):
+    """Stand-in for torch.cuda.amp.GradScaler with a constant loss scale (K-FAC only calls
+    get_scale(): kfac/layers/base.py:374-375)."""
+
+    def __init__(self, scale):
+        self.scale = scale
+
+    def get_scale(self):
+        return self.scale
+
+
 def make_cnn(seed=0):
     torch.manual_seed(seed)
     return SmallCNN()

@@ -197,3 +197,13 @@ def test_resnet32_cifar_config_matches_reference(mode):
                                        rtol=1e-2, atol=1e-4)
         torch.testing.assert_close(pre.layers[-1].module.bias.grad.cpu(), gold['bias_out'], rtol=1e-2, atol=1e-4)
         opt.step()
+
+
+@pytest.mark.parametrize('name', ['in_hook', 'accumulate', 'no_prediv', 'grad_scaler'])
+def test_variants_match_reference_on_gpu(mode, name):
+    """compute_factor_in_hook=True, accumulate_data=True over two micro-batches, and
+    precompute_outer_eigen=False, against reference-generated goldens."""
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    from test_host_logic import _run_variant
+    _run_variant(name, DEV)

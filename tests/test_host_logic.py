@@ -266,3 +266,37 @@ def test_world2_gloo_matches_reference(tmp_path, idx, method, fraction):
             for rank in range(2):
                 has = 'QA' in ranks[rank]['held'][i]
                 assert has == (rank == a['a_rank'])
+
+
+# ---- SURVEY §8f rank 2/3 switches: in-hook factors, accumulated micro-batches, no prediv -------
+
+def _run_variant(name, device='cpu'):
+    rec = load_golden('cnn_variants.pt')[name]
+    model = models.make_cnn().to(device)
+    opt = torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.9)
+    kw = dict(damping=0.003, factor_decay=0.95, factor_update_freq=1, inv_update_freq=2, kl_clip=0.001,
+              lr=0.1)
+    scale = rec.get('scale', 1.0)
+    extra = dict(rec['kwargs'])
+    if scale != 1.0:
+        extra['grad_scaler'] = models.FixedScaler(scale)
+    pre = kfac.KFAC(model, **dict(kw, **extra))
+    for s, gold in enumerate(rec['steps']):
+        opt.zero_grad()
+        for m in range(rec['micro']):
+            x, y = models.cnn_batch(10 * s + m)
+            (F.cross_entropy(model(x.to(device)), y.to(device)) * scale / rec['micro']).backward()
+        if scale != 1.0:
+            for p in model.parameters():
+                p.grad.div_(scale)
+        pre.step()
+        for i, layer in enumerate(pre.layers):
+            torch.testing.assert_close(layer.state['A'].cpu(), gold['A'][i], **FACTOR_TOL)
+            torch.testing.assert_close(layer.state['G'].cpu(), gold['G'][i], **FACTOR_TOL)
+            torch.testing.assert_close(layer.module.weight.grad.cpu(), gold['grads_out'][i][0], **GRAD_TOL)
+        opt.step()
+
+
+@pytest.mark.parametrize('name', ['in_hook', 'accumulate', 'no_prediv', 'grad_scaler'])
+def test_variants_match_reference(cpu_ops, name):
+    _run_variant(name)
