@@ -53,7 +53,7 @@ class CSyevdJob(C.Structure):
 
 class CPrecondJob(C.Structure):
     _fields_ = [('da', C.c_int32), ('dg', C.c_int32), ('has_bias', C.c_int32),
-                ('reserved', C.c_int32), ('weight_grad', C.c_void_p), ('bias_grad', C.c_void_p),
+                ('use_inverse', C.c_int32), ('weight_grad', C.c_void_p), ('bias_grad', C.c_void_p),
                 ('EA', C.c_void_p), ('QA', C.c_void_p), ('ld_a', C.c_int64),
                 ('EG', C.c_void_p), ('QG', C.c_void_p), ('ld_g', C.c_int64),
                 ('dGdA', C.c_void_p), ('ld_dgda', C.c_int64),
@@ -86,6 +86,9 @@ _SIGNATURES = {
                             C.c_int64, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]),
     'kfb_syevd_batch_workspace_bytes': (C.c_size_t, [C.POINTER(CSyevdJob), C.c_int32]),
     'kfb_syevd_batch': (C.c_int, [C.POINTER(CSyevdJob), C.c_int32, C.c_void_p, C.c_size_t, C.c_void_p]),
+    'kfb_cholesky_inverse_workspace_bytes': (C.c_size_t, [C.c_int32]),
+    'kfb_cholesky_inverse': (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_float, C.c_void_p, C.c_int64,
+                                       C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]),
     'kfb_transpose': (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
                                 C.c_int64, C.c_void_p]),
     'kfb_outer_recip': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_float,
@@ -150,12 +153,14 @@ class FactorJob(object):
 class PrecondJob(object):
     """Persistent per-layer description of the precondition GEMM chain; only
     ``weight_grad`` / ``bias_grad`` change from step to step."""
-    __slots__ = ('da', 'dg', 'has_bias', 'weight_grad', 'bias_grad', 'EA', 'QA', 'EG', 'QG',
+    __slots__ = ('da', 'dg', 'has_bias', 'use_inverse', 'weight_grad', 'bias_grad', 'EA', 'QA', 'EG', 'QG',
                  'dGdA', 'gmat', 'V', 'out', 'T', '_c')
 
     def __init__(self, **kw):
         self._c = None
         self.weight_grad = self.bias_grad = None
+        self.use_inverse = False       # True: EA holds A_inv, QG holds G_inv, out = G_inv gmat A_inv
+        self.QA = self.EG = self.dGdA = self.V = None
         for k, v in kw.items():
             setattr(self, k, v)
 
@@ -328,6 +333,16 @@ class CudaOps(object):
         ws = self.workspace(nbytes, jobs[0][0].device)
         self._call('kfb_syevd_batch', cjobs, len(jobs), ws.data_ptr(), ws.numel(), stream)
 
+    def cholesky_inverse(self, factor, damping, out, info):
+        """out = (factor + damping I)^-1 (full symmetric), cuSOLVER potrf + potri."""
+        stream = self._enter(factor)
+        _check_cuda(out, info)
+        _check_f32(factor, out)
+        d = factor.shape[0]
+        ws = self.workspace(self.lib.kfb_cholesky_inverse_workspace_bytes(d), factor.device)
+        self._call('kfb_cholesky_inverse', factor.data_ptr(), _pitch(factor), d, float(damping), out.data_ptr(),
+                   _pitch(out), ws.data_ptr(), ws.numel(), info.data_ptr(), stream)
+
     def transpose(self, src, dst):
         stream = self._enter(src)
         _check_cuda(dst)
@@ -350,13 +365,15 @@ class CudaOps(object):
             c = CPrecondJob()
             _check_cuda(j.EA, j.QA, j.EG, j.QG, j.dGdA, j.gmat, j.V, j.out, j.T)
             _check_f32(j.EA, j.QA, j.EG, j.QG, j.dGdA, j.gmat, j.V, j.out, j.T)
-            c.da, c.dg, c.has_bias = j.da, j.dg, int(j.has_bias)
-            c.EA, c.QA, c.ld_a = j.EA.data_ptr(), j.QA.data_ptr(), _pitch(j.EA)
-            c.EG, c.QG, c.ld_g = j.EG.data_ptr(), j.QG.data_ptr(), _pitch(j.EG)
-            assert _pitch(j.QA) == c.ld_a and _pitch(j.QG) == c.ld_g
-            c.dGdA, c.ld_dgda = j.dGdA.data_ptr(), _pitch(j.dGdA)
-            c.gmat, c.V, c.out, c.ld_v = j.gmat.data_ptr(), j.V.data_ptr(), j.out.data_ptr(), _pitch(j.out)
-            assert _pitch(j.gmat) == c.ld_v and _pitch(j.V) == c.ld_v
+            c.da, c.dg, c.has_bias, c.use_inverse = j.da, j.dg, int(j.has_bias), int(j.use_inverse)
+            c.EA, c.QA, c.ld_a = j.EA.data_ptr(), _ptr(j.QA), _pitch(j.EA)
+            c.EG, c.QG, c.ld_g = _ptr(j.EG), j.QG.data_ptr(), _pitch(j.QG)
+            if not j.use_inverse:
+                assert _pitch(j.QA) == c.ld_a and _pitch(j.EG) == c.ld_g
+                c.dGdA, c.ld_dgda = j.dGdA.data_ptr(), _pitch(j.dGdA)
+                assert _pitch(j.V) == _pitch(j.out)
+            c.gmat, c.V, c.out, c.ld_v = j.gmat.data_ptr(), _ptr(j.V), j.out.data_ptr(), _pitch(j.out)
+            assert _pitch(j.gmat) == c.ld_v
             c.T, c.ld_t = j.T.data_ptr(), _pitch(j.T)
             j._c = c
         wg, bg = j.weight_grad, j.bias_grad

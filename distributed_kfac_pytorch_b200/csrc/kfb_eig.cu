@@ -354,6 +354,61 @@ int kfb_syevd_batch(const kfb_syevd_job* jobs, int32_t n_jobs, void* workspace, 
   return KFB_OK;
 }
 
+// ---- explicit damped inverse ------------------------------------------------------------------------
+namespace {
+__global__ void add_diag_kernel(float* a, int64_t ld, int d, float v) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < d) a[(int64_t)i * ld + i] += v;
+}
+// potri leaves only one triangle valid: copy it over the other (row-major upper <- lower)
+__global__ void __launch_bounds__(256) mirror_kernel(float* a, int64_t ld, int d) {
+  const int i = blockIdx.y * 16 + threadIdx.y, j = blockIdx.x * 16 + threadIdx.x;
+  if (i < d && j < d && j > i) a[(int64_t)i * ld + j] = a[(int64_t)j * ld + i];
+}
+}  // namespace
+
+size_t kfb_cholesky_inverse_workspace_bytes(int32_t d) {
+  kfb::Context* ctx = kfb::current_context();
+  if (!ctx || d <= 0) return 0;
+  int l1 = 0, l2 = 0;
+  cusolverDnHandle_t h = (cusolverDnHandle_t)ctx->cusolver;
+  if (cusolverDnSpotrf_bufferSize(h, CUBLAS_FILL_MODE_UPPER, d, nullptr, (d + 3) / 4 * 4, &l1) != CUSOLVER_STATUS_SUCCESS) return 0;
+  if (cusolverDnSpotri_bufferSize(h, CUBLAS_FILL_MODE_UPPER, d, nullptr, (d + 3) / 4 * 4, &l2) != CUSOLVER_STATUS_SUCCESS) return 0;
+  return (size_t)std::max(l1, l2) * sizeof(float) + 256;
+}
+
+int kfb_cholesky_inverse(const float* factor, int64_t ld_factor, int32_t d, float damping, float* out,
+                         int64_t ld_out, void* workspace, size_t workspace_bytes, int32_t* dev_info, void* stream_) {
+  kfb::Context* ctx;
+  int rc = kfb::require_context(&ctx);
+  if (rc) return rc;
+  KFB_REQUIRE(factor && out && dev_info && d > 0 && ld_factor >= d && ld_out >= d, "bad cholesky_inverse arguments");
+  cudaStream_t stream = (cudaStream_t)stream_;
+  cusolverDnHandle_t h = (cusolverDnHandle_t)ctx->cusolver;
+  if (cusolverDnSetStream(h, stream) != CUSOLVER_STATUS_SUCCESS) KFB_FAIL(KFB_ERR_CUSOLVER, "cusolverDnSetStream failed");
+  int l1 = 0, l2 = 0;
+  if (cusolverDnSpotrf_bufferSize(h, CUBLAS_FILL_MODE_UPPER, d, out, (int)ld_out, &l1) != CUSOLVER_STATUS_SUCCESS ||
+      cusolverDnSpotri_bufferSize(h, CUBLAS_FILL_MODE_UPPER, d, out, (int)ld_out, &l2) != CUSOLVER_STATUS_SUCCESS)
+    KFB_FAIL(KFB_ERR_CUSOLVER, "potrf/potri bufferSize failed for d=%d", d);
+  const size_t need = (size_t)std::max(l1, l2) * sizeof(float);
+  if (!workspace || workspace_bytes < need)
+    KFB_FAIL(KFB_ERR_WORKSPACE, "cholesky_inverse workspace: need %zu bytes, got %zu", need, workspace_bytes);
+  KFB_CUDA(cudaMemcpy2DAsync(out, ld_out * sizeof(float), factor, ld_factor * sizeof(float), (size_t)d * sizeof(float), d,
+                             cudaMemcpyDeviceToDevice, stream));
+  add_diag_kernel<<<kfb::ceil_div(d, 256), 256, 0, stream>>>(out, ld_out, d, damping);
+  KFB_CHECK_LAUNCH();
+  // the symmetric matrix read column-major is itself; cuSOLVER's UPPER triangle (column-major) is
+  // the LOWER triangle of the row-major view, which mirror_kernel copies to the upper one
+  if (cusolverDnSpotrf(h, CUBLAS_FILL_MODE_UPPER, d, out, (int)ld_out, (float*)workspace, l1, dev_info) != CUSOLVER_STATUS_SUCCESS)
+    KFB_FAIL(KFB_ERR_CUSOLVER, "cusolverDnSpotrf failed for d=%d", d);
+  if (cusolverDnSpotri(h, CUBLAS_FILL_MODE_UPPER, d, out, (int)ld_out, (float*)workspace, l2, dev_info) != CUSOLVER_STATUS_SUCCESS)
+    KFB_FAIL(KFB_ERR_CUSOLVER, "cusolverDnSpotri failed for d=%d", d);
+  dim3 grid(kfb::ceil_div(d, 16), kfb::ceil_div(d, 16)), block(16, 16);
+  mirror_kernel<<<grid, block, 0, stream>>>(out, ld_out, d);
+  KFB_CHECK_LAUNCH();
+  return KFB_OK;
+}
+
 int kfb_transpose(const float* in, int64_t ld_in, int32_t rows, int32_t cols, float* out, int64_t ld_out,
                   void* stream) {
   kfb::Context* ctx;

@@ -214,14 +214,19 @@ int kfb_precondition(const kfb_precond_job* jobs, int32_t n_jobs, float* vg_acc,
   cudaStream_t stream = (cudaStream_t)stream_;
   std::vector<GradJob> pack;
   pack.reserve(n_jobs);
-  std::vector<GemmProb> s1(n_jobs), s2(n_jobs), s3(n_jobs), s4(n_jobs);
+  std::vector<GemmProb> s1(n_jobs), s2, s3, s4(n_jobs);
   for (int i = 0; i < n_jobs; ++i) {
     const kfb_precond_job& j = jobs[i];
     KFB_REQUIRE(j.da > 0 && j.dg > 0, "precond job %d: empty", i);
-    KFB_REQUIRE(j.weight_grad && j.EA && j.QA && j.EG && j.QG && j.dGdA && j.gmat && j.V && j.out && j.T,
-                "precond job %d: null pointer", i);
+    if (j.use_inverse) {
+      KFB_REQUIRE(j.weight_grad && j.EA && j.QG && j.gmat && j.out && j.T, "precond job %d: null pointer", i);
+    } else {
+      KFB_REQUIRE(j.weight_grad && j.EA && j.QA && j.EG && j.QG && j.dGdA && j.gmat && j.V && j.out && j.T,
+                  "precond job %d: null pointer", i);
+    }
     KFB_REQUIRE(!j.has_bias || j.bias_grad, "precond job %d: has_bias without bias_grad", i);
-    KFB_REQUIRE(j.ld_a >= j.da && j.ld_g >= j.dg && j.ld_dgda >= j.da && j.ld_v >= j.da && j.ld_t >= j.dg,
+    KFB_REQUIRE(j.ld_a >= j.da && j.ld_g >= j.dg && (j.use_inverse || j.ld_dgda >= j.da) && j.ld_v >= j.da &&
+                    j.ld_t >= j.dg,
                 "precond job %d: pitch too small", i);
     // Without a bias column the contiguous weight gradient already IS the [dg x da] matrix; if
     // its rows are 16-byte aligned the GEMMs read it in place and nothing is packed.
@@ -238,17 +243,21 @@ int kfb_precondition(const kfb_precond_job* jobs, int32_t n_jobs, float* vg_acc,
     }
     GemmProb z;
     memset(&z, 0, sizeof(z));
-    // T = EA gmat^T
+    // T = EA gmat^T          (explicit-inverse mode: EA is A_inv, so T = (gmat A_inv)^T)
     s1[i] = z; s1[i].A = j.EA; s1[i].lda = j.ld_a; s1[i].B = gm; s1[i].ldb = ld_gm;
     s1[i].D = j.T; s1[i].ldd = j.ld_t; s1[i].M = j.da; s1[i].N = j.dg; s1[i].K = j.da;
-    // V = (EG T^T) * dGdA
-    s2[i] = z; s2[i].A = j.EG; s2[i].lda = j.ld_g; s2[i].B = j.T; s2[i].ldb = j.ld_t;
-    s2[i].D = j.V; s2[i].ldd = j.ld_v; s2[i].M = j.dg; s2[i].N = j.da; s2[i].K = j.dg;
-    s2[i].Mul = j.dGdA; s2[i].ldmul = j.ld_dgda;
-    // T = QA V^T
-    s3[i] = z; s3[i].A = j.QA; s3[i].lda = j.ld_a; s3[i].B = j.V; s3[i].ldb = j.ld_v;
-    s3[i].D = j.T; s3[i].ldd = j.ld_t; s3[i].M = j.da; s3[i].N = j.dg; s3[i].K = j.da;
-    // out = QG T^T, dot with gmat
+    if (!j.use_inverse) {
+      // V = (EG T^T) * dGdA
+      GemmProb p2 = z; p2.A = j.EG; p2.lda = j.ld_g; p2.B = j.T; p2.ldb = j.ld_t;
+      p2.D = j.V; p2.ldd = j.ld_v; p2.M = j.dg; p2.N = j.da; p2.K = j.dg;
+      p2.Mul = j.dGdA; p2.ldmul = j.ld_dgda;
+      s2.push_back(p2);
+      // T = QA V^T
+      GemmProb p3 = z; p3.A = j.QA; p3.lda = j.ld_a; p3.B = j.V; p3.ldb = j.ld_v;
+      p3.D = j.T; p3.ldd = j.ld_t; p3.M = j.da; p3.N = j.dg; p3.K = j.da;
+      s3.push_back(p3);
+    }
+    // out = QG T^T, dot with gmat     (explicit-inverse mode: QG is G_inv)
     s4[i] = z; s4[i].A = j.QG; s4[i].lda = j.ld_g; s4[i].B = j.T; s4[i].ldb = j.ld_t;
     s4[i].D = j.out; s4[i].ldd = j.ld_v; s4[i].M = j.dg; s4[i].N = j.da; s4[i].K = j.dg;
     if (vg_acc) { s4[i].Dot = gm; s4[i].lddot = ld_gm; }
@@ -256,8 +265,8 @@ int kfb_precondition(const kfb_precond_job* jobs, int32_t n_jobs, float* vg_acc,
   rc = run_grad<kPack>(pack.data(), (int)pack.size(), nullptr, nullptr, 0.f, 0.f, 1.f, stream);
   if (rc) return rc;
   if ((rc = run_stage(ctx, s1, nullptr, stream))) return rc;
-  if ((rc = run_stage(ctx, s2, nullptr, stream))) return rc;
-  if ((rc = run_stage(ctx, s3, nullptr, stream))) return rc;
+  if (!s2.empty() && (rc = run_stage(ctx, s2, nullptr, stream))) return rc;
+  if (!s3.empty() && (rc = run_stage(ctx, s3, nullptr, stream))) return rc;
   return run_stage(ctx, s4, vg_acc, stream);
 }
 

@@ -56,8 +56,6 @@ class KFACLayer(object):
         self.eps = 1e-10
         if inv_dtype not in (None, torch.float32) or factor_dtype not in (None, torch.float32):
             raise NotImplementedError('the B200 kernels keep factors and inverses in float32')
-        if not use_eigen_decomp:
-            raise NotImplementedError('use_eigen_decomp=False (explicit inverses) is not built yet')
 
         # Should be overridden by implementing class
         self.has_bias = False
@@ -288,6 +286,12 @@ class KFACLayer(object):
     def _ensure_inv_buffers(self, key):
         d = self.state[key].shape[0]
         dev = self.state[key].device
+        if self._info is None:
+            self._info = torch.zeros(2, device=dev, dtype=torch.int32)
+        if not self.use_eigen_decomp:
+            if key + '_inv' not in self.state:
+                self._set2d(key + '_inv', d, d, dev)
+            return
         if 'Q' + key not in self.state:
             self._set2d('Q' + key, d, d, dev)
             self._alloc_E(key, d, dev)
@@ -309,8 +313,17 @@ class KFACLayer(object):
             self._ensure_inv_buffers(key)
         if ignore_rank or mine:
             info = self._info[0:1] if key == 'A' else self._info[1:2]
+            if not self.use_eigen_decomp:
+                return (self.state[key], self.state[key + '_inv'], info)
             return (self.state[key], self._E[key], self.state['Q' + key], self.state['d' + key], info)
         return None
+
+    def _run_inv_job(self, job, damping):
+        if self.use_eigen_decomp:
+            get_ops().syevd(*job)
+        else:     # explicit damped inverse (kfac/layers/utils.py:76-96)
+            factor, out, info = job
+            get_ops().cholesky_inverse(factor, damping, out, info)
 
     def _finish_G_inv(self, damping):
         """dGdA = 1/(dG dA^T + damping) on the rank that decomposed G (base.py:300-306)."""
@@ -325,21 +338,27 @@ class KFACLayer(object):
         """Eigendecompose A on its assigned rank (kfac/layers/base.py:198-256)."""
         job = self._inv_job('A', ignore_rank)
         if job is not None:
-            get_ops().syevd(*job)
+            self._run_inv_job(job, damping)
 
     def compute_G_inv(self, damping=0.001, ignore_rank=False):
         """Eigendecompose G on its assigned rank and, with prediv_eigenvalues, build
         dGdA = 1/(dG dA^T + damping) there (kfac/layers/base.py:258-308)."""
         job = self._inv_job('G', ignore_rank)
         if job is not None:
-            get_ops().syevd(*job)
-            self._finish_G_inv(damping)
+            self._run_inv_job(job, damping)
+            if self.use_eigen_decomp:
+                self._finish_G_inv(damping)
 
     def broadcast_inverses(self):
         """Ship QA, QG and dGdA (or dA, dG) over the inverse groups (base.py:129-171).
         Receivers must call ``finish_inverse_broadcast`` once the handles completed."""
         if not self.keep_inv_copy:
             return []
+        if not self.use_eigen_decomp:
+            return [comm.backend.broadcast(self._buf['A_inv'], src=self.compute_A_inv_rank,
+                                           group=self.broadcast_A_inv_group),
+                    comm.backend.broadcast(self._buf['G_inv'], src=self.compute_G_inv_rank,
+                                           group=self.broadcast_G_inv_group)]
         ops = [comm.backend.broadcast(self._buf['QA'], src=self.compute_A_inv_rank,
                                       group=self.broadcast_A_inv_group),
                comm.backend.broadcast(self._buf['QG'], src=self.compute_G_inv_rank,
@@ -356,7 +375,7 @@ class KFACLayer(object):
 
     def finish_inverse_broadcast(self):
         """Rebuild E = Q^T for the factors this rank received rather than computed."""
-        if not self.keep_inv_copy:
+        if not self.keep_inv_copy or not self.use_eigen_decomp:
             return
         rank = comm.backend.rank()
         if rank != self.compute_A_inv_rank:
@@ -425,16 +444,24 @@ class KFACLayer(object):
             dev = self.state['A'].device
             out = self._ensure_out()
             bufs = {}
-            for name, (r, c) in (('gmat', (dg, da)), ('V', (dg, da)), ('T', (da, dg))):
+            names = (('gmat', (dg, da)), ('V', (dg, da)), ('T', (da, dg))) if self.use_eigen_decomp \
+                else (('gmat', (dg, da)), ('T', (da, dg)))
+            for name, (r, c) in names:
                 self._buf[name], bufs[name] = alloc2d(r, c, dev, zero=True)
-            if 'dGdA' not in self.state:
-                self._set2d('dGdA', dg, da, dev)
-            self._job = PrecondJob(da=da, dg=dg, has_bias=self.has_bias,
-                                   EA=self._E['A'], QA=self.state['QA'],
-                                   EG=self._E['G'], QG=self.state['QG'],
-                                   dGdA=self.state['dGdA'], gmat=bufs['gmat'], V=bufs['V'],
-                                   out=out, T=bufs['T'])
-        if not self.prediv_eigenvalues:
+            if not self.use_eigen_decomp:
+                # out = G_inv gmat A_inv  (kfac/layers/base.py:472-475): two GEMM stages
+                self._job = PrecondJob(da=da, dg=dg, has_bias=self.has_bias, use_inverse=True,
+                                       EA=self.state['A_inv'], QG=self.state['G_inv'],
+                                       gmat=bufs['gmat'], out=out, T=bufs['T'])
+            else:
+                if 'dGdA' not in self.state:
+                    self._set2d('dGdA', dg, da, dev)
+                self._job = PrecondJob(da=da, dg=dg, has_bias=self.has_bias,
+                                       EA=self._E['A'], QA=self.state['QA'],
+                                       EG=self._E['G'], QG=self.state['QG'],
+                                       dGdA=self.state['dGdA'], gmat=bufs['gmat'], V=bufs['V'],
+                                       out=out, T=bufs['T'])
+        if self.use_eigen_decomp and not self.prediv_eigenvalues:
             # 1/(dG dA^T + damping) with the CURRENT damping (base.py:468-469)
             get_ops().outer_recip(self.state['dG'], self.state['dA'], damping, self.state['dGdA'])
         self._job.weight_grad = self._get_weight_grad()

@@ -445,6 +445,12 @@ class KFAC(optim.Optimizer):
     def compute_inverses(self, damping=0.001):
         """Eigendecompose the factors assigned to this rank (preconditioner.py:555-564).
         A before G: G's pass builds dGdA from both spectra."""
+        if not self.use_eigen_decomp:      # explicit damped inverses, one Cholesky per factor
+            for layer in self.layers:
+                layer.compute_A_inv(damping=damping)
+                layer.compute_G_inv(damping=damping)
+            self._check_info()
+            return
         jobs, g_done = [], []
         for layer in self.layers:
             a_job = layer._inv_job('A')
@@ -458,10 +464,13 @@ class KFAC(optim.Optimizer):
         get_ops().syevd_batch(jobs)
         for layer in g_done:
             layer._finish_G_inv(damping)
+        self._check_info()
+
+    def _check_info(self):
         if self.check_eig_info:
             infos = [l._info for l in self.layers if l._info is not None]
             if infos and bool(torch.stack(infos).ne(0).any()):
-                raise RuntimeError('cuSOLVER syevd did not converge for at least one factor')
+                raise RuntimeError('cuSOLVER reported a failed factorisation for at least one factor')
 
     def broadcast_inverses(self):
         """preconditioner.py:535-543."""
@@ -607,7 +616,7 @@ class KFAC(optim.Optimizer):
             return slabs
 
         fused_inv = (self.comm_method in (CommMethod.COMM_OPT, CommMethod.HYBRID_OPT)
-                     and not self.distribute_layer_factors
+                     and not self.distribute_layer_factors and self.use_eigen_decomp
                      and not any('QA' in l.state or 'QG' in l.state for l in self.layers))
         if fused_inv:
             plan = {}

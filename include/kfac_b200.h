@@ -165,6 +165,13 @@ typedef struct kfb_syevd_job {
 KFB_API size_t kfb_syevd_batch_workspace_bytes(const kfb_syevd_job* jobs, int32_t n_jobs);
 KFB_API int kfb_syevd_batch(const kfb_syevd_job* jobs, int32_t n_jobs, void* workspace, size_t workspace_bytes,
                             void* stream);
+/* Explicit damped inverse, out = (factor + damping I)^-1, by Cholesky factorisation (cuSOLVER potrf +
+ * potri) - replaces get_inverse (kfac/layers/utils.py:76-96) for use_eigen_decomp=False.  `out` is
+ * written as a full symmetric matrix; `factor` is not modified; `dev_info` as for kfb_syevd. */
+KFB_API size_t kfb_cholesky_inverse_workspace_bytes(int32_t d);
+KFB_API int kfb_cholesky_inverse(const float* factor, int64_t ld_factor, int32_t d, float damping,
+                                 float* out, int64_t ld_out, void* workspace, size_t workspace_bytes,
+                                 int32_t* dev_info, void* stream);
 /* out <- in^T  (receivers of a broadcast Q rebuild E) */
 KFB_API int kfb_transpose(const float* in, int64_t ld_in, int32_t rows, int32_t cols,
                   float* out, int64_t ld_out, void* stream);
@@ -186,7 +193,8 @@ KFB_API int kfb_outer_recip(const float* dG, const float* dA, int32_t dg, int32_
 typedef struct kfb_precond_job {
   int32_t da, dg;          /* da includes the bias column */
   int32_t has_bias;
-  int32_t reserved;
+  int32_t use_inverse;     /* 1: explicit-inverse mode, out = G_inv gmat A_inv (kfac/layers/base.py:472-475):
+                              EA must point to A_inv and QG to G_inv (both symmetric); QA, EG, dGdA, V unused */
   const float* weight_grad;   /* contiguous [dg][da - has_bias] */
   const float* bias_grad;     /* [dg] or NULL */
   const float* EA; const float* QA; int64_t ld_a;   /* da x da */

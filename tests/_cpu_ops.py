@@ -83,6 +83,10 @@ class OracleOps(object):
         for job in jobs:
             self.syevd(*job)
 
+    def cholesky_inverse(self, factor, damping, out, info):
+        out.copy_(O.damped_inverse(factor.clone(), damping))
+        info.zero_()
+
     def transpose(self, src, dst):
         dst.copy_(src.t())
 
@@ -94,8 +98,11 @@ class OracleOps(object):
         for j in jobs:
             g = O.grad_matrix(j.weight_grad, j.bias_grad)
             j.gmat.copy_(g)
-            v2 = (j.EG @ g @ j.EA.t()) * j.dGdA        # = QG^T g QA
-            j.out.copy_(j.QG @ v2 @ j.QA.t())
+            if j.use_inverse:
+                j.out.copy_(O.precondition_inv(g, j.EA, j.QG))
+            else:
+                v2 = (j.EG @ g @ j.EA.t()) * j.dGdA        # = QG^T g QA
+                j.out.copy_(j.QG @ v2 @ j.QA.t())
             if vg_acc is not None:
                 vg_acc += (j.out * g).sum()
 

@@ -104,6 +104,7 @@ def gen_cnn_variants():
     for name, kw, micro in (('in_hook', dict(compute_factor_in_hook=True), 1),
                             ('accumulate', dict(accumulate_data=True), 2),
                             ('no_prediv', dict(precompute_outer_eigen=False), 1),
+                            ('inverse', dict(use_eigen_decomp=False), 1),
                             ('grad_scaler', dict(grad_scaler=models.FixedScaler(1024.0)), 1)):
         model = models.make_cnn()
         opt = torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.9)

@@ -238,6 +238,24 @@ def test_syevd_batch_matches_single(ops):
         assert (recon - f.double()).abs().max().item() <= 2e-4 * max(f.abs().max().item(), 1e-6)
 
 
+@pytest.mark.parametrize('d', [1, 5, 64, 147, 400])
+def test_cholesky_inverse(ops, d):
+    x = torch.randn(2 * d + 3, d, generator=torch.Generator().manual_seed(d))
+    f = x.t() @ x / x.shape[0]
+    _, F_ = alloc2d(d, d, DEV)
+    F_.copy_(f)
+    buf, out = alloc2d(d, d, DEV)
+    buf.fill_(float('nan'))
+    info = torch.ones(1, dtype=torch.int32, device=DEV)
+    ops.cholesky_inverse(F_, 0.003, out, info)
+    torch.cuda.synchronize()
+    assert info.item() == 0
+    ref = O.damped_inverse(f, 0.003)
+    torch.testing.assert_close(out.cpu(), ref, rtol=2e-3, atol=2e-4 * ref.abs().max().item())
+    assert torch.equal(out, out.t())
+    torch.testing.assert_close(F_.cpu(), f, rtol=0, atol=0)
+
+
 def test_transpose_and_outer_recip(ops):
     a = torch.randn(70, 45)
     _, src = alloc2d(70, 45, DEV)

@@ -297,6 +297,6 @@ def _run_variant(name, device='cpu'):
         opt.step()
 
 
-@pytest.mark.parametrize('name', ['in_hook', 'accumulate', 'no_prediv', 'grad_scaler'])
+@pytest.mark.parametrize('name', ['in_hook', 'accumulate', 'no_prediv', 'grad_scaler', 'inverse'])
 def test_variants_match_reference(cpu_ops, name):
     _run_variant(name)
