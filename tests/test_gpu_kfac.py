@@ -228,3 +228,50 @@ def test_variants_match_reference_on_gpu(mode, name):
     torch.backends.cuda.matmul.allow_tf32 = False
     from test_host_logic import _run_variant
     _run_variant(name, DEV)
+
+
+def test_lstm_language_model_shape_matches_oracle(mode):
+    """BASELINE.json configs[3]: the language-model LSTM shape (2 layers x 650 hidden, sequence
+    35, batch 20, K-FAC on the LSTM cell's Linear layers with accumulate_data) — four
+    LinearMultiLayers with da = 651, dg = 2600, each fed 35 calls of 20 rows.  One full step on the
+    GPU against the oracle stepping on the same captures and gradients."""
+    from oracle import kfac_oracle as O
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(0)
+    ntoken, nhid, seq, batch = 1000, 650, 35, 20
+
+    class LM(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.encoder = torch.nn.Embedding(ntoken, nhid)
+            self.layers = torch.nn.ModuleList([kfac.modules.LSTM(nhid, nhid, batch_first=False) for _ in range(2)])
+            self.decoder = torch.nn.Linear(nhid, ntoken)
+
+        def forward(self, tokens):
+            x = self.encoder(tokens)
+            for layer in self.layers:
+                x, _ = layer(x)
+            return F.log_softmax(self.decoder(x).view(-1, ntoken), dim=1)
+
+    model = LM().to(DEV)
+    kw = dict(damping=0.003, factor_decay=0.95, factor_update_freq=1, inv_update_freq=1, kl_clip=0.001, lr=0.1)
+    pre = kfac.KFAC(model, batch_first=False, accumulate_data=True, skip_layers=['linear', 'embedding'], **kw)
+    assert len(pre.layers) == 4
+    g = torch.Generator().manual_seed(5)
+    x = torch.randint(0, ntoken, (seq, batch), generator=g).to(DEV)
+    y = torch.randint(0, ntoken, (seq * batch,), generator=g).to(DEV)
+    F.nll_loss(model(x), y).backward()
+    assert all(len(l.a_inputs) == seq and len(l.g_outputs) == seq for l in pre.layers)
+    caps = [[([a.cpu() for a in l.a_inputs], [t.cpu() for t in l.g_outputs]) for l in pre.layers]]
+    grads = [(l.module.weight.grad.cpu().clone(), l.module.bias.grad.cpu().clone()) for l in pre.layers]
+    pre.step()
+    torch.cuda.synchronize()
+    specs = [O.LayerSpec('linear_multi', l.module.weight.shape, True, batch_first=False) for l in pre.layers]
+    oracle = O.OracleKFAC(specs, **kw)
+    ref = oracle.step(caps, grads)
+    for i, l in enumerate(pre.layers):
+        assert l.state['A'].shape == (651, 651) and l.state['G'].shape == (2600, 2600)
+        assert_factor_close(l.state['A'], oracle.A[i])
+        assert_factor_close(l.state['G'], oracle.G[i])
+        torch.testing.assert_close(l.module.weight.grad.cpu(), ref[i][0], rtol=1e-2, atol=1e-4)
+        torch.testing.assert_close(l.module.bias.grad.cpu(), ref[i][1], rtol=1e-2, atol=1e-4)
