@@ -39,6 +39,9 @@ KFAC_KW = dict(damping=0.001, factor_decay=0.95, kl_clip=0.001, lr=0.0125,
                factor_update_freq=CADENCE, inv_update_freq=CADENCE,
                distribute_layer_factors=False)
 WORKLOAD = 'resnet50_224_b32_kfac_comm_opt_freq10'
+# DRAM bytes per launch from the committed ncu capture (profiles/r1_tc_kernels_ncu.txt), 1 GPU
+NCU_TRAFFIC = {'resnet50': {'precondition': int((627.075 + 67.804 + 327.166 + 61.839 + 626.493 + 69.178 + 327.435 + 62.111) * 1e6),
+                            'syrk': int(4.645928e9 + 548.241e6)}}
 
 
 def parse_args():
@@ -317,14 +320,17 @@ def run_ours(args):
         ach = work['precond_flops'] / (precond_ms * 1e-3) / 1e12
         out['roofline'] = {'kernel': 'precondition GEMM chain (4 grouped stages + pack)', 'bound': 'tensor',
                            'achieved': ach, 'peak': tf32_peak, 'unit': 'TFLOP/s', 'frac': ach / tf32_peak,
-                           'traffic': None,
+                           # dram__bytes_read+write summed over the four GEMM launches of one step, ncu
+                           # --set full, profiles/r1_tc_kernels_ncu.txt (algorithmic minimum 921.5 MB)
+                           'traffic': NCU_TRAFFIC.get(args.model, {}).get('precondition'),
                            'peak_source': '%s bf16 sustained / 2 (TF32 runs at half the bf16 rate)' % pk['source']}
     if factor_ms:
         ach = work['syrk_flops'] / (factor_ms * 1e-3) / 1e12
         gbs = work['factor_bytes'] / (factor_ms * 1e-3) / 1e9
         out['roofline_factor'] = {'kernel': 'factor SYRK + finalize', 'bound': 'tensor', 'achieved': ach,
                                   'peak': tf32_peak, 'unit': 'TFLOP/s', 'frac': ach / tf32_peak,
-                                  'hbm_gbs': gbs, 'hbm_frac': gbs / pk['hbm_gbs'], 'traffic': None}
+                                  'hbm_gbs': gbs, 'hbm_frac': gbs / pk['hbm_gbs'],
+                                  'traffic': NCU_TRAFFIC.get(args.model, {}).get('syrk')}
 
     if not args.no_e2e:
         out['e2e'] = run_e2e(args, pre, caps, grads, device, dist_on)
