@@ -19,6 +19,7 @@ _lib = None
 _ops = None
 
 KFB_SEG_ROWS, KFB_SEG_NCHW, KFB_SEG_IM2COL = 0, 1, 2
+KFB_DTYPES = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}
 
 
 class NativeError(RuntimeError):
@@ -31,7 +32,7 @@ class CSegment(C.Structure):
                 ('n', C.c_int64), ('c', C.c_int64), ('h', C.c_int64), ('w', C.c_int64),
                 ('kh', C.c_int32), ('kw', C.c_int32), ('sh', C.c_int32), ('sw', C.c_int32),
                 ('ph', C.c_int32), ('pw', C.c_int32), ('ld', C.c_int64),
-                ('weight', C.c_float), ('reserved', C.c_int32)]
+                ('weight', C.c_float), ('dtype', C.c_int32)]
 
 
 class CFactorJob(C.Structure):
@@ -242,7 +243,10 @@ class CudaOps(object):
             segs = (CSegment * len(j.segments))()
             for cs, s in zip(segs, j.segments):
                 _check_cuda(s.tensor)
-                _check_f32(s.tensor)
+                if s.tensor.dtype not in KFB_DTYPES:
+                    raise NativeError('captured tensors must be float32, float16 or bfloat16, got %s'
+                                      % s.tensor.dtype)
+                cs.dtype = KFB_DTYPES[s.tensor.dtype]
                 if not s.tensor.is_contiguous() and s.kind != KFB_SEG_ROWS:
                     raise NativeError('captured conv tensors must be contiguous NCHW')
                 cs.kind, cs.has_bias, cs.data = s.kind, int(s.has_bias), s.tensor.data_ptr()

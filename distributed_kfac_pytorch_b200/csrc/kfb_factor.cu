@@ -64,7 +64,7 @@ __device__ __forceinline__ void load_tile(const DevSegment& s, int d, int64_t k0
       int kk = (t >> 6) + j * (NT / TS);
       int64_t k = k0 + kk;
       float v = 0.f;
-      if (in && k < k_end) v = bias ? 1.f : __ldg(s.data + k * s.ld + i);
+      if (in && k < k_end) v = bias ? 1.f : load_elem(s.data, s.dtype, k * s.ld + i);
       dst[kk][ii] = v;
     }
   } else {
@@ -97,10 +97,10 @@ __device__ __forceinline__ void load_tile(const DevSegment& s, int d, int64_t k0
         if (e.valid == 2) {
           v = 1.f;
         } else if (s.kind == KFB_SEG_NCHW) {
-          v = __ldg(s.data + base + e.off);
+          v = load_elem(s.data, s.dtype, base + e.off);
         } else {
           int y = y0 + e.ky, x = x0 + e.kx;
-          if (y >= 0 && y < s.h && x >= 0 && x < s.w) v = __ldg(s.data + base + e.off);
+          if (y >= 0 && y < s.h && x >= 0 && x < s.w) v = load_elem(s.data, s.dtype, base + e.off);
         }
       }
       dst[kk][ii] = v;
@@ -355,7 +355,8 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
       KFB_REQUIRE(s.data && s.n > 0 && s.c > 0, "factor job %d segment %d: empty", ji, si);
       DevSegment ds;
       memset(&ds, 0, sizeof(ds));
-      ds.data = s.data; ds.kind = s.kind; ds.has_bias = s.has_bias; ds.c = (int)s.c;
+      KFB_REQUIRE(s.dtype >= KFB_F32 && s.dtype <= KFB_BF16, "unknown segment dtype %d", s.dtype);
+      ds.data = s.data; ds.dtype = s.dtype; ds.kind = s.kind; ds.has_bias = s.has_bias; ds.c = (int)s.c;
       ds.h = (int)s.h; ds.w = (int)s.w; ds.ld = s.ld; ds.weight = s.weight;
       ds.kh = ds.kw = ds.sh = ds.sw = 1;
       int feat;

@@ -2,12 +2,15 @@
 #pragma once
 #include <vector>
 
+#include <cuda_fp16.h>
+
 #include "kfb_common.cuh"
 
 namespace kfb {
 
 struct DevSegment {
-  const float* data;
+  const void* data;
+  int dtype;             // KFB_F32 / KFB_F16 / KFB_BF16
   int kind, has_bias;
   int c;                 // features without the bias column
   int h, w;              // NCHW: spatial extent; IM2COL: input extent
@@ -36,6 +39,15 @@ struct DevJob {
   int T32;               // 32-wide blocks per side for finalize
   int use_tc;            // 1: handled by the tcgen05 SYRK
 };
+
+// One captured element, widened to fp32 (16-bit captures come from AMP autocast).
+__device__ __forceinline__ float widen16(unsigned short u, int dtype) {
+  return dtype == KFB_F16 ? __half2float(__ushort_as_half(u)) : __uint_as_float((uint32_t)u << 16);
+}
+__device__ __forceinline__ float load_elem(const void* base, int dtype, int64_t idx) {
+  if (dtype == KFB_F32) return __ldg(reinterpret_cast<const float*>(base) + idx);
+  return widen16(__ldg(reinterpret_cast<const unsigned short*>(base) + idx), dtype);
+}
 
 struct TcItem {            // one unit of tensor-core SYRK work: a 2x2 block of 128-wide tiles
   int job, seg;

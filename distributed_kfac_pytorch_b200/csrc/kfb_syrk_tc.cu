@@ -129,7 +129,8 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
       const int S = s.oh * s.ow;
       const uint32_t uS = (uint32_t)S, uow = (uint32_t)s.ow;
       const uint32_t k_end32 = item.k_end;       // K < 2^31 (checked on the host)
-      const bool vec4 = s.kind == KFB_SEG_NCHW && (S & 3) == 0 && (((uintptr_t)s.data) & 15) == 0;
+      const int esh = s.dtype == KFB_F32 ? 2 : 1;          // log2(bytes per captured element)
+      const bool vec4 = s.kind == KFB_SEG_NCHW && (S & 3) == 0 && (((uintptr_t)s.data) & ((4u << esh) - 1)) == 0;
       const bool wide = s.kind == KFB_SEG_IM2COL && s.kh * s.kw > 30;
       // does this warp own the bias feature's row in one of the tiles?
       int bias_slot = -1, bias_row = 0;
@@ -158,15 +159,23 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
           const uint32_t k = k0 + 4 * vec_kq;
           const bool kin = k < k_end32;
           const uint32_t n = k / uS;
-          const float* src = s.data + ((int64_t)n * s.c * S + (k - n * uS));
+          const char* src = reinterpret_cast<const char*>(s.data) + (((int64_t)n * s.c * S + (k - n * uS)) << esh);
           float4 v[4][2];
 #pragma unroll
           for (int t = 0; t < 4; ++t)
 #pragma unroll
             for (int i = 0; i < 2; ++i) {
               v[t][i] = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (kin && (info[t][i] & 63u) == kBitAlways)
-                v[t][i] = __ldg(reinterpret_cast<const float4*>(src + (info[t][i] >> 6)));
+              if (kin && (info[t][i] & 63u) == kBitAlways) {
+                const char* p = src + ((size_t)(info[t][i] >> 6) << esh);
+                if (esh == 2) {
+                  v[t][i] = __ldg(reinterpret_cast<const float4*>(p));
+                } else {               // four 16-bit captures in one 8-byte load
+                  const uint2 h = __ldg(reinterpret_cast<const uint2*>(p));
+                  v[t][i] = make_float4(widen16((unsigned short)(h.x & 0xffff), s.dtype), widen16((unsigned short)(h.x >> 16), s.dtype),
+                                        widen16((unsigned short)(h.y & 0xffff), s.dtype), widen16((unsigned short)(h.y >> 16), s.dtype));
+                }
+              }
             }
 #pragma unroll
           for (int t = 0; t < 4; ++t)
@@ -196,15 +205,15 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
           const bool kin = k < k_end32;
           const uint32_t n = k / uS;
           const uint32_t r = k - n * uS;
-          const float* src;
+          const char* src;
           uint32_t mlo = 0, mhi = 0;
           if (s.kind == KFB_SEG_NCHW) {
-            src = s.data + ((int64_t)n * s.c * S + r);
+            src = reinterpret_cast<const char*>(s.data) + (((int64_t)n * s.c * S + r) << esh);
             if (kin) mhi = 1u << (kBitAlways - 32);
           } else {
             const int oy = (int)(r / uow), ox = (int)(r - (uint32_t)oy * uow);
             const int y0 = oy * s.sh - s.ph, x0 = ox * s.sw - s.pw;
-            src = s.data + ((int64_t)n * s.c * s.h * s.w + (int64_t)y0 * s.w + x0);
+            src = reinterpret_cast<const char*>(s.data) + (((int64_t)n * s.c * s.h * s.w + (int64_t)y0 * s.w + x0) << esh);
             if (kin) {
               const int kx_lo = max(0, -x0), kx_hi = min(s.kw, s.w - x0);
               const int ky_lo = max(0, -y0), ky_hi = min(s.kh, s.h - y0);
@@ -230,7 +239,11 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
                 const uint32_t inf = info[2 * tp + u][j];
                 const bool ok = wide ? row_valid<true>(inf, mlo, mhi) : row_valid<false>(inf, mnarrow, 0u);
                 v[u][j] = 0.f;
-                if (ok) v[u][j] = __ldg(src + (inf >> 6));
+                if (ok) {
+                  const char* p = src + ((int64_t)(inf >> 6) << esh);
+                  v[u][j] = esh == 2 ? __ldg(reinterpret_cast<const float*>(p))
+                                     : widen16(__ldg(reinterpret_cast<const unsigned short*>(p)), s.dtype);
+                }
               }
 #pragma unroll
             for (int u = 0; u < 2; ++u)

@@ -197,7 +197,9 @@ class KFACLayer(object):
 
     @staticmethod
     def _as_f32(t):
-        if t.dtype != torch.float32:
+        """Captures are handed to the SYRK as they are when it can read them (fp32, and the fp16 /
+        bf16 tensors autocast produces: they are widened while being gathered, never copied)."""
+        if t.dtype not in (torch.float32, torch.float16, torch.bfloat16):
             t = t.float()
         return t
 
@@ -228,14 +230,18 @@ class KFACLayer(object):
 
     def _G_job(self, alpha, tri_out=None):
         outputs = self.g_outputs
+        inv_scale_sq = None
         if self.grad_scaler is not None:
-            # AMP: unscale, drop captures with inf/nan (kfac/layers/base.py:397-407)
-            kept = []
+            # AMP: the captures carry the loss scale.  Drop captures with inf/nan (kfac/layers/
+            # base.py:397-407) and fold the unscale into the segment weight - G is quadratic in g,
+            # so (g/s)^T (g/s) = g^T g / s^2 - instead of dividing the tensors.
+            kept, inv_scale_sq = [], []
             for g, scale in outputs:
-                g = self._as_f32(g) / scale
+                g = self._as_f32(g)
                 if not bool(torch.isfinite(g).all()):
                     continue
                 kept.append(g)
+                inv_scale_sq.append(1.0 / (float(scale) * float(scale)))
             if len(kept) != len(outputs):
                 warnings.warn('Some gradients were discarded when computing '
                               'G because they were unable to be unscaled. '
@@ -249,6 +255,9 @@ class KFACLayer(object):
             return None
         self.g_outputs = []                      # clear accumulated outputs (base.py:414)
         d, segments = self._g_segments(outputs)
+        if inv_scale_sq is not None:
+            for seg, f in zip(segments, inv_scale_sq):
+                seg.weight *= f
         return self._factor_job('G', d, segments, alpha, tri_out)
 
     def update_A_factor(self, alpha=0.95):

@@ -77,15 +77,18 @@ enum {
 typedef struct kfb_segment {
   int32_t kind;
   int32_t has_bias;      /* 1: X has one extra trailing feature that is constant 1 (ROWS, IM2COL) */
-  const float* data;
+  const void* data;
   int64_t n;             /* ROWS: row count; NCHW / IM2COL: batch size */
   int64_t c;             /* feature / channel count (without the bias feature) */
   int64_t h, w;          /* NCHW: spatial extent; IM2COL: INPUT height and width */
   int32_t kh, kw, sh, sw, ph, pw;   /* IM2COL kernel, stride, padding */
   int64_t ld;            /* ROWS: row pitch in elements */
   float weight;          /* e.g. 1/(N*S^3) for conv, 1/M for linear */
-  int32_t reserved;
+  int32_t dtype;         /* element type of `data`: KFB_F32 (0), KFB_F16 (1) or KFB_BF16 (2).  16-bit captures
+                            (AMP autocast activations / output gradients) are widened to fp32 as they are
+                            gathered; accumulation and the factor stay fp32 */
 } kfb_segment;
+enum { KFB_F32 = 0, KFB_F16 = 1, KFB_BF16 = 2 };
 
 typedef struct kfb_factor_job {
   int32_t d;                     /* factor dimension, = c*kh*kw + has_bias */

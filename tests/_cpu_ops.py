@@ -13,7 +13,7 @@ from distributed_kfac_pytorch_b200 import _native as N
 
 def segment_matrix(s):
     """Materialise X_s of a Segment (what the CUDA kernels read implicitly)."""
-    t = s.tensor
+    t = s.tensor.float()
     if s.kind == N.KFB_SEG_ROWS:
         x = t.reshape(-1, s.c)
     elif s.kind == N.KFB_SEG_NCHW:

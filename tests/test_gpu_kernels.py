@@ -121,6 +121,28 @@ def test_linear_factor_rows(ops, rows, feat, bias):
     assert_factor_close(state, O.factor_ema(O.linear_A([a], bias), None, 0.95))
 
 
+@pytest.mark.parametrize('dtype', [torch.float16, torch.bfloat16], ids=['fp16', 'bf16'])
+def test_half_precision_captures(ops, dtype):
+    """AMP captures (fp16 / bf16) are read natively: same factor as for the widened fp32 copy."""
+    g = torch.Generator().manual_seed(21)
+    x = torch.randn(4, 12, 14, 14, generator=g).to(dtype)          # im2col, 14x14 map
+    d, segs = conv_segments(x, (3, 3), (1, 1), (1, 1), True)
+    state, _, _ = run_both(ops, d, segs)
+    assert_factor_close(state, O.factor_ema(O.conv2d_A([x.float()], (3, 3), (1, 1), (1, 1), True), None, 0.95))
+    go = torch.randn(3, 130, 8, 8, generator=g).to(dtype)           # NCHW, 8-byte vector path
+    seg = N.Segment(N.KFB_SEG_NCHW, go.to(DEV), 3, 130, 1.0 / (64.0 * 64 * 3 * 64), h=8, w=8)
+    state, _, _ = run_both(ops, 130, [seg])
+    assert_factor_close(state, O.factor_ema(O.conv2d_G([go.float()]), None, 0.95))
+    go7 = torch.randn(3, 40, 7, 7, generator=g).to(dtype)           # NCHW, scalar path (49 not /4)
+    seg = N.Segment(N.KFB_SEG_NCHW, go7.to(DEV), 3, 40, 1.0 / (49.0 * 49 * 3 * 49), h=7, w=7)
+    state, _, _ = run_both(ops, 40, [seg])
+    assert_factor_close(state, O.factor_ema(O.conv2d_G([go7.float()]), None, 0.95))
+    a = torch.randn(48, 65, generator=g).to(dtype)                  # Linear rows (SIMT path)
+    seg = N.Segment(N.KFB_SEG_ROWS, a.to(DEV), 48, 65, 1.0 / 48, has_bias=True, ld=65)
+    state, _, _ = run_both(ops, 66, [seg])
+    assert_factor_close(state, O.factor_ema(O.linear_A([a.float()], True), None, 0.95))
+
+
 def test_multi_segment_and_running_average(ops):
     """LinearMultiLayer: sum over calls, each with its own 1/rows; then a second EMA update."""
     gen = torch.Generator().manual_seed(11)

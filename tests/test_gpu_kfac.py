@@ -275,3 +275,43 @@ def test_lstm_language_model_shape_matches_oracle(mode):
         assert_factor_close(l.state['G'], oracle.G[i])
         torch.testing.assert_close(l.module.weight.grad.cpu(), ref[i][0], rtol=1e-2, atol=1e-4)
         torch.testing.assert_close(l.module.bias.grad.cpu(), ref[i][1], rtol=1e-2, atol=1e-4)
+
+
+@pytest.mark.parametrize('amp_dtype', [torch.bfloat16, torch.float16], ids=['bf16', 'fp16'])
+def test_autocast_training_step_matches_oracle(mode, amp_dtype):
+    """the realistic mixed-precision loop.  The model runs under autocast, so
+    the hooks capture 16-bit activations and (loss-scaled) 16-bit output gradients; K-FAC reads
+    them natively, unscales G through the segment weight, and must match the oracle stepping on
+    the widened copies of the very same captures."""
+    from oracle import kfac_oracle as O
+    model = models.make_cnn().to(DEV)
+    scaler = models.FixedScaler(256.0)
+    kw = dict(damping=0.003, factor_decay=0.95, factor_update_freq=1, inv_update_freq=1, kl_clip=0.001, lr=0.1)
+    pre = kfac.KFAC(model, grad_scaler=scaler, **kw)
+    x, y = models.cnn_batch(0)
+    with torch.autocast('cuda', dtype=amp_dtype):
+        loss = F.cross_entropy(model(x.to(DEV)), y.to(DEV))
+    (loss * scaler.get_scale()).backward()
+    for p in model.parameters():
+        p.grad.div_(scaler.get_scale())
+    assert any(l.a_inputs[0].dtype == amp_dtype for l in pre.layers)
+    assert all(l.g_outputs[0][0].dtype == amp_dtype for l in pre.layers)
+    caps = [[([a.float().cpu() for a in l.a_inputs], [(g.float() / s).cpu() for g, s in l.g_outputs])
+             for l in pre.layers]]
+    grads = [(l.module.weight.grad.cpu().clone(),
+              None if l.module.bias is None else l.module.bias.grad.cpu().clone()) for l in pre.layers]
+    pre.step()
+    torch.cuda.synchronize()
+    specs = []
+    for l in pre.layers:
+        m = l.module
+        if isinstance(m, torch.nn.Conv2d):
+            specs.append(O.LayerSpec('conv2d', m.weight.shape, m.bias is not None, m.kernel_size, m.stride, m.padding))
+        else:
+            specs.append(O.LayerSpec('linear', m.weight.shape, m.bias is not None))
+    oracle = O.OracleKFAC(specs, **kw)
+    ref = oracle.step(caps, grads)
+    for i, l in enumerate(pre.layers):
+        assert_factor_close(l.state['A'], oracle.A[i])
+        assert_factor_close(l.state['G'], oracle.G[i])
+        torch.testing.assert_close(l.module.weight.grad.cpu(), ref[i][0], rtol=1e-2, atol=1e-4)
