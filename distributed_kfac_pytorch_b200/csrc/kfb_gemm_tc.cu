@@ -1,6 +1,8 @@
 // Grouped TF32 GEMM on the 5th-generation tensor cores:  D[m][n] = sum_k A[m][k] * B[n][k].
 //
-// One persistent CTA per SM walks the tile list of ALL problems of a stage (all K-FAC layers):
+// Two kernels with the same roles: gemm_tc2_kernel (default) pairs two CTAs per tile with
+// tcgen05 cta_group::2 (256 x 256 tiles); gemm_tc_kernel is the single-CTA version (128 x 256).
+// One persistent CTA (pair) per SM (pair) walks the tile list of ALL problems of a stage (all layers):
 //   warp 0      TMA producer: 128x32 (A) and 128x32 (B) fp32 boxes, 128B-swizzled, 6-stage ring
 //   warp 1      MMA issuer: 4 x tcgen05.mma.kind::tf32 (M=128, N=128, K=8) per stage, fp32
 //               accumulators in TMEM, double buffered (2 x 128 columns)
@@ -8,6 +10,8 @@
 //               warp-shuffle reduction (the KL-clip inner product)
 // Operands are consumed as fp32 straight from HBM (kind::tf32 reads the top 19 bits), so there
 // is no conversion pass.
+#include <stdlib.h>
+
 #include <algorithm>
 #include <mutex>
 #include <unordered_map>
@@ -238,6 +242,194 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
   }
 }
 
+// ==============================================================================================
+// CTA-pair variant (cta_group::2): a cluster of two CTAs on one TPC computes a 256 x BN tile.
+// Each CTA loads 128 rows of A and HALF of the B tile (BN/2 rows); the pair's tensor cores read
+// both halves, so per SM the shared-memory traffic per MMA drops from 12 KB written + 12 KB read
+// to 8 KB + 12 KB, lifting the shared-memory ceiling of fp32-operand TF32 from 67 % to ~80 %.
+// The leader CTA (cluster rank 0) issues the MMAs; TMA completions of both CTAs are credited to the
+// leader's full barrier; commits are multicast to both CTAs' empty / accumulator-full barriers.
+// ==============================================================================================
+constexpr int kStages2 = 6;
+constexpr int kStageBytes2 = (128 + 128) * BK * 4;                 // A 16 KB + half of B 16 KB
+constexpr int kSmemBytes2 = kStages2 * kStageBytes2 + 1024 + 256;
+
+__device__ __forceinline__ int snake_cluster_tile(int round, int total) {
+  const int g = gridDim.x >> 1, c = blockIdx.x >> 1;
+  const int t = round * g + ((round & 1) ? g - 1 - c : c);
+  return t < total ? t : -1;
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+    gemm_tc2_kernel(const __grid_constant__ TcBatch batch, float* __restrict__ dot_acc) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint64_t* full = (uint64_t*)(smem + kStages2 * kStageBytes2);
+  uint64_t* empty = full + kStages2;
+  uint64_t* tfull = empty + kStages2;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = (uint32_t*)(tempty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = umma::cluster_ctarank();
+  const bool leader = rank == 0;
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < kStages2; ++s) { umma::mbar_init(&full[s], 1); umma::mbar_init(&empty[s], 1); }
+    // tempty lives in the leader: all 2 x 128 epilogue threads of the pair arrive there
+    for (int s = 0; s < 2; ++s) { umma::mbar_init(&tfull[s], 1); umma::mbar_init(&tempty[s], 2 * 32 * kEpilogueWarps); }
+    umma::fence_barrier_init();
+  }
+  if (warp == 1) umma::tmem_alloc_pair<kTmemCols>(tmem_slot);
+  umma::tc_fence_before();
+  __syncthreads();
+  umma::cluster_sync_all();                 // both CTAs' barriers exist before anything remote happens
+  umma::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer (both CTAs) =====================
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int round = 0, tile; (tile = snake_cluster_tile(round, batch.total_tiles)) >= 0; ++round) {
+        const int p = find_prob(batch, tile);
+        const TcProb& pr = batch.probs[p];
+        const int local = tile - batch.start[p];
+        const int half = pr.bn >> 1;
+        const int m0 = (local / pr.tiles_n()) * 256 + (int)rank * 128;
+        const int n0 = (local % pr.tiles_n()) * pr.bn + (int)rank * half;
+        const int kblocks = (pr.K + BK - 1) / BK;
+        const uint32_t tx = 2u * (uint32_t)(128 + half) * BK * 4;      // both CTAs' bytes
+        for (int kb = 0; kb < kblocks; ++kb) {
+          umma::mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * kStageBytes2;
+          uint8_t* sb = sa + 128 * BK * 4;
+          if (leader) umma::mbar_arrive_expect_tx(&full[stage], tx);
+          umma::tma_load_2d_pair(sa, &pr.mapA, &full[stage], kb * BK, m0);
+          umma::tma_load_2d_pair(sb, &pr.mapB, &full[stage], kb * BK, n0);
+          if (++stage == kStages2) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader only) =====================
+    if (leader && lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      int acc = 0; uint32_t acc_phase = 0;
+      for (int round = 0, tile; (tile = snake_cluster_tile(round, batch.total_tiles)) >= 0; ++round) {
+        const int p = find_prob(batch, tile);
+        const int kblocks = (batch.probs[p].K + BK - 1) / BK;
+        const uint32_t idesc = umma::make_idesc_tf32(256, batch.probs[p].bn);
+        umma::mbar_wait(&tempty[acc], acc_phase ^ 1);
+        umma::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          umma::mbar_wait(&full[stage], phase);
+          umma::tc_fence_after();
+          const uint32_t sa = umma::smem_u32(smem + stage * kStageBytes2);
+          const uint32_t sb = sa + 128 * BK * 4;
+          const uint64_t da = umma::make_kmajor_sw128_desc(sa);
+          const uint64_t db = umma::make_kmajor_sw128_desc(sb);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k)
+            umma::mma_tf32_ss_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+          umma::tc_commit_pair(&empty[stage]);
+          if (++stage == kStages2) { stage = 0; phase ^= 1; }
+        }
+        umma::tc_commit_pair(&tfull[acc]);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else {
+    // ===================== epilogue (both CTAs: each drains its own 128 accumulator rows) =====
+    const int q = warp & 3;
+    int acc = 0; uint32_t acc_phase = 0;
+    float dot = 0.f;
+    for (int round = 0, tile; (tile = snake_cluster_tile(round, batch.total_tiles)) >= 0; ++round) {
+      const int p = find_prob(batch, tile);
+      const TcProb& pr = batch.probs[p];
+      const int local = tile - batch.start[p];
+      const int m0 = (local / pr.tiles_n()) * 256 + (int)rank * 128, n0 = (local % pr.tiles_n()) * pr.bn;
+      const int m = m0 + q * 32 + lane;
+      const bool row_ok = m < pr.M;
+      const float* mrow = (pr.Mul && row_ok) ? pr.Mul + (int64_t)m * pr.ldmul + n0 : nullptr;
+      const float* grow = (pr.Dot && row_ok) ? pr.Dot + (int64_t)m * pr.lddot + n0 : nullptr;
+      float* drow = pr.D + (int64_t)m * pr.ldd + n0;
+      const int ncols = min(pr.bn, pr.N - n0);
+      float4 mm[8], gg[8];
+      auto load_aux = [&](int c, float4 (&dm)[8], float4 (&dg)[8]) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          dm[j] = make_float4(1.f, 1.f, 1.f, 1.f);
+          dg[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+          const int col = c * 32 + 4 * j;
+          if (col + 3 < ncols) {
+            if (mrow) dm[j] = __ldg(reinterpret_cast<const float4*>(mrow + col));
+            if (grow) dg[j] = __ldg(reinterpret_cast<const float4*>(grow + col));
+          } else if (col < ncols) {
+            float tm[4] = {1.f, 1.f, 1.f, 1.f}, tg[4] = {0.f, 0.f, 0.f, 0.f};
+            for (int e = 0; e < 4; ++e)
+              if (col + e < ncols) {
+                if (mrow) tm[e] = mrow[col + e];
+                if (grow) tg[e] = grow[col + e];
+              }
+            dm[j] = make_float4(tm[0], tm[1], tm[2], tm[3]);
+            dg[j] = make_float4(tg[0], tg[1], tg[2], tg[3]);
+          }
+        }
+      };
+      const int nchunks = (ncols + 31) / 32;
+      load_aux(0, mm, gg);
+      umma::mbar_wait(&tfull[acc], acc_phase);
+      umma::tc_fence_after();
+      const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
+#pragma unroll 1
+      for (int c = 0; c < nchunks; ++c) {
+        uint32_t r[32];
+        umma::tmem_ld_32x32(taddr + c * 32, r);
+        float4 mm_next[8], gg_next[8];
+        if (c + 1 < nchunks) load_aux(c + 1, mm_next, gg_next);
+        umma::tmem_ld_wait();
+        if (row_ok) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int col = c * 32 + 4 * j;
+            float4 v = make_float4(__uint_as_float(r[4 * j]) * mm[j].x, __uint_as_float(r[4 * j + 1]) * mm[j].y,
+                                   __uint_as_float(r[4 * j + 2]) * mm[j].z, __uint_as_float(r[4 * j + 3]) * mm[j].w);
+            if (col + 3 < ncols) {
+              *reinterpret_cast<float4*>(drow + col) = v;
+            } else if (col < ncols) {
+              const float tv[4] = {v.x, v.y, v.z, v.w};
+              for (int e = 0; e < 4; ++e)
+                if (col + e < ncols) drow[col + e] = tv[e];
+            }
+            dot = fmaf(v.x, gg[j].x, fmaf(v.y, gg[j].y, fmaf(v.z, gg[j].z, fmaf(v.w, gg[j].w, dot))));
+          }
+        }
+        if (c + 1 < nchunks) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) { mm[j] = mm_next[j]; gg[j] = gg_next[j]; }
+        }
+      }
+      umma::tc_fence_before();
+      umma::mbar_arrive_leader(&tempty[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+    if (dot_acc) {
+      dot = warp_sum(dot);
+      if (lane == 0 && dot != 0.f) atomicAdd(dot_acc, dot);
+    }
+  }
+
+  umma::tc_fence_before();
+  __syncthreads();
+  umma::cluster_sync_all();                 // the peer may still be signalling this CTA's barriers
+  if (warp == 1) {
+    umma::tc_fence_after();
+    umma::tmem_dealloc_pair<kTmemCols>(tmem_base);
+  }
+}
+
 // ---- tensor-map cache ----------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -296,7 +488,49 @@ bool gemm_tc_eligible(const GemmProb& p) {
   return p.M > 0 && p.N > 0 && p.K > 0;
 }
 
+static int gemm_grouped_tc2(Context* ctx, const GemmProb* probs, int n, float* dot_acc, cudaStream_t stream) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    KFB_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes2));
+    attr_set = true;
+  }
+  std::vector<GemmProb> sorted(probs, probs + n);
+  std::stable_sort(sorted.begin(), sorted.end(), [](const GemmProb& a, const GemmProb& b) { return a.K > b.K; });
+  probs = sorted.data();
+  static TcBatch batch;
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lock(mu);
+  for (int base = 0; base < n; base += kTcBatch) {
+    batch.n = std::min(kTcBatch, n - base);
+    int tiles = 0;
+    for (int i = 0; i < batch.n; ++i) {
+      const GemmProb& g = probs[base + i];
+      TcProb& t = batch.probs[i];
+      int rc = get_map(ctx, g.A, g.lda, g.M, g.K, 128, &t.mapA);
+      if (rc) return rc;
+      t.bn = g.N > 128 ? 256 : 128;
+      rc = get_map(ctx, g.B, g.ldb, g.N, g.K, t.bn / 2, &t.mapB);      // each CTA loads half of the B tile
+      if (rc) return rc;
+      t.D = g.D; t.Mul = g.Mul; t.Dot = g.Dot; t.ldd = g.ldd; t.ldmul = g.ldmul; t.lddot = g.lddot;
+      t.M = g.M; t.N = g.N; t.K = g.K;
+      batch.start[i] = tiles;
+      tiles += ceil_div(g.M, 256) * t.tiles_n();
+    }
+    batch.start[batch.n] = tiles;
+    batch.total_tiles = tiles;
+    const int clusters = std::min(tiles, ctx->num_sms / 2);
+    gemm_tc2_kernel<<<2 * clusters, kThreads, kSmemBytes2, stream>>>(batch, dot_acc);
+    KFB_CHECK_LAUNCH();
+  }
+  return KFB_OK;
+}
+
 int gemm_grouped_tc(Context* ctx, const GemmProb* probs, int n, float* dot_acc, cudaStream_t stream) {
+  // CTA-pair kernel by default (measured 0.72 -> 0.67 ms for the ResNet-50 chain; routing the
+  // problems with M <= 128 to the single-CTA kernel instead was slower); KFB_GEMM_2CTA=0 selects
+  // the single-CTA kernel
+  static const bool use_pair = []() { const char* e = getenv("KFB_GEMM_2CTA"); return !e || atoi(e) != 0; }();
+  if (use_pair) return gemm_grouped_tc2(ctx, probs, n, dot_acc, stream);
   static bool attr_set = false;
   if (!attr_set) {
     KFB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
