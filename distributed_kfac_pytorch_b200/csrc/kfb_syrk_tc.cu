@@ -15,6 +15,7 @@
 //                 over (ky,kx) (padding / image border), coalesced along the output row
 // Operands stay fp32 in shared memory; kind::tf32 reads the top 19 bits, so no conversion pass.
 #include <algorithm>
+#include <type_traits>
 #include <vector>
 
 #include "kfb_factor.cuh"
@@ -74,6 +75,15 @@ __device__ __forceinline__ int snake_item(int round, int total) {
   return t < total ? t : -1;
 }
 
+// explicit shared-space stores: through a generic pointer the compiler emits ST.E (generic
+// address translation on every store) instead of STS
+__device__ __forceinline__ void sts_f32(uint32_t addr, float v) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void sts_v4(uint32_t addr, float4 v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
@@ -110,6 +120,7 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
     // swizzle term (row & 7) is the same for all of them
     const uint32_t lane_off = (uint32_t)((((lane >> 2) ^ (pw & 7)) << 4) | ((lane & 3) << 2));
     const uint32_t vec_kq = lane & 7, vec_rsub = lane >> 3;
+    const uint32_t smem_base = umma::smem_u32(smem);
     int stage = 0; uint32_t phase = 0;
     for (int round = 0, it; (it = snake_item(round, n_items)) >= 0; ++round) {
       const TcItem item = items[it];
@@ -129,8 +140,8 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
       const int S = s.oh * s.ow;
       const uint32_t uS = (uint32_t)S, uow = (uint32_t)s.ow;
       const uint32_t k_end32 = item.k_end;       // K < 2^31 (checked on the host)
-      const int esh = s.dtype == KFB_F32 ? 2 : 1;          // log2(bytes per captured element)
-      const bool vec4 = s.kind == KFB_SEG_NCHW && (S & 3) == 0 && (((uintptr_t)s.data) & ((4u << esh) - 1)) == 0;
+      const bool vec4 = s.kind == KFB_SEG_NCHW && (S & 3) == 0 &&
+                        (((uintptr_t)s.data) & (s.dtype == KFB_F32 ? 15u : 7u)) == 0;
       const bool wide = s.kind == KFB_SEG_IM2COL && s.kh * s.kw > 30;
       // does this warp own the bias feature's row in one of the tiles?
       int bias_slot = -1, bias_row = 0;
@@ -145,123 +156,130 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
         }
       }
 
-      if (vec4) {
-        // ---- NCHW, 16B-alignable: 8 lanes x float4 = one tile row (32 k), 4 rows per instruction
-        uint32_t info[4][2];
-#pragma unroll
-        for (int t = 0; t < 4; ++t)
-#pragma unroll
-          for (int i = 0; i < 2; ++i)
-            info[t][i] = t < n_slots ? row_info(s, d, tile_of[t] * TM + pw + kProducerWarps * (4 * i + vec_rsub)) : kBitNever;
-        for (uint32_t k0 = item.k_begin; k0 < k_end32; k0 += BK) {
-          umma::mbar_wait(&empty[stage], phase ^ 1);
-          uint8_t* st = smem + stage * kStageBytes;
-          const uint32_t k = k0 + 4 * vec_kq;
-          const bool kin = k < k_end32;
-          const uint32_t n = k / uS;
-          const char* src = reinterpret_cast<const char*>(s.data) + (((int64_t)n * s.c * S + (k - n * uS)) << esh);
-          float4 v[4][2];
-#pragma unroll
+      // The gather loops are instantiated once per element width so that the fp32 path carries no
+      // run-time dtype tests (they cost ~30 % of the factor stage when left in the loop).
+      auto gather = [&](auto esh_tag) {
+        constexpr int esh = decltype(esh_tag)::value;     // log2(bytes per captured element)
+        if (vec4) {
+          // ---- NCHW, 16B-alignable: 8 lanes x float4 = one tile row (32 k), 4 rows per instruction
+          uint32_t info[4][2];
+  #pragma unroll
           for (int t = 0; t < 4; ++t)
-#pragma unroll
-            for (int i = 0; i < 2; ++i) {
-              v[t][i] = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (kin && (info[t][i] & 63u) == kBitAlways) {
-                const char* p = src + ((size_t)(info[t][i] >> 6) << esh);
-                if (esh == 2) {
-                  v[t][i] = __ldg(reinterpret_cast<const float4*>(p));
-                } else {               // four 16-bit captures in one 8-byte load
-                  const uint2 h = __ldg(reinterpret_cast<const uint2*>(p));
-                  v[t][i] = make_float4(widen16((unsigned short)(h.x & 0xffff), s.dtype), widen16((unsigned short)(h.x >> 16), s.dtype),
-                                        widen16((unsigned short)(h.y & 0xffff), s.dtype), widen16((unsigned short)(h.y >> 16), s.dtype));
-                }
-              }
-            }
-#pragma unroll
-          for (int t = 0; t < 4; ++t)
-#pragma unroll
+  #pragma unroll
             for (int i = 0; i < 2; ++i)
-              if (t < n_slots) {
-                const int r = pw + kProducerWarps * (4 * i + vec_rsub);
-                *reinterpret_cast<float4*>(st + slot_of[t] * kTileBytes + r * 128 + ((vec_kq ^ (r & 7)) << 4)) = v[t][i];
-              }
-          umma::fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) umma::mbar_arrive(&full[stage]);
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
-        }
-      } else {
-        // ---- general gather: one X row per lane, this warp's 8 rows of every tile per stage
-        uint32_t info[4][kRowsPerWarp];
-#pragma unroll
-        for (int t = 0; t < 4; ++t)
-#pragma unroll
-          for (int j = 0; j < kRowsPerWarp; ++j)
-            info[t][j] = t < n_slots ? row_info(s, d, tile_of[t] * TM + pw + kProducerWarps * j) : kBitNever;
-        for (uint32_t k0 = item.k_begin; k0 < k_end32; k0 += BK) {
-          umma::mbar_wait(&empty[stage], phase ^ 1);
-          uint8_t* st = smem + stage * kStageBytes + pw * 128 + lane_off;
-          const uint32_t k = k0 + lane;
-          const bool kin = k < k_end32;
-          const uint32_t n = k / uS;
-          const uint32_t r = k - n * uS;
-          const char* src;
-          uint32_t mlo = 0, mhi = 0;
-          if (s.kind == KFB_SEG_NCHW) {
-            src = reinterpret_cast<const char*>(s.data) + (((int64_t)n * s.c * S + r) << esh);
-            if (kin) mhi = 1u << (kBitAlways - 32);
-          } else {
-            const int oy = (int)(r / uow), ox = (int)(r - (uint32_t)oy * uow);
-            const int y0 = oy * s.sh - s.ph, x0 = ox * s.sw - s.pw;
-            src = reinterpret_cast<const char*>(s.data) + (((int64_t)n * s.c * s.h * s.w + (int64_t)y0 * s.w + x0) << esh);
-            if (kin) {
-              const int kx_lo = max(0, -x0), kx_hi = min(s.kw, s.w - x0);
-              const int ky_lo = max(0, -y0), ky_hi = min(s.kh, s.h - y0);
-              uint64_t m = 0;
-              const uint64_t xm = kx_hi > kx_lo ? (((1ull << (kx_hi - kx_lo)) - 1) << kx_lo) : 0;
-              for (int ky = ky_lo; ky < ky_hi; ++ky) m |= xm << (ky * s.kw);
-              mlo = (uint32_t)m;
-              mhi = (uint32_t)(m >> 32);
-            }
-          }
-          // narrow: (ky,kx) bits in mlo; "always" moves to bit 30 so one word decides everything
-          // (row_info's 6-bit field: 62 & 31 = 30, 63 & 31 = 31 which is never set)
-          const uint32_t mnarrow = mlo | ((mhi >> (kBitAlways - 32)) << 30);
-          // two tiles (16 independent loads per lane) in flight at a time
-#pragma unroll
-          for (int tp = 0; tp < 2; ++tp) {
-            if (2 * tp >= n_slots) break;
-            float v[2][kRowsPerWarp];
-#pragma unroll
-            for (int u = 0; u < 2; ++u)
-#pragma unroll
-              for (int j = 0; j < kRowsPerWarp; ++j) {
-                const uint32_t inf = info[2 * tp + u][j];
-                const bool ok = wide ? row_valid<true>(inf, mlo, mhi) : row_valid<false>(inf, mnarrow, 0u);
-                v[u][j] = 0.f;
-                if (ok) {
-                  const char* p = src + ((int64_t)(inf >> 6) << esh);
-                  v[u][j] = esh == 2 ? __ldg(reinterpret_cast<const float*>(p))
-                                     : widen16(__ldg(reinterpret_cast<const unsigned short*>(p)), s.dtype);
+              info[t][i] = t < n_slots ? row_info(s, d, tile_of[t] * TM + pw + kProducerWarps * (4 * i + vec_rsub)) : kBitNever;
+          for (uint32_t k0 = item.k_begin; k0 < k_end32; k0 += BK) {
+            umma::mbar_wait(&empty[stage], phase ^ 1);
+            const uint32_t st = smem_base + stage * kStageBytes;
+            const uint32_t k = k0 + 4 * vec_kq;
+            const bool kin = k < k_end32;
+            const uint32_t n = k / uS;
+            const char* src = reinterpret_cast<const char*>(s.data) + (((int64_t)n * s.c * S + (k - n * uS)) << esh);
+            float4 v[4][2];
+  #pragma unroll
+            for (int t = 0; t < 4; ++t)
+  #pragma unroll
+              for (int i = 0; i < 2; ++i) {
+                v[t][i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (kin && (info[t][i] & 63u) == kBitAlways) {
+                  const char* p = src + ((uint64_t)(info[t][i] >> 6) << esh);
+                  if (esh == 2) {
+                    v[t][i] = __ldg(reinterpret_cast<const float4*>(p));
+                  } else {               // four 16-bit captures in one 8-byte load
+                    const uint2 h = __ldg(reinterpret_cast<const uint2*>(p));
+                    v[t][i] = make_float4(widen16((unsigned short)(h.x & 0xffff), s.dtype), widen16((unsigned short)(h.x >> 16), s.dtype),
+                                          widen16((unsigned short)(h.y & 0xffff), s.dtype), widen16((unsigned short)(h.y >> 16), s.dtype));
+                  }
                 }
               }
-#pragma unroll
-            for (int u = 0; u < 2; ++u)
-#pragma unroll
-              for (int j = 0; j < kRowsPerWarp; ++j)
-                if (2 * tp + u < n_slots)
-                  *reinterpret_cast<float*>(st + slot_of[2 * tp + u] * kTileBytes + j * (kProducerWarps * 128)) = v[u][j];
+  #pragma unroll
+            for (int t = 0; t < 4; ++t)
+  #pragma unroll
+              for (int i = 0; i < 2; ++i)
+                if (t < n_slots) {
+                  const int r = pw + kProducerWarps * (4 * i + vec_rsub);
+                  sts_v4(st + slot_of[t] * kTileBytes + r * 128 + ((vec_kq ^ (r & 7)) << 4), v[t][i]);
+                }
+            umma::fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) umma::mbar_arrive(&full[stage]);
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
-          // the bias feature is the constant 1 wherever the X row exists
-          if (bias_slot >= 0)
-            *reinterpret_cast<float*>(smem + stage * kStageBytes + bias_slot * kTileBytes + bias_row * 128 + lane_off) =
-                kin ? 1.f : 0.f;
-          umma::fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) umma::mbar_arrive(&full[stage]);
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        } else {
+          // ---- general gather: one X row per lane, this warp's 8 rows of every tile per stage
+          uint32_t info[4][kRowsPerWarp];
+  #pragma unroll
+          for (int t = 0; t < 4; ++t)
+  #pragma unroll
+            for (int j = 0; j < kRowsPerWarp; ++j)
+              info[t][j] = t < n_slots ? row_info(s, d, tile_of[t] * TM + pw + kProducerWarps * j) : kBitNever;
+          for (uint32_t k0 = item.k_begin; k0 < k_end32; k0 += BK) {
+            umma::mbar_wait(&empty[stage], phase ^ 1);
+            const uint32_t st = smem_base + stage * kStageBytes + pw * 128 + lane_off;
+            const uint32_t k = k0 + lane;
+            const bool kin = k < k_end32;
+            const uint32_t n = k / uS;
+            const uint32_t r = k - n * uS;
+            const char* src;
+            uint32_t mlo = 0, mhi = 0;
+            if (s.kind == KFB_SEG_NCHW) {
+              src = reinterpret_cast<const char*>(s.data) + (((int64_t)n * s.c * S + r) << esh);
+              if (kin) mhi = 1u << (kBitAlways - 32);
+            } else {
+              const int oy = (int)(r / uow), ox = (int)(r - (uint32_t)oy * uow);
+              const int y0 = oy * s.sh - s.ph, x0 = ox * s.sw - s.pw;
+              src = reinterpret_cast<const char*>(s.data) + (((int64_t)n * s.c * s.h * s.w + (int64_t)y0 * s.w + x0) << esh);
+              if (kin) {
+                const int kx_lo = max(0, -x0), kx_hi = min(s.kw, s.w - x0);
+                const int ky_lo = max(0, -y0), ky_hi = min(s.kh, s.h - y0);
+                uint64_t m = 0;
+                const uint64_t xm = kx_hi > kx_lo ? (((1ull << (kx_hi - kx_lo)) - 1) << kx_lo) : 0;
+                for (int ky = ky_lo; ky < ky_hi; ++ky) m |= xm << (ky * s.kw);
+                mlo = (uint32_t)m;
+                mhi = (uint32_t)(m >> 32);
+              }
+            }
+            // narrow: (ky,kx) bits in mlo; "always" moves to bit 30 so one word decides everything
+            // (row_info's 6-bit field: 62 & 31 = 30, 63 & 31 = 31 which is never set)
+            const uint32_t mnarrow = mlo | ((mhi >> (kBitAlways - 32)) << 30);
+            // two tiles (16 independent loads per lane) in flight at a time
+  #pragma unroll
+            for (int tp = 0; tp < 2; ++tp) {
+              if (2 * tp >= n_slots) break;
+              float v[2][kRowsPerWarp];
+  #pragma unroll
+              for (int u = 0; u < 2; ++u)
+  #pragma unroll
+                for (int j = 0; j < kRowsPerWarp; ++j) {
+                  const uint32_t inf = info[2 * tp + u][j];
+                  const bool ok = wide ? row_valid<true>(inf, mlo, mhi) : row_valid<false>(inf, mnarrow, 0u);
+                  v[u][j] = 0.f;
+                  if (ok) {
+                    const char* p = src + ((uint64_t)(inf >> 6) << esh);
+                    v[u][j] = esh == 2 ? __ldg(reinterpret_cast<const float*>(p))
+                                       : widen16(__ldg(reinterpret_cast<const unsigned short*>(p)), s.dtype);
+                  }
+                }
+  #pragma unroll
+              for (int u = 0; u < 2; ++u)
+  #pragma unroll
+                for (int j = 0; j < kRowsPerWarp; ++j)
+                  if (2 * tp + u < n_slots)
+                    sts_f32(st + slot_of[2 * tp + u] * kTileBytes + j * (kProducerWarps * 128), v[u][j]);
+            }
+            // the bias feature is the constant 1 wherever the X row exists
+            if (bias_slot >= 0)
+              sts_f32(smem_base + stage * kStageBytes + bias_slot * kTileBytes + bias_row * 128 + lane_off,
+                      kin ? 1.f : 0.f);
+            umma::fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) umma::mbar_arrive(&full[stage]);
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
+          }
         }
-      }
+      };
+      if (s.dtype == KFB_F32) gather(std::integral_constant<int, 2>{});
+      else gather(std::integral_constant<int, 1>{});
     }
   } else if (warp == 4) {
     // ===================== MMA issuer =====================
