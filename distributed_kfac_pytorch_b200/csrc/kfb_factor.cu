@@ -343,8 +343,6 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
     dj.state = j.state; dj.ld_state = j.ld_state;
     dj.seed_identity = j.seed_identity; dj.write_state = j.write_state; dj.tri_out = j.tri_out;
     dj.ld_scratch = (j.d + 3) / 4 * 4;
-    dj.scratch_off = plan->scratch_floats;
-    plan->scratch_floats += align_up((size_t)dj.ld_scratch * j.d, 64);
     dj.T = ceil_div(j.d, TS);
     dj.n_pairs = dj.T * (dj.T + 1) / 2;
     dj.T32 = ceil_div(j.d, 32);
@@ -401,10 +399,15 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
     }
     dj.n_chunks = chunks;
     dj.use_tc = tc ? 1 : 0;
+    // short-K single-segment jobs (the 7x7-map layers: the LARGEST factors) are one work item per
+    // block: their SYRK epilogue fuses scale + running average + mirror + triangle export
+    dj.fused = (tc && j.n_segments == 1 && k_total <= kFusedMaxRows) ? 1 : 0;
+    dj.scratch_off = plan->scratch_floats;
+    if (!dj.fused) plan->scratch_floats += align_up((size_t)dj.ld_scratch * j.d, 64);
     plan->item_start.push_back(items);
     plan->fin_start.push_back(fins);
     if (!tc) items += dj.n_pairs * chunks;
-    fins += dj.T32 * (dj.T32 + 1) / 2;
+    if (!dj.fused) fins += dj.T32 * (dj.T32 + 1) / 2;
     plan->jobs.push_back(dj);
   }
   plan->item_start.push_back(items);
@@ -491,7 +494,7 @@ int kfb_factor_update(const kfb_factor_job* jobs, int32_t n_jobs, float alpha, v
   KFB_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
   rc = kfb::upload_plan(&plan, workspace, stream);
   if (rc) return rc;
-  rc = kfb::launch_syrk(plan, workspace, ctx, stream);
+  rc = kfb::launch_syrk(plan, workspace, ctx, alpha, stream);
   if (rc) return rc;
   return kfb::launch_finalize(plan, workspace, alpha, stream);
 }

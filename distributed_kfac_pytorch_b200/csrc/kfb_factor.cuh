@@ -38,6 +38,8 @@ struct DevJob {
   int n_chunks;          // split-K chunks over all segments
   int T32;               // 32-wide blocks per side for finalize
   int use_tc;            // 1: handled by the tcgen05 SYRK
+  int fused;             // 1: one K chunk, one segment: the SYRK epilogue applies the running average
+                         //    itself and writes the state - no scratch, no reds, no finalize pass
 };
 
 // One captured element, widened to fp32 (16-bit captures come from AMP autocast).
@@ -71,7 +73,8 @@ KFB_HIDDEN int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, 
 KFB_HIDDEN void plan_syrk_tc(FactorPlan* plan);
 KFB_HIDDEN int upload_plan(FactorPlan* plan, void* workspace, cudaStream_t stream);
 KFB_HIDDEN int launch_syrk_simt(const FactorPlan& plan, void* workspace, cudaStream_t stream);
-KFB_HIDDEN int launch_syrk(const FactorPlan& plan, void* workspace, Context* ctx, cudaStream_t stream);
+KFB_HIDDEN int launch_syrk(const FactorPlan& plan, void* workspace, Context* ctx, float alpha, cudaStream_t stream);
+constexpr int64_t kFusedMaxRows = 4096;   // jobs with at most this many rows of X are never split along K
 KFB_HIDDEN int launch_finalize(const FactorPlan& plan, void* workspace, float alpha, cudaStream_t stream);
 
 }  // namespace kfb

@@ -70,7 +70,7 @@ int kfb_factor_update_static(const kfb_factor_job* jobs, int32_t n_jobs, float a
   // upload_plan clears the accumulators: whatever the previous call left in the array is gone
   rc = upload_plan(&plan, ws, stream);
   if (rc) return rc;
-  rc = launch_syrk(plan, ws, ctx, stream);
+  rc = launch_syrk(plan, ws, ctx, alpha, stream);
   if (rc) return rc;
   return launch_finalize(plan, ws, alpha, stream);
 }

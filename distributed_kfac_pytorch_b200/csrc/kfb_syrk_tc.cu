@@ -90,7 +90,7 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
 
 __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __restrict__ jobs,
                                                             const DevSegment* __restrict__ segs,
-                                                            const TcItem* __restrict__ items, int n_items) {
+                                                            const TcItem* __restrict__ items, int n_items, float alpha) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint64_t* full = (uint64_t*)(smem + kStages * kStageBytes);
@@ -327,6 +327,7 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
       const float weight = segs[item.seg].weight;
       const int d = job.d;
       const bool diag = item.a0 == item.b0;
+      const float ratio = alpha / (1.f - alpha), one_m = 1.f - alpha;
       umma::mbar_wait(tfull, acc_phase);
       umma::tc_fence_after();
       for (int m = 0; m < item.mi; ++m) {
@@ -341,6 +342,54 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
             uint32_t r[32];
             umma::tmem_ld_32x32(taddr + c * 32, r);
             umma::tmem_ld_wait();
+            if (job.fused) {
+              // ---- fused finish: this item holds the COMPLETE sum for its block.
+              //   new = (old * alpha/(1-alpha) + w*acc) * (1-alpha)     (kfac/layers/utils.py:175-178)
+              // written to the state row (this thread owns row i), mirrored into column i (one
+              // coalesced 128-byte store per column: the 32 lanes are 32 consecutive rows), and
+              // exported to the packed triangle.  A diagonal TILE holds both of its triangles.
+              const bool diag_tile = (item.a0 + m) == (item.b0 + nn);
+              const bool row_ok = i < d;
+              if (row_ok) {
+                const float* orow = job.state + (int64_t)i * job.ld_state + jb;
+#pragma unroll
+                for (int e = 0; e < 32; ++e) {
+                  const int j = jb + e;
+                  float old = 0.f;
+                  if (j < d) old = job.seed_identity ? (i == j ? 1.f : 0.f) : orow[e];
+                  r[e] = __float_as_uint((old * ratio + __uint_as_float(r[e]) * weight) * one_m);
+                }
+                if (job.write_state) {
+                  float* srow = job.state + (int64_t)i * job.ld_state + jb;
+#pragma unroll
+                  for (int g = 0; g < 8; ++g) {
+                    const int j = jb + 4 * g;
+                    if (j + 3 < d) {
+                      *reinterpret_cast<uint4*>(srow + 4 * g) = make_uint4(r[4 * g], r[4 * g + 1], r[4 * g + 2], r[4 * g + 3]);
+                    } else {
+                      for (int e = 0; e < 4; ++e)
+                        if (j + e < d) srow[4 * g + e] = __uint_as_float(r[4 * g + e]);
+                    }
+                  }
+                }
+                if (job.tri_out) {
+                  float* trow = job.tri_out + ((int64_t)i * d - ((int64_t)i * (i - 1)) / 2 - i);
+#pragma unroll
+                  for (int e = 0; e < 32; ++e) {
+                    const int j = jb + e;
+                    if (j < d && j >= i) trow[j] = __uint_as_float(r[e]);
+                  }
+                }
+              }
+              if (!diag_tile && job.write_state) {
+#pragma unroll
+                for (int e = 0; e < 32; ++e) {
+                  const int j = jb + e;
+                  if (row_ok && j < d) job.state[(int64_t)j * job.ld_state + i] = __uint_as_float(r[e]);
+                }
+              }
+              continue;
+            }
             if (i < d && jb + 31 >= i) {
               float* row = job.scratch + (int64_t)i * job.ld_scratch + jb;
 #pragma unroll
@@ -386,7 +435,7 @@ void plan_syrk_tc(FactorPlan* plan) {
     const int TB = ceil_div(T, 2);            // 256-wide blocks per side
     for (int si = 0; si < j.n_segments; ++si) {
       const DevSegment& s = plan->segs[j.seg_start + si];
-      const int64_t nch = std::max<int64_t>(1, ceil_div64(s.K, kChunk));
+      const int64_t nch = j.fused ? 1 : std::max<int64_t>(1, ceil_div64(s.K, kChunk));
       const int64_t len = ceil_div64(ceil_div64(s.K, nch), BK) * BK;
       for (int64_t k = 0; k < s.K; k += len)
         for (int bi = 0; bi < TB; ++bi)
@@ -408,7 +457,7 @@ void plan_syrk_tc(FactorPlan* plan) {
                    [&](const TcItem& a, const TcItem& b) { return cost(a) > cost(b); });
 }
 
-int launch_syrk_tc(const FactorPlan& plan, void* workspace, Context* ctx, cudaStream_t stream) {
+int launch_syrk_tc(const FactorPlan& plan, void* workspace, Context* ctx, float alpha, cudaStream_t stream) {
   if (plan.tc_items.empty()) return KFB_OK;
   static bool attr_set = false;
   if (!attr_set) {
@@ -420,13 +469,13 @@ int launch_syrk_tc(const FactorPlan& plan, void* workspace, Context* ctx, cudaSt
   const int grid = std::min(n, ctx->num_sms);
   syrk_tc_kernel<<<grid, kThreads, kSmemBytes, stream>>>((const DevJob*)(ws + plan.off_jobs),
                                                        (const DevSegment*)(ws + plan.off_segs),
-                                                       (const TcItem*)(ws + plan.off_tc_items), n);
+                                                       (const TcItem*)(ws + plan.off_tc_items), n, alpha);
   KFB_CHECK_LAUNCH();
   return KFB_OK;
 }
 
-int launch_syrk(const FactorPlan& plan, void* workspace, Context* ctx, cudaStream_t stream) {
-  int rc = launch_syrk_tc(plan, workspace, ctx, stream);
+int launch_syrk(const FactorPlan& plan, void* workspace, Context* ctx, float alpha, cudaStream_t stream) {
+  int rc = launch_syrk_tc(plan, workspace, ctx, alpha, stream);
   if (rc) return rc;
   return launch_syrk_simt(plan, workspace, stream);
 }
