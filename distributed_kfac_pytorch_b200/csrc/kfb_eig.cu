@@ -178,7 +178,11 @@ struct BatchPlan {
 
 // measured on B200 (tools/try_syev_batched.py): the batched solver wins for n <= 512 and, with
 // enough matrices to amortise over, up to n = 1024; above that syevd per matrix is faster
-bool batched_wins(int d, size_t count) { return count >= 2 && (d <= 512 || (d <= 1024 && count >= 8)); }
+bool batched_wins(int d, size_t count) {
+  static const int big_max = []() { const char* e = getenv("KFB_SYEV_BATCH_MAX_D"); return e ? atoi(e) : 1024; }();
+  static const int big_min_count = []() { const char* e = getenv("KFB_SYEV_BATCH_MIN_COUNT"); return e ? atoi(e) : 8; }();
+  return count >= 2 && (d <= 512 || (d <= big_max && (int)count >= big_min_count));
+}
 
 int make_plan(kfb::Context* ctx, LanePool* pool, const kfb_syevd_job* jobs, int n, BatchPlan* plan) {
   std::vector<int> order(n);
