@@ -6,6 +6,7 @@
 // shapes the tensor-core kernel does not take) and the finalize / pack / unpack kernels.
 // The tcgen05 SYRK lives in kfb_syrk_tc.cu and writes the same scratch convention.
 #include <algorithm>
+#include <mutex>
 #include <vector>
 
 #include "kfb_factor.cuh"
@@ -427,6 +428,86 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
   return KFB_OK;
 }
 
+// ---- plan cache ---------------------------------------------------------------------------------
+// Planning (tile/chunk tables, the sorted tensor-core work list) depends only on the GEOMETRY of the
+// jobs, which is the same at every factor update of a training run; only pointers, weights and the
+// seed/write flags change.  The last plan is kept and patched instead of being rebuilt twice per
+// update (once for the workspace size, once for the launch).
+namespace {
+std::mutex g_plan_mu;
+FactorPlan g_plan;
+std::vector<int64_t> g_plan_sig;
+
+void signature(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool tc, std::vector<int64_t>* sig) {
+  sig->clear();
+  sig->push_back(n_jobs); sig->push_back(num_sms); sig->push_back(tc);
+  for (int i = 0; i < n_jobs; ++i) {
+    const kfb_factor_job& j = jobs[i];
+    sig->push_back(j.d); sig->push_back(j.n_segments); sig->push_back(j.ld_state);
+    if (!j.segments) continue;
+    for (int k = 0; k < j.n_segments; ++k) {
+      const kfb_segment& s = j.segments[k];
+      const int64_t v[] = {s.kind, s.has_bias, s.n, s.c, s.h, s.w, s.kh, s.kw, s.sh, s.sw, s.ph, s.pw, s.ld, s.dtype};
+      sig->insert(sig->end(), v, v + sizeof(v) / sizeof(v[0]));
+    }
+  }
+}
+}  // namespace
+
+// Returns the (cached or freshly built) plan with this call's pointers patched in.  The caller
+// must hold g_plan_mu for as long as it uses the plan.
+static int cached_plan(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool tc, FactorPlan** out) {
+  KFB_REQUIRE(n_jobs >= 0 && (jobs || n_jobs == 0), "bad job array");
+  std::vector<int64_t> sig;
+  signature(jobs, n_jobs, num_sms, tc, &sig);
+  if (sig != g_plan_sig) {
+    g_plan_sig.clear();
+    int rc = plan_factor(jobs, n_jobs, num_sms, tc, &g_plan);
+    if (rc) return rc;
+    g_plan_sig.swap(sig);
+  } else {
+    for (int i = 0; i < n_jobs; ++i) {
+      const kfb_factor_job& j = jobs[i];
+      KFB_REQUIRE(j.state, "factor job %d: null state", i);
+      DevJob& dj = g_plan.jobs[i];
+      dj.state = j.state; dj.seed_identity = j.seed_identity; dj.write_state = j.write_state; dj.tri_out = j.tri_out;
+      for (int k = 0; k < j.n_segments; ++k) {
+        KFB_REQUIRE(j.segments[k].data, "factor job %d segment %d: null data", i, k);
+        DevSegment& ds = g_plan.segs[dj.seg_start + k];
+        ds.data = j.segments[k].data;
+        ds.weight = j.segments[k].weight;
+      }
+    }
+  }
+  *out = &g_plan;
+  return KFB_OK;
+}
+
+int factor_update_with(const kfb_factor_job* jobs, int n_jobs, float alpha, Context* ctx, void* workspace,
+                       size_t workspace_bytes, const char* what, cudaStream_t stream) {
+  std::lock_guard<std::mutex> lock(g_plan_mu);
+  FactorPlan* plan;
+  int rc = cached_plan(jobs, n_jobs, ctx->num_sms, ctx->umma_ok && mma_mode() == 1, &plan);
+  if (rc) return rc;
+  if (!workspace || workspace_bytes < plan->total_bytes)
+    KFB_FAIL(KFB_ERR_WORKSPACE, "%s: these %d job(s) need %zu bytes of scratch but %zu are available", what, n_jobs,
+             plan->total_bytes, workspace_bytes);
+  KFB_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+  rc = upload_plan(plan, workspace, stream);
+  if (rc) return rc;
+  rc = launch_syrk(*plan, workspace, ctx, alpha, stream);
+  if (rc) return rc;
+  return launch_finalize(*plan, workspace, alpha, stream);
+}
+
+size_t factor_workspace_bytes(const kfb_factor_job* jobs, int n_jobs, Context* ctx) {
+  std::lock_guard<std::mutex> lock(g_plan_mu);
+  FactorPlan* plan;
+  bool tc = ctx && ctx->umma_ok && mma_mode() == 1;
+  if (cached_plan(jobs, n_jobs, ctx ? ctx->num_sms : 148, tc, &plan) != KFB_OK) return 0;
+  return plan->total_bytes;
+}
+
 int upload_plan(FactorPlan* plan, void* workspace, cudaStream_t stream) {
   char* ws = (char*)workspace;
   float* scratch = (float*)(ws + plan->off_scratch);
@@ -470,11 +551,7 @@ int launch_finalize(const FactorPlan& plan, void* workspace, float alpha, cudaSt
 extern "C" {
 
 size_t kfb_factor_workspace_bytes(const kfb_factor_job* jobs, int32_t n_jobs) {
-  kfb::FactorPlan plan;
-  kfb::Context* ctx = kfb::current_context();
-  bool tc = ctx && ctx->umma_ok && kfb::mma_mode() == 1;
-  if (kfb::plan_factor(jobs, n_jobs, ctx ? ctx->num_sms : 148, tc, &plan) != KFB_OK) return 0;
-  return plan.total_bytes;
+  return kfb::factor_workspace_bytes(jobs, n_jobs, kfb::current_context());
 }
 
 int kfb_factor_update(const kfb_factor_job* jobs, int32_t n_jobs, float alpha, void* workspace,
@@ -485,18 +562,8 @@ int kfb_factor_update(const kfb_factor_job* jobs, int32_t n_jobs, float alpha, v
   if (n_jobs == 0) return KFB_OK;
   KFB_REQUIRE(alpha > 0.f && alpha <= 1.f, "alpha must be in (0, 1], got %g", alpha);
   if (alpha == 1.f) return KFB_OK;   // update_running_avg is a no-op (kfac/layers/utils.py:175)
-  cudaStream_t stream = (cudaStream_t)stream_;
-  kfb::FactorPlan plan;
-  rc = kfb::plan_factor(jobs, n_jobs, ctx->num_sms, ctx->umma_ok && kfb::mma_mode() == 1, &plan);
-  if (rc) return rc;
-  if (!workspace || workspace_bytes < plan.total_bytes)
-    KFB_FAIL(KFB_ERR_WORKSPACE, "factor workspace: need %zu bytes, got %zu", plan.total_bytes, workspace_bytes);
-  KFB_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
-  rc = kfb::upload_plan(&plan, workspace, stream);
-  if (rc) return rc;
-  rc = kfb::launch_syrk(plan, workspace, ctx, alpha, stream);
-  if (rc) return rc;
-  return kfb::launch_finalize(plan, workspace, alpha, stream);
+  return kfb::factor_update_with(jobs, n_jobs, alpha, ctx, workspace, workspace_bytes, "kfb_factor_update",
+                                 (cudaStream_t)stream_);
 }
 
 int kfb_tri_unpack(const kfb_tri_job* jobs, int32_t n_jobs, float scale, void* stream) {

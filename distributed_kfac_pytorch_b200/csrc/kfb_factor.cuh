@@ -75,6 +75,9 @@ KFB_HIDDEN int upload_plan(FactorPlan* plan, void* workspace, cudaStream_t strea
 KFB_HIDDEN int launch_syrk_simt(const FactorPlan& plan, void* workspace, cudaStream_t stream);
 KFB_HIDDEN int launch_syrk(const FactorPlan& plan, void* workspace, Context* ctx, float alpha, cudaStream_t stream);
 constexpr int64_t kFusedMaxRows = 4096;   // jobs with at most this many rows of X are never split along K
+KFB_HIDDEN int factor_update_with(const kfb_factor_job* jobs, int n_jobs, float alpha, Context* ctx, void* workspace,
+                                  size_t workspace_bytes, const char* what, cudaStream_t stream);
+KFB_HIDDEN size_t factor_workspace_bytes(const kfb_factor_job* jobs, int n_jobs, Context* ctx);
 KFB_HIDDEN int launch_finalize(const FactorPlan& plan, void* workspace, float alpha, cudaStream_t stream);
 
 }  // namespace kfb

@@ -55,24 +55,20 @@ int kfb_factor_update_static(const kfb_factor_job* jobs, int32_t n_jobs, float a
   KFB_CUDA(cudaGetDevice(&device));
   KFB_REQUIRE(device == ctx->device, "current device %d is not the device of the kfb context (%d)", device,
               ctx->device);
-  FactorPlan plan;
-  rc = plan_factor(jobs, n_jobs, ctx->num_sms, ctx->umma_ok && mma_mode() == 1, &plan);
-  if (rc) return rc;
-  if (plan.total_bytes > (size_t)KFB_STATIC_SCRATCH_BYTES)
+  const size_t need = factor_workspace_bytes(jobs, n_jobs, ctx);
+  if (need == 0) return KFB_ERR_INVALID;      // the planner has set the message
+  if (need > (size_t)KFB_STATIC_SCRATCH_BYTES)
     KFB_FAIL(KFB_ERR_WORKSPACE,
              "kfb_factor_update_static: these %d job(s) need %zu bytes of scratch but the built-in array holds "
              "%zu; split the call or use kfb_factor_update with a caller workspace",
-             n_jobs, plan.total_bytes, (size_t)KFB_STATIC_SCRATCH_BYTES);
+             n_jobs, need, (size_t)KFB_STATIC_SCRATCH_BYTES);
   void* ws = nullptr;
   rc = static_scratch(device, &ws);   // first call on a device resolves the symbol address
   if (rc) return rc;
-  cudaStream_t stream = (cudaStream_t)stream_;
-  // upload_plan clears the accumulators: whatever the previous call left in the array is gone
-  rc = upload_plan(&plan, ws, stream);
-  if (rc) return rc;
-  rc = launch_syrk(plan, ws, ctx, alpha, stream);
-  if (rc) return rc;
-  return launch_finalize(plan, ws, alpha, stream);
+  // the shared factor-update body clears the accumulators it uses: whatever the previous call left
+  // in the array is gone before anything is accumulated
+  return factor_update_with(jobs, n_jobs, alpha, ctx, ws, (size_t)KFB_STATIC_SCRATCH_BYTES,
+                            "kfb_factor_update_static", (cudaStream_t)stream_);
 }
 
 }  // extern "C"
