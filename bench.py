@@ -40,8 +40,8 @@ KFAC_KW = dict(damping=0.001, factor_decay=0.95, kl_clip=0.001, lr=0.0125,
                distribute_layer_factors=False)
 WORKLOAD = 'resnet50_224_b32_kfac_comm_opt_freq10'
 # DRAM bytes per launch from the committed ncu capture (profiles/r1_tc_kernels_ncu.txt), 1 GPU
-NCU_TRAFFIC = {'resnet50': {'precondition': int((627.075 + 67.804 + 327.166 + 61.839 + 626.493 + 69.178 + 327.435 + 62.111) * 1e6),
-                            'syrk': int(4.645928e9 + 548.241e6)}}
+NCU_TRAFFIC = {'resnet50': {'precondition': int((629.781 + 67.143 + 325.810 + 61.935 + 628.606 + 67.421 + 325.971 + 61.123) * 1e6),
+                            'syrk': int(4.415812e9 + 660.628e6)}}
 
 
 def parse_args():
