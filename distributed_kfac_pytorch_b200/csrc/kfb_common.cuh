@@ -59,6 +59,8 @@ struct Context {
 KFB_HIDDEN Context* current_context();          // context selected by the last kfb_init on this thread
 KFB_HIDDEN int require_context(Context** out);  // KFB_OK or error if kfb_init was never called
 KFB_HIDDEN int mma_mode();                      // 0 SIMT, 1 tcgen05
+KFB_HIDDEN int stage_mode();                    // factor SYRK: 1 (default) im2col operands are read from zero-padded fp32 staging copies; env KFB_SYRK_STAGE=0: in place
+KFB_HIDDEN int tma_mode();                      // factor SYRK: 1 (default) feeds eligible NCHW operands by TMA; env KFB_SYRK_TMA=0: gathers only
 
 static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }

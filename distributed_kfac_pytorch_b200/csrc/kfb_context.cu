@@ -5,6 +5,8 @@
 #include <atomic>
 #include <mutex>
 
+#include <cstdlib>
+
 #include "kfb_common.cuh"
 
 namespace kfb {
@@ -34,6 +36,14 @@ int require_context(Context** out) {
 }
 
 int mma_mode() { return g_mma_mode; }
+int stage_mode() {
+  const char* e = getenv("KFB_SYRK_STAGE");
+  return !(e && e[0] == '0');
+}
+int tma_mode() {
+  const char* e = getenv("KFB_SYRK_TMA");
+  return !(e && e[0] == '0');
+}
 
 static int init_device(int device) {
   KFB_REQUIRE(device >= 0 && device < 64, "device index %d out of range", device);

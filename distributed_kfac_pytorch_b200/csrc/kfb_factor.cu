@@ -297,6 +297,38 @@ __global__ void __launch_bounds__(256) tri_kernel(const __grid_constant__ TriBat
   }
 }
 
+// Staging copies for the tensor-core SYRK (PadJob): every thread writes four consecutive floats of
+// one copy.  HBM-bound: reads the capture once, writes 1.0-1.2x its size.
+__global__ void __launch_bounds__(256) pad_kernel(const PadJob* __restrict__ pads, const int* __restrict__ start, int n_pads) {
+  int lo = 0, hi = n_pads;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (start[mid] <= (int)blockIdx.x) lo = mid; else hi = mid;
+  }
+  const PadJob& p = pads[lo];
+  const int64_t e0 = ((int64_t)(blockIdx.x - start[lo]) * 256 + threadIdx.x) * 4;
+  if (e0 >= p.total) return;
+  const int64_t row = e0 / p.wp;
+  int x = (int)(e0 - row * p.wp);
+  const int64_t plane = row / p.hp;
+  int y = (int)(row - plane * p.hp);
+  int64_t pl = plane;
+  float v[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int sy = y * p.step - p.pad_h, sx = x * p.step - p.pad_w;
+    v[i] = 0.f;
+    if (e0 + i < p.total && sy >= 0 && sy < p.h && sx >= 0 && sx < p.w)
+      v[i] = load_elem(p.src, p.dtype, (pl * p.h + sy) * p.w + sx);
+    if (++x == p.wp) { x = 0; if (++y == p.hp) { y = 0; ++pl; } }
+  }
+  if (e0 + 3 < p.total) {
+    *reinterpret_cast<float4*>(p.dst + e0) = make_float4(v[0], v[1], v[2], v[3]);
+  } else {
+    for (int i = 0; i < 4 && e0 + i < p.total; ++i) p.dst[e0 + i] = v[i];
+  }
+}
+
 int run_tri(const kfb_tri_job* jobs, int n_jobs, float scale, bool unpack, cudaStream_t stream) {
   KFB_REQUIRE(n_jobs >= 0 && (jobs || n_jobs == 0), "bad job array");
   for (int base = 0; base < n_jobs; base += kTriBatch) {
@@ -329,6 +361,9 @@ static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_tc, FactorPlan* plan) {
   KFB_REQUIRE(n_jobs >= 0 && (jobs || n_jobs == 0), "bad job array");
   plan->jobs.clear(); plan->segs.clear(); plan->item_start.clear(); plan->fin_start.clear();
+  plan->tmaps.clear(); plan->tmap_ptr.clear();
+  plan->pads.clear(); plan->seg_pad.clear(); plan->pad_off.clear(); plan->pad_start.clear();
+  plan->stage_floats = 0;
   plan->scratch_floats = 0;
   int items = 0, fins = 0;
   const int target = std::max(1, num_sms) * 4;
@@ -384,7 +419,10 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
       k_total += ds.K;
       KFB_REQUIRE(ds.K < ((int64_t)1 << 31), "segment has %lld rows; at most 2^31-1 are supported", (long long)ds.K);
       if (s.kind == KFB_SEG_ROWS) tc = false;
-      if (s.c * s.h * s.w >= ((int64_t)1 << 26)) tc = false;   // packed row offsets hold 26 bits   // feature-contiguous operands stay on the SIMT path
+      if (s.c * s.h * s.w >= ((int64_t)1 << 26)) tc = false;   // packed row offsets hold 26 bits
+      ds.tma = -1;
+      ds.nb = 0;
+      ds.nomask = 0;
       plan->segs.push_back(ds);
     }
     // split K so that the job alone offers ~4 CTAs per SM, chunks of at least 256 rows
@@ -400,6 +438,54 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
     }
     dj.n_chunks = chunks;
     dj.use_tc = tc ? 1 : 0;
+    for (int si = 0; si < j.n_segments; ++si) {
+      DevSegment& ds = plan->segs[dj.seg_start + si];
+      plan->seg_pad.push_back(-1);
+      if (!tc) continue;
+      bool aligned = ((uintptr_t)ds.data & 15) == 0;
+      if (ds.kind == KFB_SEG_IM2COL && stage_mode()) {
+        // read this capture from an fp32 staging copy instead (see PadJob)
+        PadJob pj;
+        memset(&pj, 0, sizeof(pj));
+        pj.src = ds.data; pj.dtype = ds.dtype; pj.h = ds.h; pj.w = ds.w;
+        const int64_t planes = (ds.K / ((int64_t)ds.oh * ds.ow)) * ds.c;
+        if (ds.kh == 1 && ds.kw == 1) {
+          pj.step = ds.sh; pj.pad_h = ds.ph; pj.pad_w = ds.pw;     // (sh == sw is not required:
+          pj.hp = ds.oh; pj.wp = ds.ow;                            //  see below)
+          if (ds.sh != ds.sw) { pj.step = 0; }
+        } else {
+          pj.step = 1; pj.pad_h = ds.ph; pj.pad_w = ds.pw;
+          pj.hp = (ds.oh - 1) * ds.sh + ds.kh;
+          pj.wp = ((ds.ow - 1) * ds.sw + ds.kw + 3) / 4 * 4;
+        }
+        pj.total = planes * pj.hp * pj.wp;
+        if (pj.step > 0 && (int64_t)ds.c * pj.hp * pj.wp < ((int64_t)1 << 26)) {
+          plan->seg_pad.back() = (int)plan->pads.size();
+          plan->pad_off.push_back(plan->stage_floats);
+          plan->stage_floats += align_up((size_t)pj.total, 64);
+          plan->pads.push_back(pj);
+          ds.dtype = KFB_F32;
+          ds.h = pj.hp; ds.w = pj.wp;
+          ds.ph = ds.pw = 0;
+          if (ds.kh == 1 && ds.kw == 1) {
+            ds.sh = ds.sw = 1;
+            if (!ds.has_bias) ds.kind = KFB_SEG_NCHW;
+          } else {
+            ds.nomask = 1;
+          }
+          aligned = true;       // staging copies start on 256-byte boundaries
+        }
+      }
+      // fp32 NCHW operands whose image rows are 16-byte multiples are fetched by TMA (3-D map
+      // (pixel, channel, image), box 32 x 128 x 1); everything else is gathered by the producer warps
+      const int64_t S = (int64_t)ds.oh * ds.ow;
+      if (tma_mode() && ds.kind == KFB_SEG_NCHW && ds.dtype == KFB_F32 && (S & 3) == 0 && S >= BK && aligned) {
+        ds.nb = (int)ceil_div64(S, BK);
+        ds.tma = (int)plan->tmaps.size();
+        plan->tmaps.emplace_back();
+        plan->tmap_ptr.push_back(nullptr);
+      }
+    }
     // short-K single-segment jobs (the 7x7-map layers: the LARGEST factors) are one work item per
     // block: their SYRK epilogue fuses scale + running average + mirror + triangle export
     dj.fused = (tc && j.n_segments == 1 && k_total <= kFusedMaxRows) ? 1 : 0;
@@ -423,8 +509,19 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
   plan->off_fin = off;    off = align_up(off + plan->fin_start.size() * sizeof(int), 256);
   plan_syrk_tc(plan);
   plan->off_tc_items = off; off = align_up(off + plan->tc_items.size() * sizeof(TcItem), 256);
-  plan->off_scratch = off;
-  plan->total_bytes = off + plan->scratch_floats * sizeof(float);
+  plan->off_tmaps = off;    off = align_up(off + plan->tmaps.size() * sizeof(CUtensorMap), 256);
+  // staging copies: blocks of 256 threads x 4 floats
+  int pad_blocks = 0;
+  for (const PadJob& pj : plan->pads) {
+    plan->pad_start.push_back(pad_blocks);
+    pad_blocks += (int)ceil_div64(pj.total, 1024);
+  }
+  plan->pad_start.push_back(pad_blocks);
+  plan->off_pads = off;      off = align_up(off + plan->pads.size() * sizeof(PadJob), 256);
+  plan->off_pad_start = off; off = align_up(off + plan->pad_start.size() * sizeof(int), 256);
+  plan->off_scratch = off;   off = align_up(off + plan->scratch_floats * sizeof(float), 256);
+  plan->off_stage = off;
+  plan->total_bytes = off + plan->stage_floats * sizeof(float);
   return KFB_OK;
 }
 
@@ -440,14 +537,15 @@ std::vector<int64_t> g_plan_sig;
 
 void signature(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool tc, std::vector<int64_t>* sig) {
   sig->clear();
-  sig->push_back(n_jobs); sig->push_back(num_sms); sig->push_back(tc);
+  sig->push_back(n_jobs); sig->push_back(num_sms); sig->push_back(tc); sig->push_back(tma_mode());
   for (int i = 0; i < n_jobs; ++i) {
     const kfb_factor_job& j = jobs[i];
     sig->push_back(j.d); sig->push_back(j.n_segments); sig->push_back(j.ld_state);
     if (!j.segments) continue;
     for (int k = 0; k < j.n_segments; ++k) {
       const kfb_segment& s = j.segments[k];
-      const int64_t v[] = {s.kind, s.has_bias, s.n, s.c, s.h, s.w, s.kh, s.kw, s.sh, s.sw, s.ph, s.pw, s.ld, s.dtype};
+      const int64_t v[] = {s.kind, s.has_bias, s.n, s.c, s.h, s.w, s.kh, s.kw, s.sh, s.sw, s.ph, s.pw, s.ld, s.dtype,
+                           (int64_t)((uintptr_t)s.data & 15)};   // alignment decides TMA eligibility
       sig->insert(sig->end(), v, v + sizeof(v) / sizeof(v[0]));
     }
   }
@@ -474,7 +572,9 @@ static int cached_plan(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool
       for (int k = 0; k < j.n_segments; ++k) {
         KFB_REQUIRE(j.segments[k].data, "factor job %d segment %d: null data", i, k);
         DevSegment& ds = g_plan.segs[dj.seg_start + k];
-        ds.data = j.segments[k].data;
+        const int pad = g_plan.seg_pad[dj.seg_start + k];
+        if (pad >= 0) g_plan.pads[pad].src = j.segments[k].data;   // ds.data is the staging copy
+        else ds.data = j.segments[k].data;
         ds.weight = j.segments[k].weight;
       }
     }
@@ -493,7 +593,12 @@ int factor_update_with(const kfb_factor_job* jobs, int n_jobs, float alpha, Cont
     KFB_FAIL(KFB_ERR_WORKSPACE, "%s: these %d job(s) need %zu bytes of scratch but %zu are available", what, n_jobs,
              plan->total_bytes, workspace_bytes);
   KFB_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+  bind_workspace(plan, workspace);
+  rc = refresh_tmaps(plan, ctx);
+  if (rc) return rc;
   rc = upload_plan(plan, workspace, stream);
+  if (rc) return rc;
+  rc = launch_pad(*plan, workspace, stream);
   if (rc) return rc;
   rc = launch_syrk(*plan, workspace, ctx, alpha, stream);
   if (rc) return rc;
@@ -508,16 +613,35 @@ size_t factor_workspace_bytes(const kfb_factor_job* jobs, int n_jobs, Context* c
   return plan->total_bytes;
 }
 
-int upload_plan(FactorPlan* plan, void* workspace, cudaStream_t stream) {
+// Point the plan's scratch accumulators and staging copies into this call's workspace.
+void bind_workspace(FactorPlan* plan, void* workspace) {
   char* ws = (char*)workspace;
   float* scratch = (float*)(ws + plan->off_scratch);
   for (auto& j : plan->jobs) j.scratch = scratch + j.scratch_off;
+  float* stage = (float*)(ws + plan->off_stage);
+  for (size_t i = 0; i < plan->segs.size(); ++i) {
+    const int pad = plan->seg_pad[i];
+    if (pad < 0) continue;
+    plan->pads[pad].dst = stage + plan->pad_off[pad];
+    plan->segs[i].data = plan->pads[pad].dst;
+  }
+}
+
+int upload_plan(FactorPlan* plan, void* workspace, cudaStream_t stream) {
+  char* ws = (char*)workspace;
+  float* scratch = (float*)(ws + plan->off_scratch);
+  if (!plan->pads.empty()) {
+    KFB_CUDA(cudaMemcpyAsync(ws + plan->off_pads, plan->pads.data(), plan->pads.size() * sizeof(PadJob), cudaMemcpyHostToDevice, stream));
+    KFB_CUDA(cudaMemcpyAsync(ws + plan->off_pad_start, plan->pad_start.data(), plan->pad_start.size() * sizeof(int), cudaMemcpyHostToDevice, stream));
+  }
   KFB_CUDA(cudaMemcpyAsync(ws + plan->off_jobs, plan->jobs.data(), plan->jobs.size() * sizeof(DevJob), cudaMemcpyHostToDevice, stream));
   KFB_CUDA(cudaMemcpyAsync(ws + plan->off_segs, plan->segs.data(), plan->segs.size() * sizeof(DevSegment), cudaMemcpyHostToDevice, stream));
   KFB_CUDA(cudaMemcpyAsync(ws + plan->off_items, plan->item_start.data(), plan->item_start.size() * sizeof(int), cudaMemcpyHostToDevice, stream));
   KFB_CUDA(cudaMemcpyAsync(ws + plan->off_fin, plan->fin_start.data(), plan->fin_start.size() * sizeof(int), cudaMemcpyHostToDevice, stream));
   if (!plan->tc_items.empty())
     KFB_CUDA(cudaMemcpyAsync(ws + plan->off_tc_items, plan->tc_items.data(), plan->tc_items.size() * sizeof(TcItem), cudaMemcpyHostToDevice, stream));
+  if (!plan->tmaps.empty())
+    KFB_CUDA(cudaMemcpyAsync(ws + plan->off_tmaps, plan->tmaps.data(), plan->tmaps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice, stream));
   KFB_CUDA(cudaMemsetAsync(scratch, 0, plan->scratch_floats * sizeof(float), stream));
   return KFB_OK;
 }
@@ -529,6 +653,15 @@ int launch_syrk_simt(const FactorPlan& plan, void* workspace, cudaStream_t strea
                                                    (const DevSegment*)(ws + plan.off_segs),
                                                    (const int*)(ws + plan.off_items),
                                                    (int)plan.jobs.size());
+  KFB_CHECK_LAUNCH();
+  return KFB_OK;
+}
+
+int launch_pad(const FactorPlan& plan, void* workspace, cudaStream_t stream) {
+  if (plan.pads.empty() || plan.pad_start.back() == 0) return KFB_OK;
+  char* ws = (char*)workspace;
+  pad_kernel<<<plan.pad_start.back(), 256, 0, stream>>>((const PadJob*)(ws + plan.off_pads),
+                                                       (const int*)(ws + plan.off_pad_start), (int)plan.pads.size());
   KFB_CHECK_LAUNCH();
   return KFB_OK;
 }

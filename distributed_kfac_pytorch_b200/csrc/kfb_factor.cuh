@@ -2,6 +2,7 @@
 #pragma once
 #include <vector>
 
+#include <cuda.h>        // CUtensorMap (type only)
 #include <cuda_fp16.h>
 
 #include "kfb_common.cuh"
@@ -22,6 +23,9 @@ struct DevSegment {
   int n_chunks;          // split-K chunks of this segment
   int chunk_start;       // first chunk index inside the job
   int64_t chunk_len;
+  int nomask;            // IM2COL read from a zero-padded staging copy: every tap of every X row is in range
+  int tma;               // index of this segment's TMA descriptor, -1: gathered by the producer warps
+  int nb;                // TMA segments: 32-row blocks per image (the last one zero-filled past oh*ow)
 };
 
 struct DevJob {
@@ -51,11 +55,26 @@ __device__ __forceinline__ float load_elem(const void* base, int dtype, int64_t 
   return widen16(__ldg(reinterpret_cast<const unsigned short*>(base) + idx), dtype);
 }
 
+// Staging copy of one im2col capture for the tensor-core SYRK (fp32, whatever the capture's type):
+//   dst[plane][y][x] = src[plane][y*step - pad_h][x*step - pad_w]   (0 outside the source image)
+// step = 1: the zero-padded image, so that the gather needs no border tests (row pitch wp is a
+// multiple of 4 floats); step = conv stride for 1x1 strided convs: the dense sub-sampled image,
+// which then is an ordinary NCHW operand.
+struct PadJob {
+  const void* src;
+  float* dst;
+  int dtype;
+  int h, w;              // source image
+  int hp, wp;            // staged image (wp = row pitch)
+  int step, pad_h, pad_w;
+  int64_t total;         // planes * hp * wp
+};
+
 struct TcItem {            // one unit of tensor-core SYRK work: a 2x2 block of 128-wide tiles
   int job, seg;
   int a0, b0;              // first row tile / first column tile (a0 <= b0; equal on the diagonal)
   int mi, nj;              // tiles in the block's rows / columns (1 or 2)
-  uint32_t k_begin, k_end; // rows of X
+  uint32_t k_begin, k_end; // rows of X (TMA segments: rows of the per-image padded matrix, nb*32 per image)
 };
 
 struct FactorPlan {
@@ -64,6 +83,14 @@ struct FactorPlan {
   std::vector<DevJob> jobs;
   std::vector<DevSegment> segs;
   std::vector<int> item_start, fin_start;
+  std::vector<PadJob> pads;              // staging copies, one per staged segment
+  std::vector<int> seg_pad;              // per segment: index into pads or -1
+  std::vector<size_t> pad_off;           // float offset of each copy inside the staging region
+  std::vector<int> pad_start;            // first block of each PadJob (+ total)
+  size_t stage_floats = 0, off_stage = 0, off_pads = 0, off_pad_start = 0;
+  std::vector<CUtensorMap> tmaps;        // one per TMA-fed segment
+  std::vector<const void*> tmap_ptr;     // the address each descriptor was encoded for
+  size_t off_tmaps = 0;
   int n_items = 0, n_fin = 0;
   size_t scratch_floats = 0;
   size_t off_jobs = 0, off_segs = 0, off_items = 0, off_fin = 0, off_scratch = 0, total_bytes = 0;
@@ -72,6 +99,9 @@ struct FactorPlan {
 KFB_HIDDEN int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_tc, FactorPlan* plan);
 KFB_HIDDEN void plan_syrk_tc(FactorPlan* plan);
 KFB_HIDDEN int upload_plan(FactorPlan* plan, void* workspace, cudaStream_t stream);
+KFB_HIDDEN int refresh_tmaps(FactorPlan* plan, Context* ctx);
+KFB_HIDDEN void bind_workspace(FactorPlan* plan, void* workspace);
+KFB_HIDDEN int launch_pad(const FactorPlan& plan, void* workspace, cudaStream_t stream);
 KFB_HIDDEN int launch_syrk_simt(const FactorPlan& plan, void* workspace, cudaStream_t stream);
 KFB_HIDDEN int launch_syrk(const FactorPlan& plan, void* workspace, Context* ctx, float alpha, cudaStream_t stream);
 constexpr int64_t kFusedMaxRows = 4096;   // jobs with at most this many rows of X are never split along K

@@ -11,8 +11,16 @@
 //   warps 5-20  producers: gather X^T tiles (128 features x 32 rows of X, K-major) from global
 //               memory straight into the 128B-swizzled UMMA shared-memory layout
 //               - NCHW operands with 16-byte alignable rows: 128-bit loads/stores
-//               - im2col operands: one 32-bit load per element with a per-lane validity bitmask
-//                 over (ky,kx) (padding / image border), coalesced along the output row
+//               - im2col operands: read from a zero-padded fp32 staging copy (kfb_factor.cu, PadJob),
+//                 one 4-byte cp.async per element, coalesced along the output row; the copies of a
+//                 whole stage are in flight per lane and report to the stage's mbarrier themselves
+//                 (cp.async.mbarrier.arrive), so the producers never wait for data
+//               - the same from the capture in place (KFB_SYRK_STAGE=0, NCHW operands with odd row
+//                 lengths): cp.async with zero fill under a per-lane validity bitmask over (ky,kx)
+//               - fp32 NCHW operands with 16-byte image rows and >= 32 pixels per image skip the
+//                 gather: one producer lane issues a TMA box (32 pixels x 128 channels x 1 image,
+//                 SWIZZLE_128B) per tile and stage; K runs over per-image 32-row blocks, the tail
+//                 of an image's last block is zero-filled by the TMA unit
 // Operands stay fp32 in shared memory; kind::tf32 reads the top 19 bits, so no conversion pass.
 #include <algorithm>
 #include <type_traits>
@@ -84,13 +92,28 @@ __device__ __forceinline__ void sts_v4(uint32_t addr, float4 v) {
   asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
+// Asynchronous 4-byte global -> shared copies (LDGSTS): no register staging, so a lane keeps a whole
+// stage (32 elements) in flight instead of waiting for every batch of loads before it may store.
+// src_bytes = 0 writes a zero without touching global memory (borders, padding rows, K tails).
+__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async4_zfill(uint32_t dst, const void* src, uint32_t src_bytes) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+// this thread's arrival on `bar` happens when all of its earlier cp.async copies have landed
+__device__ __forceinline__ void cp_async_arrive(uint64_t* bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(umma::smem_u32(bar)) : "memory");
+}
+
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
 __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __restrict__ jobs,
                                                             const DevSegment* __restrict__ segs,
-                                                            const TcItem* __restrict__ items, int n_items, float alpha) {
+                                                            const TcItem* __restrict__ items, int n_items, float alpha,
+                                                            const CUtensorMap* __restrict__ tmaps) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint64_t* full = (uint64_t*)(smem + kStages * kStageBytes);
@@ -102,7 +125,7 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kStages; ++s) { umma::mbar_init(&full[s], kProducerWarps); umma::mbar_init(&empty[s], 1); }
+    for (int s = 0; s < kStages; ++s) { umma::mbar_init(&full[s], kProducerWarps * 32); umma::mbar_init(&empty[s], 1); }
     umma::mbar_init(tfull, 1);
     umma::mbar_init(tempty, 128);
     umma::fence_barrier_init();
@@ -140,6 +163,33 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
       const int S = s.oh * s.ow;
       const uint32_t uS = (uint32_t)S, uow = (uint32_t)s.ow;
       const uint32_t k_end32 = item.k_end;       // K < 2^31 (checked on the host)
+      if (s.tma >= 0) {
+        // ---- TMA-fed operand: k counts rows of the per-image padded matrix (nb blocks of 32)
+        const CUtensorMap* tm = tmaps + s.tma;
+        const bool issuer = pw == 0 && lane == 0;
+        // the descriptor was written by a host copy into memory that held other descriptors before
+        if (issuer) umma::fence_tensormap_acquire(tm);
+        const uint32_t unb = (uint32_t)s.nb;
+        uint32_t b = item.k_begin / BK;
+        uint32_t n = b / unb, sb = b - n * unb;
+        for (uint32_t k0 = item.k_begin; k0 < k_end32; k0 += BK) {
+          umma::mbar_wait(&empty[stage], phase ^ 1);
+          if (issuer) {
+            umma::mbar_arrive_expect_tx(&full[stage], (uint32_t)(n_slots * kTileBytes));
+            uint8_t* st = smem + stage * kStageBytes;
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+              if (t < n_slots)
+                umma::tma_load_3d(st + slot_of[t] * kTileBytes, tm, &full[stage], (int)(sb * BK), tile_of[t] * TM, (int)n);
+          } else {
+            umma::mbar_arrive(&full[stage]);
+          }
+          __syncwarp();
+          if (++sb == unb) { sb = 0; ++n; }
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+        continue;
+      }
       const bool vec4 = s.kind == KFB_SEG_NCHW && (S & 3) == 0 &&
                         (((uintptr_t)s.data) & (s.dtype == KFB_F32 ? 15u : 7u)) == 0;
       const bool wide = s.kind == KFB_SEG_IM2COL && s.kh * s.kw > 30;
@@ -201,8 +251,65 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
                   sts_v4(st + slot_of[t] * kTileBytes + r * 128 + ((vec_kq ^ (r & 7)) << 4), v[t][i]);
                 }
             umma::fence_proxy_async_smem();
-            __syncwarp();
-            if (lane == 0) umma::mbar_arrive(&full[stage]);
+            umma::mbar_arrive(&full[stage]);
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
+          }
+        } else if (esh == 2 && s.nomask) {
+          // ---- im2col from the zero-padded staging copy: every tap of every X row is in range, so a
+          // tile row is just (lane's window origin) + (row's byte offset).  Word = byte offset | 1 if
+          // the feature does not exist (>= d, or the bias feature, written separately below).
+          uint32_t off[4][kRowsPerWarp];
+          bool pair_clean[2] = {true, true};
+  #pragma unroll
+          for (int t = 0; t < 4; ++t) {
+  #pragma unroll
+            for (int j = 0; j < kRowsPerWarp; ++j) {
+              const uint32_t inf = t < n_slots ? row_info(s, d, tile_of[t] * TM + pw + kProducerWarps * j) : kBitNever;
+              off[t][j] = (inf & 63u) == kBitNever ? 1u : ((inf >> 6) << 2);
+            }
+            if (t < n_slots && (tile_of[t] + 1) * TM > d - s.has_bias) pair_clean[t >> 1] = false;
+          }
+          const int64_t img = (int64_t)s.c * s.h * s.w;
+          for (uint32_t k0 = item.k_begin; k0 < k_end32; k0 += BK) {
+            umma::mbar_wait(&empty[stage], phase ^ 1);
+            const uint32_t st = smem_base + stage * kStageBytes + pw * 128 + lane_off;
+            const uint32_t k = k0 + lane;
+            const bool kin = k < k_end32;
+            const bool full_stage = k0 + BK <= k_end32;
+            const uint32_t n = k / uS;
+            const uint32_t r = k - n * uS;
+            const uint32_t oy = r / uow, ox = r - oy * uow;
+            // lanes past the end of the item read image 0's window (in range) and are zeroed below
+            const char* src = reinterpret_cast<const char*>(s.data) +
+                              ((kin ? (int64_t)n * img : 0) + (int64_t)(oy * s.sh) * s.w + ox * s.sw) * 4;
+  #pragma unroll
+            for (int tp = 0; tp < 2; ++tp) {
+              if (2 * tp >= n_slots) break;
+              if (full_stage && pair_clean[tp]) {
+  #pragma unroll
+                for (int u = 0; u < 2; ++u)
+  #pragma unroll
+                  for (int j = 0; j < kRowsPerWarp; ++j)
+                    if (2 * tp + u < n_slots)
+                      cp_async4(st + slot_of[2 * tp + u] * kTileBytes + j * (kProducerWarps * 128), src + off[2 * tp + u][j]);
+              } else {
+  #pragma unroll
+                for (int u = 0; u < 2; ++u)
+  #pragma unroll
+                  for (int j = 0; j < kRowsPerWarp; ++j)
+                    if (2 * tp + u < n_slots) {
+                      const uint32_t o = off[2 * tp + u][j];
+                      cp_async4_zfill(st + slot_of[2 * tp + u] * kTileBytes + j * (kProducerWarps * 128), src + (o & ~3u),
+                                      (kin && !(o & 1u)) ? 4u : 0u);
+                    }
+              }
+            }
+            if (bias_slot >= 0) {
+              sts_f32(smem_base + stage * kStageBytes + bias_slot * kTileBytes + bias_row * 128 + lane_off,
+                      kin ? 1.f : 0.f);
+              umma::fence_proxy_async_smem();
+            }
+            cp_async_arrive(&full[stage]);
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
         } else {
@@ -242,38 +349,47 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
             // narrow: (ky,kx) bits in mlo; "always" moves to bit 30 so one word decides everything
             // (row_info's 6-bit field: 62 & 31 = 30, 63 & 31 = 31 which is never set)
             const uint32_t mnarrow = mlo | ((mhi >> (kBitAlways - 32)) << 30);
-            // two tiles (16 independent loads per lane) in flight at a time
+            if (esh == 2) {
+              // fp32: asynchronous copies, zero-filled where the mask says the tap is outside the image
   #pragma unroll
-            for (int tp = 0; tp < 2; ++tp) {
-              if (2 * tp >= n_slots) break;
-              float v[2][kRowsPerWarp];
-  #pragma unroll
-              for (int u = 0; u < 2; ++u)
-  #pragma unroll
-                for (int j = 0; j < kRowsPerWarp; ++j) {
-                  const uint32_t inf = info[2 * tp + u][j];
-                  const bool ok = wide ? row_valid<true>(inf, mlo, mhi) : row_valid<false>(inf, mnarrow, 0u);
-                  v[u][j] = 0.f;
-                  if (ok) {
-                    const char* p = src + ((uint64_t)(inf >> 6) << esh);
-                    v[u][j] = esh == 2 ? __ldg(reinterpret_cast<const float*>(p))
-                                       : widen16(__ldg(reinterpret_cast<const unsigned short*>(p)), s.dtype);
-                  }
-                }
-  #pragma unroll
-              for (int u = 0; u < 2; ++u)
+              for (int t = 0; t < 4; ++t)
   #pragma unroll
                 for (int j = 0; j < kRowsPerWarp; ++j)
-                  if (2 * tp + u < n_slots)
-                    sts_f32(st + slot_of[2 * tp + u] * kTileBytes + j * (kProducerWarps * 128), v[u][j]);
+                  if (t < n_slots) {
+                    const uint32_t inf = info[t][j];
+                    const bool ok = wide ? row_valid<true>(inf, mlo, mhi) : row_valid<false>(inf, mnarrow, 0u);
+                    cp_async4_zfill(st + slot_of[t] * kTileBytes + j * (kProducerWarps * 128), src + ((uint64_t)(inf >> 6) << 2),
+                                    ok ? 4u : 0u);
+                  }
+            } else {
+              // 16-bit captures are widened in registers: two tiles (16 loads per lane) in flight at a time
+  #pragma unroll
+              for (int tp = 0; tp < 2; ++tp) {
+                if (2 * tp >= n_slots) break;
+                float v[2][kRowsPerWarp];
+  #pragma unroll
+                for (int u = 0; u < 2; ++u)
+  #pragma unroll
+                  for (int j = 0; j < kRowsPerWarp; ++j) {
+                    const uint32_t inf = info[2 * tp + u][j];
+                    const bool ok = wide ? row_valid<true>(inf, mlo, mhi) : row_valid<false>(inf, mnarrow, 0u);
+                    v[u][j] = 0.f;
+                    if (ok) v[u][j] = widen16(__ldg(reinterpret_cast<const unsigned short*>(src + ((uint64_t)(inf >> 6) << 1))), s.dtype);
+                  }
+  #pragma unroll
+                for (int u = 0; u < 2; ++u)
+  #pragma unroll
+                  for (int j = 0; j < kRowsPerWarp; ++j)
+                    if (2 * tp + u < n_slots)
+                      sts_f32(st + slot_of[2 * tp + u] * kTileBytes + j * (kProducerWarps * 128), v[u][j]);
+              }
             }
             // the bias feature is the constant 1 wherever the X row exists
             if (bias_slot >= 0)
               sts_f32(smem_base + stage * kStageBytes + bias_slot * kTileBytes + bias_row * 128 + lane_off,
                       kin ? 1.f : 0.f);
-            umma::fence_proxy_async_smem();
-            __syncwarp();
-            if (lane == 0) umma::mbar_arrive(&full[stage]);
+            if (esh != 2 || bias_slot >= 0) umma::fence_proxy_async_smem();
+            cp_async_arrive(&full[stage]);       // with no copies in flight this is an immediate arrival
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
         }
@@ -435,16 +551,18 @@ void plan_syrk_tc(FactorPlan* plan) {
     const int TB = ceil_div(T, 2);            // 256-wide blocks per side
     for (int si = 0; si < j.n_segments; ++si) {
       const DevSegment& s = plan->segs[j.seg_start + si];
-      const int64_t nch = j.fused ? 1 : std::max<int64_t>(1, ceil_div64(s.K, kChunk));
-      const int64_t len = ceil_div64(ceil_div64(s.K, nch), BK) * BK;
-      for (int64_t k = 0; k < s.K; k += len)
+      // TMA segments iterate the per-image padded matrix: nb blocks of 32 rows per image
+      const int64_t K = s.tma >= 0 ? (s.K / ((int64_t)s.oh * s.ow)) * s.nb * BK : s.K;
+      const int64_t nch = j.fused ? 1 : std::max<int64_t>(1, ceil_div64(K, kChunk));
+      const int64_t len = ceil_div64(ceil_div64(K, nch), BK) * BK;
+      for (int64_t k = 0; k < K; k += len)
         for (int bi = 0; bi < TB; ++bi)
           for (int bj = bi; bj < TB; ++bj) {
             TcItem it;
             it.job = (int)ji; it.seg = j.seg_start + si;
             it.a0 = 2 * bi; it.b0 = 2 * bj;
             it.mi = std::min(2, T - it.a0); it.nj = std::min(2, T - it.b0);
-            it.k_begin = (uint32_t)k; it.k_end = (uint32_t)std::min<int64_t>(s.K, k + len);
+            it.k_begin = (uint32_t)k; it.k_end = (uint32_t)std::min<int64_t>(K, k + len);
             plan->tc_items.push_back(it);
           }
     }
@@ -469,8 +587,36 @@ int launch_syrk_tc(const FactorPlan& plan, void* workspace, Context* ctx, float 
   const int grid = std::min(n, ctx->num_sms);
   syrk_tc_kernel<<<grid, kThreads, kSmemBytes, stream>>>((const DevJob*)(ws + plan.off_jobs),
                                                        (const DevSegment*)(ws + plan.off_segs),
-                                                       (const TcItem*)(ws + plan.off_tc_items), n, alpha);
+                                                       (const TcItem*)(ws + plan.off_tc_items), n, alpha,
+                                                       (const CUtensorMap*)(ws + plan.off_tmaps));
   KFB_CHECK_LAUNCH();
+  return KFB_OK;
+}
+
+// (Re-)encode the TMA descriptors of the segments whose capture moved since the last call:
+// 3-D map (pixel, channel, image) over the NCHW tensor, box 32 x 128 x 1, 128-byte swizzle - the
+// same shared-memory image the gathering producers write.
+int refresh_tmaps(FactorPlan* plan, Context* ctx) {
+  typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  for (const DevSegment& s : plan->segs) {
+    if (s.tma < 0 || plan->tmap_ptr[s.tma] == s.data) continue;
+    KFB_REQUIRE(ctx->encode_tiled, "TMA descriptor encoder is not available");
+    const int64_t S = (int64_t)s.oh * s.ow, N = s.K / S;
+    cuuint64_t dims[3] = {(cuuint64_t)S, (cuuint64_t)s.c, (cuuint64_t)N};
+    cuuint64_t strides[2] = {(cuuint64_t)S * sizeof(float), (cuuint64_t)S * s.c * sizeof(float)};
+    cuuint32_t box[3] = {(cuuint32_t)BK, (cuuint32_t)TM, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = ((EncodeTiledFn)ctx->encode_tiled)(&plan->tmaps[s.tma], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)s.data,
+                                                    dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+      KFB_FAIL(KFB_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) for an NCHW capture %p [%lld, %d, %lld]", (int)r, s.data,
+               (long long)N, s.c, (long long)S);
+    plan->tmap_ptr[s.tma] = s.data;
+  }
   return KFB_OK;
 }
 

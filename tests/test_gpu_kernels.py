@@ -82,6 +82,10 @@ CONV_CASES = [
     (3, 8, 10, 12, (3, 5), (2, 1), (0, 2), True),      # asymmetric everything
     (1, 1, 3, 3, (3, 3), (1, 1), (0, 0), False),       # single output pixel, K = 1
     (2, 70, 14, 14, (3, 3), (1, 1), (1, 1), False),    # d = 630 > several tiles
+    (9, 128, 28, 28, (3, 3), (1, 1), (1, 1), False),   # d = 1152: whole tiles only, K chunks
+    (33, 64, 14, 14, (3, 3), (2, 2), (1, 1), True),    # d = 577: bias in a tile of its own
+    (20, 256, 16, 16, (1, 1), (2, 2), (0, 0), False),  # sub-sampled 1x1 -> TMA-fed NCHW copy
+    (3, 64, 12, 12, (1, 1), (2, 2), (0, 0), True),     # sub-sampled 1x1 with bias
 ]
 
 
@@ -99,7 +103,8 @@ def test_conv_A_factor(ops, case):
     assert_factor_close(state, direct)
 
 
-@pytest.mark.parametrize('shape', [(4, 6, 5, 5), (32, 64, 7, 7), (3, 130, 14, 14), (2, 16, 56, 56), (1, 3, 1, 1)])
+@pytest.mark.parametrize('shape', [(4, 6, 5, 5), (32, 64, 7, 7), (3, 130, 14, 14), (2, 16, 56, 56), (1, 3, 1, 1),
+                                   (5, 300, 6, 6), (40, 70, 8, 8), (24, 260, 14, 14)])
 def test_conv_G_factor_nchw(ops, shape):
     n, c, h, w = shape
     g = torch.randn(*shape, generator=torch.Generator().manual_seed(7))
@@ -108,6 +113,67 @@ def test_conv_G_factor_nchw(ops, shape):
     state, tri, ref = run_both(ops, c, [seg])
     assert_factor_close(state, ref)
     assert_factor_close(state, O.factor_ema(O.conv2d_G([g]), None, 0.95))
+
+
+@pytest.mark.parametrize('case', [c for c in CONV_CASES if c[0] * c[1] >= 15], ids=lambda c: 'x'.join(map(str, c[:4])) + '_k%d' % c[4][0])
+def test_conv_A_staged_and_in_place_agree(monkeypatch, case):
+    """The tensor-core SYRK reads im2col operands from zero-padded fp32 staging copies (1x1 strided
+    convs: dense sub-sampled copies); KFB_SYRK_STAGE=0 gathers from the capture in place with border
+    masks.  Same products, so the two agree far inside the oracle tolerance - for fp32 and 16-bit
+    captures."""
+    N.set_ops(None)
+    o = N.get_ops()
+    o._enter(torch.zeros(1, device=DEV))
+    o.set_mma_mode(1)
+    n, c, h, w, k, s, p, bias = case
+    for dtype in (torch.float32, torch.bfloat16):
+        x = torch.randn(n, c, h, w, generator=torch.Generator().manual_seed(5)).to(dtype)
+        ref = O.factor_ema(O.conv2d_A([x.float()], k, s, p, bias), None, 0.95)
+        out = []
+        for env in ('1', '0'):
+            monkeypatch.setenv('KFB_SYRK_STAGE', env)
+            d, segs = conv_segments(x, k, s, p, bias)
+            buf, state = alloc2d(d, d, DEV)
+            o.factor_update([N.FactorJob(d, segs, state, True, True, None)], 0.95)
+            torch.cuda.synchronize()
+            assert_factor_close(state, ref)
+            out.append(state.clone())
+        assert_factor_close(out[0], out[1], tol=1e-5)
+
+
+def test_nchw_tma_and_gather_paths_agree(monkeypatch):
+    """fp32 NCHW operands with 16-byte image rows are fetched by TMA (per-image 32-row blocks, tail
+    zero-filled); KFB_SYRK_TMA=0 and a capture that is not 16-byte aligned use the gathering
+    producers.  All three must give the oracle's factor, across chunked and two-segment jobs."""
+    N.set_ops(None)
+    o = N.get_ops()
+    o._enter(torch.zeros(1, device=DEV))
+    o.set_mma_mode(1)
+    gen = torch.Generator().manual_seed(21)
+    for n, c, h, w in [(24, 260, 14, 14), (3, 129, 6, 6), (7, 128, 28, 28)]:
+        S = h * w
+        g1 = torch.randn(n, c, h, w, generator=gen)
+        g2 = torch.randn(n + 1, c, h, w, generator=gen)
+        ref = O.factor_ema(O.conv2d_G([g1, g2]), None, 0.95)
+        flat = torch.empty(g1.numel() + 1, device=DEV)          # misaligned copy: base + 4 bytes
+        flat[1:].copy_(g1.reshape(-1))
+        g1_off = flat[1:].view(n, c, h, w)
+        assert g1_off.data_ptr() % 16 == 4
+        results = []
+        for env, first in (('1', g1.to(DEV)), ('0', g1.to(DEV)), ('1', g1_off)):
+            monkeypatch.setenv('KFB_SYRK_TMA', env)
+            wgt = 1.0 / (S * S * (2 * n + 1) * S)           # rows of both calls are averaged together
+            segs = [N.Segment(N.KFB_SEG_NCHW, first, n, c, wgt, h=h, w=w),
+                    N.Segment(N.KFB_SEG_NCHW, g2.to(DEV), n + 1, c, wgt, h=h, w=w)]
+            buf, state = alloc2d(c, c, DEV)
+            o.factor_update([N.FactorJob(c, segs, state, True, True, None)], 0.95)
+            torch.cuda.synchronize()
+            assert_factor_close(state, ref)
+            results.append(state.clone())
+        # same TF32 products, same fp32 accumulation order inside a tile: only the reduction order
+        # of the K chunks (atomics) differs
+        assert_factor_close(results[0], results[1], tol=1e-5)
+        assert_factor_close(results[0], results[2], tol=1e-5)
 
 
 @pytest.mark.parametrize('rows,feat,bias', [(32, 2048, True), (20, 13, True), (7, 100, False), (1, 5, True),
