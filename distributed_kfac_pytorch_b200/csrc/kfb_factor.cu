@@ -358,6 +358,18 @@ int run_tri(const kfb_tri_job* jobs, int n_jobs, float scale, bool unpack, cudaS
 // ============================================================================================
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// Division by an invariant divisor d (1 <= d < 2^31) of any x < 2^31 as a multiply-high and a shift:
+// p = 31 + ceil(log2 d), m = floor(2^p / d) + 1 gives floor(x*m / 2^p) = floor(x / d) because
+// m*d - 2^p <= d <= 2^(p-31).  d = 1 is flagged by m = 0.
+static void magic_div(int64_t d, uint32_t* mul, uint32_t* shift) {
+  if (d <= 1) { *mul = 0; *shift = 0; return; }
+  int l = 0;
+  while (((int64_t)1 << l) < d) ++l;
+  const int p = 31 + l;
+  *mul = (uint32_t)(((unsigned __int128)1 << p) / (unsigned __int128)d + 1);
+  *shift = (uint32_t)(p - 32);
+}
+
 int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_tc, FactorPlan* plan) {
   KFB_REQUIRE(n_jobs >= 0 && (jobs || n_jobs == 0), "bad job array");
   plan->jobs.clear(); plan->segs.clear(); plan->item_start.clear(); plan->fin_start.clear();
@@ -423,6 +435,8 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
       ds.tma = -1;
       ds.nb = 0;
       ds.nomask = 0;
+      magic_div((int64_t)ds.oh * ds.ow, &ds.mul_s, &ds.sh_s);
+      magic_div(ds.ow, &ds.mul_w, &ds.sh_w);
       plan->segs.push_back(ds);
     }
     // split K so that the job alone offers ~4 CTAs per SM, chunks of at least 256 rows

@@ -23,6 +23,8 @@ struct DevSegment {
   int n_chunks;          // split-K chunks of this segment
   int chunk_start;       // first chunk index inside the job
   int64_t chunk_len;
+  uint32_t mul_s, sh_s;  // x / (oh*ow) = umulhi(x, mul_s) >> sh_s for x < 2^31 (mul_s = 0: divisor 1)
+  uint32_t mul_w, sh_w;  // x / ow likewise
   int nomask;            // IM2COL read from a zero-padded staging copy: every tap of every X row is in range
   int tma;               // index of this segment's TMA descriptor, -1: gathered by the producer warps
   int nb;                // TMA segments: 32-row blocks per image (the last one zero-filled past oh*ow)

@@ -5,10 +5,12 @@
 // tile products instead of 2 tiles per product) and the shared-memory traffic per MMA.
 //
 //   warps 0-3   epilogue: tcgen05.ld -> x weight -> red.global.add.v4.f32 into the job's scratch
-//   warp  4     MMA issuer: tcgen05.mma.kind::tf32, M=128, N=256 (or 128), K=8; the block's four
-//               fp32 accumulators fill all 512 TMEM columns; a diagonal block loads its two
-//               tiles once for both operands and skips the lower-left product
-//   warps 5-20  producers: gather X^T tiles (128 features x 32 rows of X, K-major) from global
+//   warp  0     lane 0 is also the MMA issuer: tcgen05.mma.kind::tf32, M=128, N=256 (or 128), K=8;
+//               the block's four fp32 accumulators fill all 512 TMEM columns, so issuing and
+//               draining alternate anyway; a diagonal block loads its two tiles once for both
+//               operands and skips the lower-left product.  (20 warps = 5 per scheduler leave 96
+//               registers per thread; a 21st warp would cap every thread at 80.)
+//   warps 4-19  producers: gather X^T tiles (128 features x 32 rows of X, K-major) from global
 //               memory straight into the 128B-swizzled UMMA shared-memory layout
 //               - NCHW operands with 16-byte alignable rows: 128-bit loads/stores
 //               - im2col operands: read from a zero-padded fp32 staging copy (kfb_factor.cu, PadJob),
@@ -40,9 +42,10 @@ constexpr int kTileBytes = TM * BK * 4; // 16 KB
 constexpr int kStageBytes = 4 * kTileBytes;          // slots 0,1: the block's row tiles; 2,3: column tiles
 constexpr int kProducerWarps = 16;
 constexpr int kRowsPerWarp = TM / kProducerWarps;   // 8 rows of each tile per producer warp
-constexpr int kThreads = 32 * (4 + 1 + kProducerWarps);
+constexpr int kThreads = 32 * (4 + kProducerWarps);
 constexpr int kTmemCols = 512;
-constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256;
+constexpr int kTableOff = kStages * kStageBytes + 256;          // after the mbarriers: 16 warps x 32 row offsets
+constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + kProducerWarps * 128;
 
 // A tile row (= one feature of X) is described by ONE packed word: (element offset << 6) | bit,
 // where `bit` selects the bit of the lane's validity mask that says whether this feature exists
@@ -75,6 +78,11 @@ __device__ __forceinline__ bool row_valid(uint32_t info, uint32_t mlo, uint32_t 
   return (__funnelshift_r(mlo, 0u, info) & 1u) != 0;
 }
 
+// x / d by the segment's precomputed multiplier (see magic_div in kfb_factor.cu); x < 2^31
+__device__ __forceinline__ uint32_t fast_div(uint32_t x, uint32_t mul, uint32_t shift) {
+  return mul ? (__umulhi(x, mul) >> shift) : x;
+}
+
 // Items are sorted longest first; hand them out boustrophedon (CTA 0..G-1, then G-1..0, ...) so the
 // per-CTA totals even out without a dynamic scheduler.
 __device__ __forceinline__ int snake_item(int round, int total) {
@@ -87,6 +95,12 @@ __device__ __forceinline__ int snake_item(int round, int total) {
 // address translation on every store) instead of STS
 __device__ __forceinline__ void sts_f32(uint32_t addr, float v) {
   asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void sts_u32(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void lds_v4(uint32_t addr, uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d) {
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(addr) : "memory");
 }
 __device__ __forceinline__ void sts_v4(uint32_t addr, float4 v) {
   asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
@@ -102,8 +116,8 @@ __device__ __forceinline__ void cp_async4_zfill(uint32_t dst, const void* src, u
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
 }
 // this thread's arrival on `bar` happens when all of its earlier cp.async copies have landed
-__device__ __forceinline__ void cp_async_arrive(uint64_t* bar) {
-  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(umma::smem_u32(bar)) : "memory");
+__device__ __forceinline__ void cp_async_arrive(uint32_t bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
 }
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
@@ -130,15 +144,16 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
     umma::mbar_init(tempty, 128);
     umma::fence_barrier_init();
   }
-  if (warp == 4) umma::tmem_alloc<kTmemCols>(tmem_slot);
+  if (warp == 0) umma::tmem_alloc<kTmemCols>(tmem_slot);
   umma::tc_fence_before();
   __syncthreads();
   umma::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp >= 5) {
+  const uint32_t full_a = umma::smem_u32(full), empty_a = umma::smem_u32(empty);
+  if (warp >= 4) {
     // ===================== producers =====================
-    const int pw = warp - 5;
+    const int pw = warp - 4;
     // byte offset of this lane inside any of this warp's tile rows: rows are pw + 16*j, so the
     // swizzle term (row & 7) is the same for all of them
     const uint32_t lane_off = (uint32_t)((((lane >> 2) ^ (pw & 7)) << 4) | ((lane & 3) << 2));
@@ -173,16 +188,16 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
         uint32_t b = item.k_begin / BK;
         uint32_t n = b / unb, sb = b - n * unb;
         for (uint32_t k0 = item.k_begin; k0 < k_end32; k0 += BK) {
-          umma::mbar_wait(&empty[stage], phase ^ 1);
+          umma::mbar_wait_a(empty_a + 8 * stage, phase ^ 1);
           if (issuer) {
-            umma::mbar_arrive_expect_tx(&full[stage], (uint32_t)(n_slots * kTileBytes));
-            uint8_t* st = smem + stage * kStageBytes;
+            umma::mbar_arrive_expect_tx_a(full_a + 8 * stage, (uint32_t)(n_slots * kTileBytes));
+            const uint32_t st = smem_base + stage * kStageBytes;
 #pragma unroll
             for (int t = 0; t < 4; ++t)
               if (t < n_slots)
-                umma::tma_load_3d(st + slot_of[t] * kTileBytes, tm, &full[stage], (int)(sb * BK), tile_of[t] * TM, (int)n);
+                umma::tma_load_3d_a(st + slot_of[t] * kTileBytes, tm, full_a + 8 * stage, (int)(sb * BK), tile_of[t] * TM, (int)n);
           } else {
-            umma::mbar_arrive(&full[stage]);
+            umma::mbar_arrive_a(full_a + 8 * stage);
           }
           __syncwarp();
           if (++sb == unb) { sb = 0; ++n; }
@@ -219,11 +234,11 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
             for (int i = 0; i < 2; ++i)
               info[t][i] = t < n_slots ? row_info(s, d, tile_of[t] * TM + pw + kProducerWarps * (4 * i + vec_rsub)) : kBitNever;
           for (uint32_t k0 = item.k_begin; k0 < k_end32; k0 += BK) {
-            umma::mbar_wait(&empty[stage], phase ^ 1);
+            umma::mbar_wait_a(empty_a + 8 * stage, phase ^ 1);
             const uint32_t st = smem_base + stage * kStageBytes;
             const uint32_t k = k0 + 4 * vec_kq;
             const bool kin = k < k_end32;
-            const uint32_t n = k / uS;
+            const uint32_t n = fast_div(k, s.mul_s, s.sh_s);
             const char* src = reinterpret_cast<const char*>(s.data) + (((int64_t)n * s.c * S + (k - n * uS)) << esh);
             float4 v[4][2];
   #pragma unroll
@@ -251,57 +266,57 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
                   sts_v4(st + slot_of[t] * kTileBytes + r * 128 + ((vec_kq ^ (r & 7)) << 4), v[t][i]);
                 }
             umma::fence_proxy_async_smem();
-            umma::mbar_arrive(&full[stage]);
+            umma::mbar_arrive_a(full_a + 8 * stage);
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
         } else if (esh == 2 && s.nomask) {
           // ---- im2col from the zero-padded staging copy: every tap of every X row is in range, so a
-          // tile row is just (lane's window origin) + (row's byte offset).  Word = byte offset | 1 if
-          // the feature does not exist (>= d, or the bias feature, written separately below).
-          uint32_t off[4][kRowsPerWarp];
+          // tile row is just (lane's window origin) + (row's byte offset).  The warp's 32 row offsets
+          // (4 slots x 8 rows) live in a shared-memory table written once per item - lane l computes
+          // entry l - and come back four at a time (LDS.128) in the stage loop, which keeps the
+          // registers free for eight independent copy addresses.  Word = byte offset | 1 if the
+          // feature does not exist (>= d, or the bias feature, written separately below).
+          const uint32_t tbl = smem_base + kTableOff + pw * 128;
           bool pair_clean[2] = {true, true};
+          {
+            const int t = lane >> 3, j = lane & 7;
+            uint32_t inf = kBitNever;
   #pragma unroll
-          for (int t = 0; t < 4; ++t) {
+            for (int tt = 0; tt < 4; ++tt)
+              if (tt == t && tt < n_slots) inf = row_info(s, d, tile_of[tt] * TM + pw + kProducerWarps * j);
+            sts_u32(tbl + lane * 4, (inf & 63u) == kBitNever ? 1u : ((inf >> 6) << 2));
   #pragma unroll
-            for (int j = 0; j < kRowsPerWarp; ++j) {
-              const uint32_t inf = t < n_slots ? row_info(s, d, tile_of[t] * TM + pw + kProducerWarps * j) : kBitNever;
-              off[t][j] = (inf & 63u) == kBitNever ? 1u : ((inf >> 6) << 2);
-            }
-            if (t < n_slots && (tile_of[t] + 1) * TM > d - s.has_bias) pair_clean[t >> 1] = false;
+            for (int tt = 0; tt < 4; ++tt)
+              if (tt < n_slots && (tile_of[tt] + 1) * TM > d - s.has_bias) pair_clean[tt >> 1] = false;
           }
+          __syncwarp();
           const int64_t img = (int64_t)s.c * s.h * s.w;
           for (uint32_t k0 = item.k_begin; k0 < k_end32; k0 += BK) {
-            umma::mbar_wait(&empty[stage], phase ^ 1);
+            umma::mbar_wait_a(empty_a + 8 * stage, phase ^ 1);
             const uint32_t st = smem_base + stage * kStageBytes + pw * 128 + lane_off;
             const uint32_t k = k0 + lane;
             const bool kin = k < k_end32;
             const bool full_stage = k0 + BK <= k_end32;
-            const uint32_t n = k / uS;
+            const uint32_t n = fast_div(k, s.mul_s, s.sh_s);
             const uint32_t r = k - n * uS;
-            const uint32_t oy = r / uow, ox = r - oy * uow;
+            const uint32_t oy = fast_div(r, s.mul_w, s.sh_w), ox = r - oy * uow;
             // lanes past the end of the item read image 0's window (in range) and are zeroed below
             const char* src = reinterpret_cast<const char*>(s.data) +
                               ((kin ? (int64_t)n * img : 0) + (int64_t)(oy * s.sh) * s.w + ox * s.sw) * 4;
   #pragma unroll
-            for (int tp = 0; tp < 2; ++tp) {
-              if (2 * tp >= n_slots) break;
-              if (full_stage && pair_clean[tp]) {
+            for (int t = 0; t < 4; ++t) {
+              if (t >= n_slots) break;
+              uint32_t o[kRowsPerWarp];
+              lds_v4(tbl + t * 32, o[0], o[1], o[2], o[3]);
+              lds_v4(tbl + t * 32 + 16, o[4], o[5], o[6], o[7]);
+              const uint32_t dst = st + slot_of[t] * kTileBytes;
+              if (full_stage && pair_clean[t >> 1]) {
   #pragma unroll
-                for (int u = 0; u < 2; ++u)
-  #pragma unroll
-                  for (int j = 0; j < kRowsPerWarp; ++j)
-                    if (2 * tp + u < n_slots)
-                      cp_async4(st + slot_of[2 * tp + u] * kTileBytes + j * (kProducerWarps * 128), src + off[2 * tp + u][j]);
+                for (int j = 0; j < kRowsPerWarp; ++j) cp_async4(dst + j * (kProducerWarps * 128), src + o[j]);
               } else {
   #pragma unroll
-                for (int u = 0; u < 2; ++u)
-  #pragma unroll
-                  for (int j = 0; j < kRowsPerWarp; ++j)
-                    if (2 * tp + u < n_slots) {
-                      const uint32_t o = off[2 * tp + u][j];
-                      cp_async4_zfill(st + slot_of[2 * tp + u] * kTileBytes + j * (kProducerWarps * 128), src + (o & ~3u),
-                                      (kin && !(o & 1u)) ? 4u : 0u);
-                    }
+                for (int j = 0; j < kRowsPerWarp; ++j)
+                  cp_async4_zfill(dst + j * (kProducerWarps * 128), src + (o[j] & ~3u), (kin && !(o[j] & 1u)) ? 4u : 0u);
               }
             }
             if (bias_slot >= 0) {
@@ -309,7 +324,7 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
                       kin ? 1.f : 0.f);
               umma::fence_proxy_async_smem();
             }
-            cp_async_arrive(&full[stage]);
+            cp_async_arrive(full_a + 8 * stage);
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
         } else {
@@ -321,11 +336,11 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
             for (int j = 0; j < kRowsPerWarp; ++j)
               info[t][j] = t < n_slots ? row_info(s, d, tile_of[t] * TM + pw + kProducerWarps * j) : kBitNever;
           for (uint32_t k0 = item.k_begin; k0 < k_end32; k0 += BK) {
-            umma::mbar_wait(&empty[stage], phase ^ 1);
+            umma::mbar_wait_a(empty_a + 8 * stage, phase ^ 1);
             const uint32_t st = smem_base + stage * kStageBytes + pw * 128 + lane_off;
             const uint32_t k = k0 + lane;
             const bool kin = k < k_end32;
-            const uint32_t n = k / uS;
+            const uint32_t n = fast_div(k, s.mul_s, s.sh_s);
             const uint32_t r = k - n * uS;
             const char* src;
             uint32_t mlo = 0, mhi = 0;
@@ -333,7 +348,7 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
               src = reinterpret_cast<const char*>(s.data) + (((int64_t)n * s.c * S + r) << esh);
               if (kin) mhi = 1u << (kBitAlways - 32);
             } else {
-              const int oy = (int)(r / uow), ox = (int)(r - (uint32_t)oy * uow);
+              const int oy = (int)fast_div(r, s.mul_w, s.sh_w), ox = (int)(r - (uint32_t)oy * uow);
               const int y0 = oy * s.sh - s.ph, x0 = ox * s.sw - s.pw;
               src = reinterpret_cast<const char*>(s.data) + (((int64_t)n * s.c * s.h * s.w + (int64_t)y0 * s.w + x0) << esh);
               if (kin) {
@@ -389,7 +404,7 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
               sts_f32(smem_base + stage * kStageBytes + bias_slot * kTileBytes + bias_row * 128 + lane_off,
                       kin ? 1.f : 0.f);
             if (esh != 2 || bias_slot >= 0) umma::fence_proxy_async_smem();
-            cp_async_arrive(&full[stage]);       // with no copies in flight this is an immediate arrival
+            cp_async_arrive(full_a + 8 * stage);       // with no copies in flight this is an immediate arrival
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
         }
@@ -397,46 +412,11 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
       if (s.dtype == KFB_F32) gather(std::integral_constant<int, 2>{});
       else gather(std::integral_constant<int, 1>{});
     }
-  } else if (warp == 4) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
-      int stage = 0; uint32_t phase = 0;
-      uint32_t acc_phase = 0;
-      for (int round = 0, it; (it = snake_item(round, n_items)) >= 0; ++round) {
-        const TcItem item = items[it];
-        const bool diag = item.a0 == item.b0;
-        umma::mbar_wait(tempty, acc_phase ^ 1);            // the epilogue has drained TMEM
-        umma::tc_fence_after();
-        bool first = true;
-        for (uint32_t k0 = item.k_begin; k0 < item.k_end; k0 += BK) {
-          umma::mbar_wait(&full[stage], phase);
-          umma::tc_fence_after();
-          const uint32_t sbase = umma::smem_u32(smem + stage * kStageBytes);
-          for (int m = 0; m < item.mi; ++m) {
-            // row tile m against column tiles n0..nj-1 in ONE instruction (N = 128 or 256); on the
-            // diagonal the column tiles are the row tiles and products below the diagonal are skipped
-            const int n0 = diag ? m : 0;
-            const int ncols = (item.nj - n0) * TM;
-            const uint64_t da = umma::make_kmajor_sw128_desc(sbase + m * kTileBytes);
-            const uint64_t db = umma::make_kmajor_sw128_desc(sbase + ((diag ? 0 : 2) + n0) * kTileBytes);
-            const uint32_t idesc = umma::make_idesc_tf32(TM, ncols);
-            const uint32_t d_tmem = tmem_base + m * 256 + n0 * TM;
-#pragma unroll
-            for (int k = 0; k < BK / UMMA_K; ++k)
-              umma::mma_tf32_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, (first && k == 0) ? 0u : 1u);
-          }
-          first = false;
-          umma::tc_commit(&empty[stage]);
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
-        }
-        umma::tc_commit(tfull);
-        acc_phase ^= 1;
-      }
-    }
   } else {
-    // ===================== epilogue (warps 0..3) =====================
+    // ===================== MMA issue (warp 0, lane 0) + epilogue (warps 0..3) =====================
     const int q = warp;
     uint32_t acc_phase = 0;
+    int stage = 0; uint32_t phase = 0;
     for (int round = 0, it; (it = snake_item(round, n_items)) >= 0; ++round) {
       const TcItem item = items[it];
       const DevJob& job = jobs[item.job];
@@ -444,6 +424,36 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
       const int d = job.d;
       const bool diag = item.a0 == item.b0;
       const float ratio = alpha / (1.f - alpha), one_m = 1.f - alpha;
+      if (warp == 0) {
+        if (lane == 0) {
+          umma::mbar_wait(tempty, acc_phase ^ 1);            // all four warps have drained TMEM
+          umma::tc_fence_after();
+          bool first = true;
+          for (uint32_t k0 = item.k_begin; k0 < item.k_end; k0 += BK) {
+            umma::mbar_wait_a(full_a + 8 * stage, phase);
+            umma::tc_fence_after();
+            const uint32_t sbase = umma::smem_u32(smem + stage * kStageBytes);
+            for (int m = 0; m < item.mi; ++m) {
+              // row tile m against column tiles n0..nj-1 in ONE instruction (N = 128 or 256); on the
+              // diagonal the column tiles are the row tiles and products below the diagonal are skipped
+              const int n0 = diag ? m : 0;
+              const int ncols = (item.nj - n0) * TM;
+              const uint64_t da = umma::make_kmajor_sw128_desc(sbase + m * kTileBytes);
+              const uint64_t db = umma::make_kmajor_sw128_desc(sbase + ((diag ? 0 : 2) + n0) * kTileBytes);
+              const uint32_t idesc = umma::make_idesc_tf32(TM, ncols);
+              const uint32_t d_tmem = tmem_base + m * 256 + n0 * TM;
+#pragma unroll
+              for (int k = 0; k < BK / UMMA_K; ++k)
+                umma::mma_tf32_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, (first && k == 0) ? 0u : 1u);
+            }
+            first = false;
+            umma::tc_commit(&empty[stage]);
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
+          }
+          umma::tc_commit(tfull);
+        }
+        __syncwarp();
+      }
       umma::mbar_wait(tfull, acc_phase);
       umma::tc_fence_after();
       for (int m = 0; m < item.mi; ++m) {
@@ -532,7 +542,7 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
 
   umma::tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == 0) {
     umma::tc_fence_after();
     umma::tmem_dealloc<kTmemCols>(tmem_base);
   }
