@@ -299,6 +299,39 @@ __global__ void __launch_bounds__(256) tri_kernel(const __grid_constant__ TriBat
 
 // Staging copies for the tensor-core SYRK (PadJob): every thread writes four consecutive floats of
 // one copy.  HBM-bound: reads the capture once, writes 1.0-1.2x its size.
+template <typename T>
+__device__ __forceinline__ float pad_load(const T* p, int dtype) {
+  if (sizeof(T) == 4) return __ldg(reinterpret_cast<const float*>(p));
+  return widen16(__ldg(reinterpret_cast<const unsigned short*>(p)), dtype);
+}
+
+template <typename T>
+__device__ __forceinline__ void pad_quad(const PadJob& p, uint32_t e0) {
+  // (plane, y, x) of the first of this thread's four consecutive floats
+  const uint32_t row = p.mul_wp ? (__umulhi(e0, p.mul_wp) >> p.sh_wp) : e0;
+  int x = (int)(e0 - row * (uint32_t)p.wp);
+  const uint32_t plane = p.mul_hp ? (__umulhi(row, p.mul_hp) >> p.sh_hp) : row;
+  int y = (int)(row - plane * (uint32_t)p.hp);
+  const T* img = reinterpret_cast<const T*>(p.src) + (size_t)plane * p.h * p.w;
+  const size_t plane_elems = (size_t)p.h * p.w;
+  const uint32_t total = (uint32_t)p.total;
+  float v[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int sy = y * p.step - p.pad_h, sx = x * p.step - p.pad_w;
+    v[i] = 0.f;
+    if (e0 + i < total && (unsigned)sy < (unsigned)p.h && (unsigned)sx < (unsigned)p.w) v[i] = pad_load(img + sy * p.w + sx, p.dtype);
+    if (++x == p.wp) { x = 0; if (++y == p.hp) { y = 0; img += plane_elems; } }
+  }
+  if (e0 + 3 < total) {
+    *reinterpret_cast<float4*>(p.dst + e0) = make_float4(v[0], v[1], v[2], v[3]);
+  } else {
+    for (int i = 0; i < 4 && e0 + i < total; ++i) p.dst[e0 + i] = v[i];
+  }
+}
+
+// Staging copies for the tensor-core SYRK (PadJob): every thread writes four consecutive floats of
+// one copy.  HBM-bound: reads the capture once, writes 1.0-1.2x its size.
 __global__ void __launch_bounds__(256) pad_kernel(const PadJob* __restrict__ pads, const int* __restrict__ start, int n_pads) {
   int lo = 0, hi = n_pads;
   while (hi - lo > 1) {
@@ -306,27 +339,10 @@ __global__ void __launch_bounds__(256) pad_kernel(const PadJob* __restrict__ pad
     if (start[mid] <= (int)blockIdx.x) lo = mid; else hi = mid;
   }
   const PadJob& p = pads[lo];
-  const int64_t e0 = ((int64_t)(blockIdx.x - start[lo]) * 256 + threadIdx.x) * 4;
-  if (e0 >= p.total) return;
-  const int64_t row = e0 / p.wp;
-  int x = (int)(e0 - row * p.wp);
-  const int64_t plane = row / p.hp;
-  int y = (int)(row - plane * p.hp);
-  int64_t pl = plane;
-  float v[4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int sy = y * p.step - p.pad_h, sx = x * p.step - p.pad_w;
-    v[i] = 0.f;
-    if (e0 + i < p.total && sy >= 0 && sy < p.h && sx >= 0 && sx < p.w)
-      v[i] = load_elem(p.src, p.dtype, (pl * p.h + sy) * p.w + sx);
-    if (++x == p.wp) { x = 0; if (++y == p.hp) { y = 0; ++pl; } }
-  }
-  if (e0 + 3 < p.total) {
-    *reinterpret_cast<float4*>(p.dst + e0) = make_float4(v[0], v[1], v[2], v[3]);
-  } else {
-    for (int i = 0; i < 4 && e0 + i < p.total; ++i) p.dst[e0 + i] = v[i];
-  }
+  const uint32_t e0 = ((uint32_t)(blockIdx.x - start[lo]) * 256 + threadIdx.x) * 4;
+  if (e0 >= (uint32_t)p.total) return;
+  if (p.dtype == KFB_F32) pad_quad<float>(p, e0);
+  else pad_quad<unsigned short>(p, e0);
 }
 
 int run_tri(const kfb_tri_job* jobs, int n_jobs, float scale, bool unpack, cudaStream_t stream) {
@@ -473,7 +489,9 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
           pj.wp = ((ds.ow - 1) * ds.sw + ds.kw + 3) / 4 * 4;
         }
         pj.total = planes * pj.hp * pj.wp;
-        if (pj.step > 0 && (int64_t)ds.c * pj.hp * pj.wp < ((int64_t)1 << 26)) {
+        magic_div(pj.wp, &pj.mul_wp, &pj.sh_wp);
+        magic_div(pj.hp, &pj.mul_hp, &pj.sh_hp);
+        if (pj.step > 0 && pj.total < ((int64_t)1 << 31) && (int64_t)ds.c * pj.hp * pj.wp < ((int64_t)1 << 26)) {
           plan->seg_pad.back() = (int)plan->pads.size();
           plan->pad_off.push_back(plan->stage_floats);
           plan->stage_floats += align_up((size_t)pj.total, 64);

@@ -69,7 +69,8 @@ struct PadJob {
   int h, w;              // source image
   int hp, wp;            // staged image (wp = row pitch)
   int step, pad_h, pad_w;
-  int64_t total;         // planes * hp * wp
+  uint32_t mul_wp, sh_wp, mul_hp, sh_hp;   // x / wp, x / hp by multiply-high (magic_div)
+  int64_t total;         // planes * hp * wp (< 2^31)
 };
 
 struct TcItem {            // one unit of tensor-core SYRK work: a 2x2 block of 128-wide tiles
