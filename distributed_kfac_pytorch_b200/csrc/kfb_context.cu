@@ -36,6 +36,10 @@ int require_context(Context** out) {
 }
 
 int mma_mode() { return g_mma_mode; }
+int syrk_pair_mode() {
+  const char* e = getenv("KFB_SYRK_2CTA");
+  return e ? atoi(e) : 0;
+}
 int stage_mode() {
   const char* e = getenv("KFB_SYRK_STAGE");
   return !(e && e[0] == '0');

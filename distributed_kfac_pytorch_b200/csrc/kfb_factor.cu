@@ -569,7 +569,7 @@ std::vector<int64_t> g_plan_sig;
 
 void signature(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool tc, std::vector<int64_t>* sig) {
   sig->clear();
-  sig->push_back(n_jobs); sig->push_back(num_sms); sig->push_back(tc); sig->push_back(tma_mode());
+  sig->push_back(n_jobs); sig->push_back(num_sms); sig->push_back(tc); sig->push_back(tma_mode()); sig->push_back(stage_mode()); sig->push_back(syrk_pair_mode());
   for (int i = 0; i < n_jobs; ++i) {
     const kfb_factor_job& j = jobs[i];
     sig->push_back(j.d); sig->push_back(j.n_segments); sig->push_back(j.ld_state);

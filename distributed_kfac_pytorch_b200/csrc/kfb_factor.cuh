@@ -81,7 +81,8 @@ struct TcItem {            // one unit of tensor-core SYRK work: a 2x2 block of 
 };
 
 struct FactorPlan {
-  std::vector<TcItem> tc_items;
+  std::vector<TcItem> tc_items;          // [0, n_pair_items): CTA-pair kernel; the rest: single-CTA kernel
+  int n_pair_items = 0;
   size_t off_tc_items = 0;
   std::vector<DevJob> jobs;
   std::vector<DevSegment> segs;

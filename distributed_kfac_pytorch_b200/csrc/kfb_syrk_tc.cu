@@ -37,15 +37,29 @@ namespace {
 constexpr int TM = 128;                 // tile side (features)
 constexpr int BK = 32;                  // rows of X per stage = one 128-byte swizzle row
 constexpr int UMMA_K = 8;
-constexpr int kStages = 3;
 constexpr int kTileBytes = TM * BK * 4; // 16 KB
-constexpr int kStageBytes = 4 * kTileBytes;          // slots 0,1: the block's row tiles; 2,3: column tiles
 constexpr int kProducerWarps = 16;
 constexpr int kRowsPerWarp = TM / kProducerWarps;   // 8 rows of each tile per producer warp
-constexpr int kThreads = 32 * (4 + kProducerWarps);
 constexpr int kTmemCols = 512;
-constexpr int kTableOff = kStages * kStageBytes + 256;          // after the mbarriers: 16 warps x 32 row offsets
-constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + kProducerWarps * 128;
+
+// Two builds of the same kernel:
+//   single CTA : a stage holds the block's four tiles (64 KB), 3 stages; the four accumulators fill
+//                TMEM, so MMA issue (warp 0, lane 0) and the drain (warps 0-3) alternate; 20 warps.
+//   CTA pair   : cta_group::2 - the leader's MMAs use both SMs; each CTA gathers ONE row tile and ONE
+//                column tile (32 KB per stage, 6 stages: twice the bytes in flight per FLOP) and
+//                holds 128 x 256 accumulators, double-buffered, so the drain of one item overlaps the
+//                MMAs of the next; warp 4 issues (leader) or relays "my half has landed" (peer).
+template <bool kPair>
+struct Cfg {
+  static constexpr int kStages = kPair ? 6 : 3;
+  static constexpr int kSlots = kPair ? 2 : 4;                 // 16 KB tiles per stage
+  static constexpr int kStageBytes = kSlots * kTileBytes;
+  static constexpr int kFirstProducer = kPair ? 5 : 4;         // first producer warp
+  static constexpr int kThreads = 32 * (kFirstProducer + kProducerWarps);
+  static constexpr int kBarOff = kStages * kStageBytes;
+  static constexpr int kTableOff = kBarOff + 256;              // 16 warps x 32 row offsets
+  static constexpr int kSmemBytes = kBarOff + 1024 + 256 + kProducerWarps * 128;
+};
 
 // A tile row (= one feature of X) is described by ONE packed word: (element offset << 6) | bit,
 // where `bit` selects the bit of the lane's validity mask that says whether this feature exists
@@ -85,8 +99,9 @@ __device__ __forceinline__ uint32_t fast_div(uint32_t x, uint32_t mul, uint32_t 
 
 // Items are sorted longest first; hand them out boustrophedon (CTA 0..G-1, then G-1..0, ...) so the
 // per-CTA totals even out without a dynamic scheduler.
+template <bool kPair>
 __device__ __forceinline__ int snake_item(int round, int total) {
-  const int g = gridDim.x, c = blockIdx.x;
+  const int g = kPair ? gridDim.x >> 1 : gridDim.x, c = kPair ? blockIdx.x >> 1 : blockIdx.x;
   const int t = round * g + ((round & 1) ? g - 1 - c : c);
   return t < total ? t : -1;
 }
@@ -124,56 +139,75 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
-__global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __restrict__ jobs,
-                                                            const DevSegment* __restrict__ segs,
-                                                            const TcItem* __restrict__ items, int n_items, float alpha,
-                                                            const CUtensorMap* __restrict__ tmaps) {
+template <bool kPair>
+__global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const DevJob* __restrict__ jobs,
+                                                                        const DevSegment* __restrict__ segs,
+                                                                        const TcItem* __restrict__ items, int n_items, float alpha,
+                                                                        const CUtensorMap* __restrict__ tmaps) {
+  using C = Cfg<kPair>;
+  constexpr int kStages = C::kStages, kStageBytes = C::kStageBytes, kSlots = C::kSlots, kTableOff = C::kTableOff;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  uint64_t* full = (uint64_t*)(smem + kStages * kStageBytes);
+  uint64_t* full = (uint64_t*)(smem + C::kBarOff);
   uint64_t* empty = full + kStages;
-  uint64_t* tfull = empty + kStages;
-  uint64_t* tempty = tfull + 1;
-  uint32_t* tmem_slot = (uint32_t*)(tempty + 1);
+  uint64_t* tfull = empty + kStages;       // [2]; the single-CTA build uses [0] only
+  uint64_t* tempty = tfull + 2;            // [2]; in a pair the LEADER's copy collects both CTAs' arrivals
+  uint32_t* tmem_slot = (uint32_t*)(tempty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = kPair ? umma::cluster_ctarank() : 0u;
+  const bool leader = rank == 0;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kStages; ++s) { umma::mbar_init(&full[s], kProducerWarps * 32); umma::mbar_init(&empty[s], 1); }
-    umma::mbar_init(tfull, 1);
-    umma::mbar_init(tempty, 128);
+    // full: every producer thread arrives (cp.async completion or plain); the pair's leader also
+    // takes one arrival per stage from the peer's relay
+    for (int s = 0; s < kStages; ++s) {
+      umma::mbar_init(&full[s], kProducerWarps * 32 + ((kPair && leader) ? 1 : 0));
+      umma::mbar_init(&empty[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) { umma::mbar_init(&tfull[s], 1); umma::mbar_init(&tempty[s], kPair ? 256 : 128); }
     umma::fence_barrier_init();
   }
-  if (warp == 0) umma::tmem_alloc<kTmemCols>(tmem_slot);
+  if (kPair) { if (warp == 4) umma::tmem_alloc_pair<kTmemCols>(tmem_slot); }
+  else       { if (warp == 0) umma::tmem_alloc<kTmemCols>(tmem_slot); }
   umma::tc_fence_before();
   __syncthreads();
+  if (kPair) umma::cluster_sync_all();      // both CTAs' barriers exist before anything remote happens
   umma::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   const uint32_t full_a = umma::smem_u32(full), empty_a = umma::smem_u32(empty);
-  if (warp >= 4) {
+  if (warp >= C::kFirstProducer) {
     // ===================== producers =====================
-    const int pw = warp - 4;
+    const int pw = warp - C::kFirstProducer;
     // byte offset of this lane inside any of this warp's tile rows: rows are pw + 16*j, so the
     // swizzle term (row & 7) is the same for all of them
     const uint32_t lane_off = (uint32_t)((((lane >> 2) ^ (pw & 7)) << 4) | ((lane & 3) << 2));
     const uint32_t vec_kq = lane & 7, vec_rsub = lane >> 3;
     const uint32_t smem_base = umma::smem_u32(smem);
     int stage = 0; uint32_t phase = 0;
-    for (int round = 0, it; (it = snake_item(round, n_items)) >= 0; ++round) {
+    for (int round = 0, it; (it = snake_item<kPair>(round, n_items)) >= 0; ++round) {
       const TcItem item = items[it];
       const DevSegment s = segs[item.seg];
       const int d = jobs[item.job].d;
       const bool diag = item.a0 == item.b0;
-      // smem slots to fill: row tiles a0.. (slots 0..mi-1) and, off the diagonal, column tiles
-      // b0.. (slots 2..2+nj-1)
-      const int n_slots = diag ? item.mi : item.mi + item.nj;
-      int slot_of[4], tile_of[4];
+      // smem slots to fill.  Single CTA: row tiles a0.. (slots 0..mi-1) and, off the diagonal, column
+      // tiles b0.. (slots 2..2+nj-1).  Pair: this CTA's row tile a0+rank (slot 0) and, off the
+      // diagonal, its half of the column tiles, b0+rank (slot 1); tiles past the factor gather zeros.
+      int n_slots;
+      int slot_of[kSlots], tile_of[kSlots];
+      if (kPair) {
+        n_slots = diag ? 1 : 2;
+        slot_of[0] = 0; tile_of[0] = item.a0 + (int)rank;
+        slot_of[1] = 1; tile_of[1] = item.b0 + (int)rank;
+      } else {
+        n_slots = diag ? item.mi : item.mi + item.nj;
 #pragma unroll
-      for (int t = 0; t < 4; ++t) {
-        const bool is_a = t < item.mi;
-        slot_of[t] = is_a ? t : 2 + (t - item.mi);
-        tile_of[t] = is_a ? item.a0 + t : item.b0 + (t - item.mi);
+        for (int t = 0; t < kSlots; ++t) {
+          const bool is_a = t < item.mi;
+          slot_of[t] = is_a ? t : 2 + (t - item.mi);
+          tile_of[t] = is_a ? item.a0 + t : item.b0 + (t - item.mi);
+        }
       }
       const int S = s.oh * s.ow;
       const uint32_t uS = (uint32_t)S, uow = (uint32_t)s.ow;
@@ -190,12 +224,22 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
         for (uint32_t k0 = item.k_begin; k0 < k_end32; k0 += BK) {
           umma::mbar_wait_a(empty_a + 8 * stage, phase ^ 1);
           if (issuer) {
-            umma::mbar_arrive_expect_tx_a(full_a + 8 * stage, (uint32_t)(n_slots * kTileBytes));
             const uint32_t st = smem_base + stage * kStageBytes;
+            if (kPair) {
+              // both CTAs' boxes are credited to the LEADER's barrier, which expects the pair's bytes
+              if (leader) umma::mbar_arrive_expect_tx_a(full_a + 8 * stage, (uint32_t)(2 * n_slots * kTileBytes));
+              else umma::mbar_arrive_a(full_a + 8 * stage);
 #pragma unroll
-            for (int t = 0; t < 4; ++t)
-              if (t < n_slots)
-                umma::tma_load_3d_a(st + slot_of[t] * kTileBytes, tm, full_a + 8 * stage, (int)(sb * BK), tile_of[t] * TM, (int)n);
+              for (int t = 0; t < kSlots; ++t)
+                if (t < n_slots)
+                  umma::tma_load_3d_pair_a(st + slot_of[t] * kTileBytes, tm, full_a + 8 * stage, (int)(sb * BK), tile_of[t] * TM, (int)n);
+            } else {
+              umma::mbar_arrive_expect_tx_a(full_a + 8 * stage, (uint32_t)(n_slots * kTileBytes));
+#pragma unroll
+              for (int t = 0; t < kSlots; ++t)
+                if (t < n_slots)
+                  umma::tma_load_3d_a(st + slot_of[t] * kTileBytes, tm, full_a + 8 * stage, (int)(sb * BK), tile_of[t] * TM, (int)n);
+            }
           } else {
             umma::mbar_arrive_a(full_a + 8 * stage);
           }
@@ -212,7 +256,7 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
       int bias_slot = -1, bias_row = 0;
       if (s.has_bias) {
 #pragma unroll
-        for (int t = 0; t < 4; ++t) {
+        for (int t = 0; t < kSlots; ++t) {
           int local = (d - 1) - tile_of[t] * TM;
           if (t < n_slots && local >= 0 && local < TM && (local % kProducerWarps) == pw) {
             bias_slot = slot_of[t];
@@ -227,9 +271,9 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
         constexpr int esh = decltype(esh_tag)::value;     // log2(bytes per captured element)
         if (vec4) {
           // ---- NCHW, 16B-alignable: 8 lanes x float4 = one tile row (32 k), 4 rows per instruction
-          uint32_t info[4][2];
+          uint32_t info[kSlots][2];
   #pragma unroll
-          for (int t = 0; t < 4; ++t)
+          for (int t = 0; t < kSlots; ++t)
   #pragma unroll
             for (int i = 0; i < 2; ++i)
               info[t][i] = t < n_slots ? row_info(s, d, tile_of[t] * TM + pw + kProducerWarps * (4 * i + vec_rsub)) : kBitNever;
@@ -240,9 +284,9 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
             const bool kin = k < k_end32;
             const uint32_t n = fast_div(k, s.mul_s, s.sh_s);
             const char* src = reinterpret_cast<const char*>(s.data) + (((int64_t)n * s.c * S + (k - n * uS)) << esh);
-            float4 v[4][2];
+            float4 v[kSlots][2];
   #pragma unroll
-            for (int t = 0; t < 4; ++t)
+            for (int t = 0; t < kSlots; ++t)
   #pragma unroll
               for (int i = 0; i < 2; ++i) {
                 v[t][i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -258,7 +302,7 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
                 }
               }
   #pragma unroll
-            for (int t = 0; t < 4; ++t)
+            for (int t = 0; t < kSlots; ++t)
   #pragma unroll
               for (int i = 0; i < 2; ++i)
                 if (t < n_slots) {
@@ -277,17 +321,17 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
           // registers free for eight independent copy addresses.  Word = byte offset | 1 if the
           // feature does not exist (>= d, or the bias feature, written separately below).
           const uint32_t tbl = smem_base + kTableOff + pw * 128;
-          bool pair_clean[2] = {true, true};
+          uint32_t clean = 0xFu;            // bit t: every row of slot t is an existing, non-bias feature
           {
-            const int t = lane >> 3, j = lane & 7;
+            const int t = lane >> 3, j = lane & 7;      // pair build: lanes 16..31 write unused entries
             uint32_t inf = kBitNever;
   #pragma unroll
-            for (int tt = 0; tt < 4; ++tt)
+            for (int tt = 0; tt < kSlots; ++tt)
               if (tt == t && tt < n_slots) inf = row_info(s, d, tile_of[tt] * TM + pw + kProducerWarps * j);
             sts_u32(tbl + lane * 4, (inf & 63u) == kBitNever ? 1u : ((inf >> 6) << 2));
   #pragma unroll
-            for (int tt = 0; tt < 4; ++tt)
-              if (tt < n_slots && (tile_of[tt] + 1) * TM > d - s.has_bias) pair_clean[tt >> 1] = false;
+            for (int tt = 0; tt < kSlots; ++tt)
+              if (tt < n_slots && (tile_of[tt] + 1) * TM > d - s.has_bias) clean &= ~(1u << tt);
           }
           __syncwarp();
           const int64_t img = (int64_t)s.c * s.h * s.w;
@@ -304,13 +348,13 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
             const char* src = reinterpret_cast<const char*>(s.data) +
                               ((kin ? (int64_t)n * img : 0) + (int64_t)(oy * s.sh) * s.w + ox * s.sw) * 4;
   #pragma unroll
-            for (int t = 0; t < 4; ++t) {
+            for (int t = 0; t < kSlots; ++t) {
               if (t >= n_slots) break;
               uint32_t o[kRowsPerWarp];
               lds_v4(tbl + t * 32, o[0], o[1], o[2], o[3]);
               lds_v4(tbl + t * 32 + 16, o[4], o[5], o[6], o[7]);
               const uint32_t dst = st + slot_of[t] * kTileBytes;
-              if (full_stage && pair_clean[t >> 1]) {
+              if (full_stage && ((clean >> t) & 1u)) {
   #pragma unroll
                 for (int j = 0; j < kRowsPerWarp; ++j) cp_async4(dst + j * (kProducerWarps * 128), src + o[j]);
               } else {
@@ -329,9 +373,9 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
           }
         } else {
           // ---- general gather: one X row per lane, this warp's 8 rows of every tile per stage
-          uint32_t info[4][kRowsPerWarp];
+          uint32_t info[kSlots][kRowsPerWarp];
   #pragma unroll
-          for (int t = 0; t < 4; ++t)
+          for (int t = 0; t < kSlots; ++t)
   #pragma unroll
             for (int j = 0; j < kRowsPerWarp; ++j)
               info[t][j] = t < n_slots ? row_info(s, d, tile_of[t] * TM + pw + kProducerWarps * j) : kBitNever;
@@ -367,7 +411,7 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
             if (esh == 2) {
               // fp32: asynchronous copies, zero-filled where the mask says the tap is outside the image
   #pragma unroll
-              for (int t = 0; t < 4; ++t)
+              for (int t = 0; t < kSlots; ++t)
   #pragma unroll
                 for (int j = 0; j < kRowsPerWarp; ++j)
                   if (t < n_slots) {
@@ -379,7 +423,7 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
             } else {
               // 16-bit captures are widened in registers: two tiles (16 loads per lane) in flight at a time
   #pragma unroll
-              for (int tp = 0; tp < 2; ++tp) {
+              for (int tp = 0; tp < kSlots / 2; ++tp) {
                 if (2 * tp >= n_slots) break;
                 float v[2][kRowsPerWarp];
   #pragma unroll
@@ -412,19 +456,59 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
       if (s.dtype == KFB_F32) gather(std::integral_constant<int, 2>{});
       else gather(std::integral_constant<int, 1>{});
     }
+  } else if (kPair && warp == 4) {
+    // ===================== pair: MMA issuer (leader) / landing relay (peer) =====================
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      int acc = 0; uint32_t acc_phase = 0;
+      for (int round = 0, it; (it = snake_item<kPair>(round, n_items)) >= 0; ++round) {
+        const TcItem item = items[it];
+        if (leader) {
+          const bool diag = item.a0 == item.b0;
+          umma::mbar_wait(&tempty[acc], acc_phase ^ 1);      // both CTAs have drained this accumulator
+          umma::tc_fence_after();
+          // rows: tile a0 (this CTA) and a0+1 (peer); columns: tile b0 (here) and b0+1 (peer's half)
+          const uint32_t idesc = umma::make_idesc_tf32(2 * TM, 2 * TM);
+          const uint32_t d_tmem = tmem_base + acc * 256;
+          bool first = true;
+          for (uint32_t k0 = item.k_begin; k0 < item.k_end; k0 += BK) {
+            umma::mbar_wait_acquire_cluster_a(full_a + 8 * stage, phase);
+            umma::tc_fence_after();
+            const uint32_t sbase = umma::smem_u32(smem + stage * kStageBytes);
+            const uint64_t da = umma::make_kmajor_sw128_desc(sbase);
+            const uint64_t db = umma::make_kmajor_sw128_desc(sbase + (diag ? 0 : kTileBytes));
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k)
+              umma::mma_tf32_ss_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, (first && k == 0) ? 0u : 1u);
+            first = false;
+            umma::tc_commit_pair(&empty[stage]);
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
+          }
+          umma::tc_commit_pair(&tfull[acc]);
+          if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        } else {
+          for (uint32_t k0 = item.k_begin; k0 < item.k_end; k0 += BK) {
+            umma::mbar_wait_a(full_a + 8 * stage, phase);    // this CTA's copies of the stage have landed
+            umma::mbar_arrive_leader_release_a(full_a + 8 * stage);
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
   } else {
-    // ===================== MMA issue (warp 0, lane 0) + epilogue (warps 0..3) =====================
+    // ============ epilogue (warps 0..3); single-CTA build: warp 0, lane 0 also issues the MMAs ============
     const int q = warp;
     uint32_t acc_phase = 0;
+    int acc = 0;
     int stage = 0; uint32_t phase = 0;
-    for (int round = 0, it; (it = snake_item(round, n_items)) >= 0; ++round) {
+    for (int round = 0, it; (it = snake_item<kPair>(round, n_items)) >= 0; ++round) {
       const TcItem item = items[it];
       const DevJob& job = jobs[item.job];
       const float weight = segs[item.seg].weight;
       const int d = job.d;
       const bool diag = item.a0 == item.b0;
       const float ratio = alpha / (1.f - alpha), one_m = 1.f - alpha;
-      if (warp == 0) {
+      if (!kPair && warp == 0) {
         if (lane == 0) {
           umma::mbar_wait(tempty, acc_phase ^ 1);            // all four warps have drained TMEM
           umma::tc_fence_after();
@@ -454,13 +538,17 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
         }
         __syncwarp();
       }
-      umma::mbar_wait(tfull, acc_phase);
+      umma::mbar_wait(&tfull[acc], acc_phase);
       umma::tc_fence_after();
-      for (int m = 0; m < item.mi; ++m) {
+      // single CTA: both row tiles, accumulators at columns m*256; pair: this CTA's row tile only
+      // (a0 + rank), accumulator buffer `acc` at columns acc*256
+      const int m_begin = kPair ? (int)rank : 0;
+      const int m_end = kPair ? min((int)rank + 1, item.mi) : item.mi;
+      for (int m = m_begin; m < m_end; ++m) {
         const int i = (item.a0 + m) * TM + q * 32 + lane;
         for (int nn = diag ? m : 0; nn < item.nj; ++nn) {
           const int j0 = (item.b0 + nn) * TM;
-          const uint32_t taddr = tmem_base + m * 256 + nn * TM + ((uint32_t)(q * 32) << 16);
+          const uint32_t taddr = tmem_base + (kPair ? acc : m) * 256 + nn * TM + ((uint32_t)(q * 32) << 16);
 #pragma unroll 1
           for (int c = 0; c < TM / 32; ++c) {
             const int jb = j0 + c * 32;
@@ -535,14 +623,25 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
         }
       }
       umma::tc_fence_before();
-      umma::mbar_arrive(tempty);
-      acc_phase ^= 1;
+      if (kPair) {
+        umma::mbar_arrive_leader(&tempty[acc]);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      } else {
+        umma::mbar_arrive(tempty);
+        acc_phase ^= 1;
+      }
     }
   }
 
   umma::tc_fence_before();
   __syncthreads();
-  if (warp == 0) {
+  if (kPair) {
+    umma::cluster_sync_all();                 // the peer may still be signalling this CTA's barriers
+    if (warp == 4) {
+      umma::tc_fence_after();
+      umma::tmem_dealloc_pair<kTmemCols>(tmem_base);
+    }
+  } else if (warp == 0) {
     umma::tc_fence_after();
     umma::tmem_dealloc<kTmemCols>(tmem_base);
   }
@@ -550,15 +649,19 @@ __global__ void __launch_bounds__(kThreads, 1) syrk_tc_kernel(const DevJob* __re
 
 }  // namespace
 
-// Build the tensor-core work list for the jobs marked use_tc: (tile pair, K chunk) items, longest first.
+// Build the tensor-core work lists for the jobs marked use_tc: (2x2 tile block, K chunk) items,
+// longest first.  Large factors go to the CTA-pair kernel, which always computes the full 256 x 256
+// block (a good deal on factors of many tiles, a waste on one- or two-tile factors).
 void plan_syrk_tc(FactorPlan* plan) {
   constexpr int64_t kChunk = 2048;     // rows of X per item: ~64 stages of 4 tile products
-  plan->tc_items.clear();
+  const int pair_min_tiles = syrk_pair_mode();
+  std::vector<TcItem> pair_items, single_items;
   for (size_t ji = 0; ji < plan->jobs.size(); ++ji) {
     const DevJob& j = plan->jobs[ji];
     if (!j.use_tc) continue;
     const int T = ceil_div(j.d, TM);          // 128-wide tiles per side
     const int TB = ceil_div(T, 2);            // 256-wide blocks per side
+    std::vector<TcItem>& out = (pair_min_tiles > 0 && T >= pair_min_tiles) ? pair_items : single_items;
     for (int si = 0; si < j.n_segments; ++si) {
       const DevSegment& s = plan->segs[j.seg_start + si];
       // TMA segments iterate the per-image padded matrix: nb blocks of 32 rows per image
@@ -573,7 +676,7 @@ void plan_syrk_tc(FactorPlan* plan) {
             it.a0 = 2 * bi; it.b0 = 2 * bj;
             it.mi = std::min(2, T - it.a0); it.nj = std::min(2, T - it.b0);
             it.k_begin = (uint32_t)k; it.k_end = (uint32_t)std::min<int64_t>(K, k + len);
-            plan->tc_items.push_back(it);
+            out.push_back(it);
           }
     }
   }
@@ -581,25 +684,50 @@ void plan_syrk_tc(FactorPlan* plan) {
     int64_t units = a.a0 == a.b0 ? (a.mi * (a.mi + 1)) / 2 : a.mi * a.nj;
     return (int64_t)(a.k_end - a.k_begin) * units;
   };
-  std::stable_sort(plan->tc_items.begin(), plan->tc_items.end(),
-                   [&](const TcItem& a, const TcItem& b) { return cost(a) > cost(b); });
+  auto by_cost = [&](const TcItem& a, const TcItem& b) { return cost(a) > cost(b); };
+  auto by_len = [](const TcItem& a, const TcItem& b) { return a.k_end - a.k_begin > b.k_end - b.k_begin; };
+  std::stable_sort(pair_items.begin(), pair_items.end(), by_len);      // a pair always does the full block
+  std::stable_sort(single_items.begin(), single_items.end(), by_cost);
+  plan->n_pair_items = (int)pair_items.size();
+  plan->tc_items = pair_items;
+  plan->tc_items.insert(plan->tc_items.end(), single_items.begin(), single_items.end());
 }
 
 int launch_syrk_tc(const FactorPlan& plan, void* workspace, Context* ctx, float alpha, cudaStream_t stream) {
   if (plan.tc_items.empty()) return KFB_OK;
-  static bool attr_set = false;
-  if (!attr_set) {
-    KFB_CUDA(cudaFuncSetAttribute(syrk_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    attr_set = true;
+  static bool attr_set[64] = {};
+  if (ctx->device >= 0 && ctx->device < 64 && !attr_set[ctx->device]) {
+    KFB_CUDA(cudaFuncSetAttribute(syrk_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<false>::kSmemBytes));
+    KFB_CUDA(cudaFuncSetAttribute(syrk_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<true>::kSmemBytes));
+    attr_set[ctx->device] = true;
   }
   char* ws = (char*)workspace;
-  const int n = (int)plan.tc_items.size();
-  const int grid = std::min(n, ctx->num_sms);
-  syrk_tc_kernel<<<grid, kThreads, kSmemBytes, stream>>>((const DevJob*)(ws + plan.off_jobs),
-                                                       (const DevSegment*)(ws + plan.off_segs),
-                                                       (const TcItem*)(ws + plan.off_tc_items), n, alpha,
-                                                       (const CUtensorMap*)(ws + plan.off_tmaps));
-  KFB_CHECK_LAUNCH();
+  const DevJob* jobs = (const DevJob*)(ws + plan.off_jobs);
+  const DevSegment* segs = (const DevSegment*)(ws + plan.off_segs);
+  const TcItem* items = (const TcItem*)(ws + plan.off_tc_items);
+  const CUtensorMap* tmaps = (const CUtensorMap*)(ws + plan.off_tmaps);
+  const int n_pair = plan.n_pair_items, n_single = (int)plan.tc_items.size() - n_pair;
+  if (n_pair > 0) {
+    KFB_REQUIRE(ctx->num_sms >= 2, "the CTA-pair SYRK needs at least two SMs");
+    const int clusters = std::min(n_pair, ctx->num_sms / 2);     // one item per cluster of 2 CTAs
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * clusters);
+    cfg.blockDim = dim3(Cfg<true>::kThreads);
+    cfg.dynamicSmemBytes = Cfg<true>::kSmemBytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    KFB_CUDA(cudaLaunchKernelEx(&cfg, syrk_tc_kernel<true>, jobs, segs, items, n_pair, alpha, tmaps));
+    count_launch();
+  }
+  if (n_single > 0) {
+    const int grid = std::min(n_single, ctx->num_sms);
+    syrk_tc_kernel<false><<<grid, Cfg<false>::kThreads, Cfg<false>::kSmemBytes, stream>>>(jobs, segs, items + n_pair, n_single, alpha, tmaps);
+    KFB_CHECK_LAUNCH();
+  }
   return KFB_OK;
 }
 

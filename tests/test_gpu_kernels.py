@@ -141,6 +141,48 @@ def test_conv_A_staged_and_in_place_agree(monkeypatch, case):
         assert_factor_close(out[0], out[1], tol=1e-5)
 
 
+def test_cta_pair_syrk_matches_single_cta(monkeypatch):
+    """KFB_SYRK_2CTA=<tiles> sends factors of at least that many 128-wide tiles per side to the
+    cta_group::2 build of the SYRK (leader issues, peer relays its landed stages, accumulators
+    double-buffered).  Off by default (measured slower while the gathers are load/store-unit bound);
+    kept parity-tested: odd tile counts, diagonal-only factors, bias tiles, TMA-fed and gathered
+    operands, fused and chunked jobs."""
+    N.set_ops(None)
+    o = N.get_ops()
+    o._enter(torch.zeros(1, device=DEV))
+    o.set_mma_mode(1)
+    gen = torch.Generator().manual_seed(33)
+    cases = [(9, 128, 28, 28, (3, 3), (1, 1), (1, 1), False), (33, 64, 14, 14, (3, 3), (2, 2), (1, 1), True),
+             (2, 70, 14, 14, (3, 3), (1, 1), (1, 1), False), (2, 3, 31, 29, (7, 7), (2, 2), (3, 3), False)]
+    for n, c, h, w, k, s, p, bias in cases:
+        x = torch.randn(n, c, h, w, generator=gen)
+        ref = O.factor_ema(O.conv2d_A([x], k, s, p, bias), None, 0.95)
+        out = []
+        for env in ('1', '0'):
+            monkeypatch.setenv('KFB_SYRK_2CTA', env)
+            d, segs = conv_segments(x, k, s, p, bias)
+            buf, state = alloc2d(d, d, DEV)
+            tri = torch.full((d * (d + 1) // 2,), float('nan'), device=DEV)
+            o.factor_update([N.FactorJob(d, segs, state, True, True, tri)], 0.95)
+            torch.cuda.synchronize()
+            assert_factor_close(state, ref)
+            torch.testing.assert_close(tri.cpu(), triu_pack(state.cpu()), rtol=0, atol=0)
+            out.append(state.clone())
+        assert_factor_close(out[0], out[1], tol=1e-5)
+    for shape in [(24, 260, 14, 14), (3, 300, 7, 7), (2, 16, 56, 56)]:      # NCHW: TMA-fed / gathered
+        n, c, h, w = shape
+        g = torch.randn(*shape, generator=gen)
+        S = h * w
+        ref = O.factor_ema(O.conv2d_G([g]), None, 0.95)
+        for env in ('1', '0'):
+            monkeypatch.setenv('KFB_SYRK_2CTA', env)
+            seg = N.Segment(N.KFB_SEG_NCHW, g.to(DEV), n, c, 1.0 / (S * S * n * S), h=h, w=w)
+            buf, state = alloc2d(c, c, DEV)
+            o.factor_update([N.FactorJob(c, [seg], state, True, True, None)], 0.95)
+            torch.cuda.synchronize()
+            assert_factor_close(state, ref)
+
+
 def test_nchw_tma_and_gather_paths_agree(monkeypatch):
     """fp32 NCHW operands with 16-byte image rows are fetched by TMA (per-image 32-row blocks, tail
     zero-filled); KFB_SYRK_TMA=0 and a capture that is not 16-byte aligned use the gathering
