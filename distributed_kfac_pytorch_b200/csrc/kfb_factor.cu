@@ -307,21 +307,27 @@ __device__ __forceinline__ float pad_load(const T* p, int dtype) {
 
 template <typename T>
 __device__ __forceinline__ void pad_quad(const PadJob& p, uint32_t e0) {
-  // (plane, y, x) of the first of this thread's four consecutive floats
+  // (plane', y, x) of the first of this thread's four consecutive floats; plane' = plane*kw + kx
   const uint32_t row = p.mul_wp ? (__umulhi(e0, p.mul_wp) >> p.sh_wp) : e0;
   int x = (int)(e0 - row * (uint32_t)p.wp);
-  const uint32_t plane = p.mul_hp ? (__umulhi(row, p.mul_hp) >> p.sh_hp) : row;
-  int y = (int)(row - plane * (uint32_t)p.hp);
-  const T* img = reinterpret_cast<const T*>(p.src) + (size_t)plane * p.h * p.w;
+  uint32_t pk = p.mul_hp ? (__umulhi(row, p.mul_hp) >> p.sh_hp) : row;
+  int y = (int)(row - pk * (uint32_t)p.hp);
+  uint32_t plane = p.mul_kw ? (__umulhi(pk, p.mul_kw) >> p.sh_kw) : pk;
+  int kx = (int)(pk - plane * (uint32_t)p.kw);
   const size_t plane_elems = (size_t)p.h * p.w;
+  const T* img = reinterpret_cast<const T*>(p.src) + (size_t)plane * plane_elems;
   const uint32_t total = (uint32_t)p.total;
   float v[4];
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    const int sy = y * p.step - p.pad_h, sx = x * p.step - p.pad_w;
+    const int sy = y * p.sy - p.pad_h, sx = x * p.sx + kx - p.pad_w;
     v[i] = 0.f;
-    if (e0 + i < total && (unsigned)sy < (unsigned)p.h && (unsigned)sx < (unsigned)p.w) v[i] = pad_load(img + sy * p.w + sx, p.dtype);
-    if (++x == p.wp) { x = 0; if (++y == p.hp) { y = 0; img += plane_elems; } }
+    if (e0 + i < total && x < p.ow_valid && (unsigned)sy < (unsigned)p.h && (unsigned)sx < (unsigned)p.w)
+      v[i] = pad_load(img + sy * p.w + sx, p.dtype);
+    if (++x == p.wp) {
+      x = 0;
+      if (++y == p.hp) { y = 0; if (++kx == p.kw) { kx = 0; img += plane_elems; } }
+    }
   }
   if (e0 + 3 < total) {
     *reinterpret_cast<float4*>(p.dst + e0) = make_float4(v[0], v[1], v[2], v[3]);
@@ -478,20 +484,23 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
         PadJob pj;
         memset(&pj, 0, sizeof(pj));
         pj.src = ds.data; pj.dtype = ds.dtype; pj.h = ds.h; pj.w = ds.w;
-        const int64_t planes = (ds.K / ((int64_t)ds.oh * ds.ow)) * ds.c;
-        if (ds.kh == 1 && ds.kw == 1) {
-          pj.step = ds.sh; pj.pad_h = ds.ph; pj.pad_w = ds.pw;     // (sh == sw is not required:
-          pj.hp = ds.oh; pj.wp = ds.ow;                            //  see below)
-          if (ds.sh != ds.sw) { pj.step = 0; }
+        pj.pad_h = ds.ph; pj.pad_w = ds.pw; pj.ow_valid = ds.ow;
+        const int64_t images = ds.K / ((int64_t)ds.oh * ds.ow);
+        const bool pointwise = ds.kh == 1 && ds.kw == 1;
+        if (pointwise) {
+          pj.kw = 1; pj.sy = ds.sh; pj.sx = ds.sw;
+          pj.hp = ds.oh; pj.wp = ds.ow;
         } else {
-          pj.step = 1; pj.pad_h = ds.ph; pj.pad_w = ds.pw;
+          pj.kw = ds.kw; pj.sy = 1; pj.sx = ds.sw;
           pj.hp = (ds.oh - 1) * ds.sh + ds.kh;
-          pj.wp = ((ds.ow - 1) * ds.sw + ds.kw + 3) / 4 * 4;
+          pj.wp = (ds.ow + 3) / 4 * 4;
         }
-        pj.total = planes * pj.hp * pj.wp;
+        pj.total = images * ds.c * pj.kw * pj.hp * pj.wp;
         magic_div(pj.wp, &pj.mul_wp, &pj.sh_wp);
         magic_div(pj.hp, &pj.mul_hp, &pj.sh_hp);
-        if (pj.step > 0 && pj.total < ((int64_t)1 << 31) && (int64_t)ds.c * pj.hp * pj.wp < ((int64_t)1 << 26)) {
+        magic_div(pj.kw, &pj.mul_kw, &pj.sh_kw);
+        if (pj.total < ((int64_t)1 << 31) && (int64_t)ds.c * pj.kw * pj.hp * pj.wp < ((int64_t)1 << 26) &&
+            images * ds.oh * pj.wp < ((int64_t)1 << 31)) {
           plan->seg_pad.back() = (int)plan->pads.size();
           plan->pad_off.push_back(plan->stage_floats);
           plan->stage_floats += align_up((size_t)pj.total, 64);
@@ -499,12 +508,18 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
           ds.dtype = KFB_F32;
           ds.h = pj.hp; ds.w = pj.wp;
           ds.ph = ds.pw = 0;
-          if (ds.kh == 1 && ds.kw == 1) {
+          if (pointwise) {
             ds.sh = ds.sw = 1;
             if (!ds.has_bias) ds.kind = KFB_SEG_NCHW;
           } else {
             ds.nomask = 1;
+            ds.ow_valid = ds.ow;
+            ds.ow = pj.wp;                       // X rows now count padded pixels
+            ds.K = images * ds.oh * ds.ow;
+            ds.sw = 1;                           // the x-stride is applied by the copy
           }
+          magic_div((int64_t)ds.oh * ds.ow, &ds.mul_s, &ds.sh_s);
+          magic_div(ds.ow, &ds.mul_w, &ds.sh_w);
           aligned = true;       // staging copies start on 256-byte boundaries
         }
       }

@@ -25,7 +25,9 @@ struct DevSegment {
   int64_t chunk_len;
   uint32_t mul_s, sh_s;  // x / (oh*ow) = umulhi(x, mul_s) >> sh_s for x < 2^31 (mul_s = 0: divisor 1)
   uint32_t mul_w, sh_w;  // x / ow likewise
-  int nomask;            // IM2COL read from a zero-padded staging copy: every tap of every X row is in range
+  int nomask;            // IM2COL read from a staging copy (PadJob): h x w is the staged plane, ow the padded
+                         // row length, K counts padded pixels; every tap of every X row is in range
+  int ow_valid;          // nomask: output pixels per row that exist (bias feature = 1 only there)
   int tma;               // index of this segment's TMA descriptor, -1: gathered by the producer warps
   int nb;                // TMA segments: 32-row blocks per image (the last one zero-filled past oh*ow)
 };
@@ -57,20 +59,26 @@ __device__ __forceinline__ float load_elem(const void* base, int dtype, int64_t 
   return widen16(__ldg(reinterpret_cast<const unsigned short*>(base) + idx), dtype);
 }
 
-// Staging copy of one im2col capture for the tensor-core SYRK (fp32, whatever the capture's type):
-//   dst[plane][y][x] = src[plane][y*step - pad_h][x*step - pad_w]   (0 outside the source image)
-// step = 1: the zero-padded image, so that the gather needs no border tests (row pitch wp is a
-// multiple of 4 floats); step = conv stride for 1x1 strided convs: the dense sub-sampled image,
-// which then is an ordinary NCHW operand.
+// Staging copy of one im2col capture for the tensor-core SYRK (fp32, whatever the capture's type).
+// For every (image, channel) plane of the capture it holds kw planes of hp x wp floats, one per
+// kernel column kx, with the conv's x-stride already applied:
+//   dst[(plane*kw + kx)][y][x] = src[plane][y*sy - pad_h][x*sx + kx - pad_w]   for x < ow_valid,
+//   0 where that is outside the source image, and 0 for the pitch padding x >= ow_valid.
+// kxk convs: sy = 1, sx = stride, hp = (oh-1)*stride_h + kh, wp = ow rounded up to 4.  Four
+// consecutive output pixels of one (ky,kx) tap are then 16 contiguous, 16-byte aligned bytes, so the
+// gather moves 16 bytes per lane and needs no border tests.
+// 1x1 strided convs: kw = 1, sy/sx = stride, hp x wp = oh x ow: the dense sub-sampled image, which
+// then is an ordinary NCHW operand.
 struct PadJob {
   const void* src;
   float* dst;
   int dtype;
   int h, w;              // source image
-  int hp, wp;            // staged image (wp = row pitch)
-  int step, pad_h, pad_w;
-  uint32_t mul_wp, sh_wp, mul_hp, sh_hp;   // x / wp, x / hp by multiply-high (magic_div)
-  int64_t total;         // planes * hp * wp (< 2^31)
+  int hp, wp;            // staged plane (wp = row pitch)
+  int kw, ow_valid;
+  int sy, sx, pad_h, pad_w;
+  uint32_t mul_wp, sh_wp, mul_hp, sh_hp, mul_kw, sh_kw;   // x / wp, x / hp, x / kw by multiply-high (magic_div)
+  int64_t total;         // planes * kw * hp * wp (< 2^31)
 };
 
 struct TcItem {            // one unit of tensor-core SYRK work: a 2x2 block of 128-wide tiles

@@ -25,6 +25,7 @@
 //                 of an image's last block is zero-filled by the TMA unit
 // Operands stay fp32 in shared memory; kind::tf32 reads the top 19 bits, so no conversion pass.
 #include <algorithm>
+#include <cstdlib>
 #include <type_traits>
 #include <vector>
 
@@ -76,6 +77,8 @@ __device__ __forceinline__ uint32_t row_info(const DevSegment& s, int d, int i) 
   int ci = i / khw;
   int q = i - ci * khw;
   int ky = q / s.kw, kx = q - ky * s.kw;
+  // staging copy (PadJob): one h x w plane per (channel, kx), rows are input rows
+  if (s.nomask) return ((uint32_t)(((ci * s.kw + kx) * s.h + ky) * s.w) << 6) | kBitAlways;
   return ((uint32_t)((ci * s.h + ky) * s.w + kx) << 6) | (uint32_t)q;
 }
 
@@ -126,6 +129,12 @@ __device__ __forceinline__ void sts_v4(uint32_t addr, float4 v) {
 // src_bytes = 0 writes a zero without touching global memory (borders, padding rows, K tails).
 __device__ __forceinline__ void cp_async4(uint32_t dst, const void* src) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async16_zfill(uint32_t dst, const void* src, uint32_t src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
 }
 __device__ __forceinline__ void cp_async4_zfill(uint32_t dst, const void* src, uint32_t src_bytes) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
@@ -314,58 +323,58 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
         } else if (esh == 2 && s.nomask) {
-          // ---- im2col from the zero-padded staging copy: every tap of every X row is in range, so a
-          // tile row is just (lane's window origin) + (row's byte offset).  The warp's 32 row offsets
-          // (4 slots x 8 rows) live in a shared-memory table written once per item - lane l computes
-          // entry l - and come back four at a time (LDS.128) in the stage loop, which keeps the
-          // registers free for eight independent copy addresses.  Word = byte offset | 1 if the
-          // feature does not exist (>= d, or the bias feature, written separately below).
-          const uint32_t tbl = smem_base + kTableOff + pw * 128;
+          // ---- im2col from the staging copy (PadJob): for a tap (ky,kx) four consecutive output pixels
+          // of a row are 16 contiguous, aligned bytes, and every tap of every (padded) pixel is in range.
+          // 8 lanes x 16 bytes = one tile row (32 k), 4 rows per instruction, like the NCHW path; the
+          // copies are asynchronous, so a lane has the whole stage in flight.
+          // Word = byte offset of the row's (channel, kx) plane + ky rows | 1 if the feature does not
+          // exist (>= d, or the bias feature, written separately below).
+          uint32_t off[kSlots][2];
           uint32_t clean = 0xFu;            // bit t: every row of slot t is an existing, non-bias feature
-          {
-            const int t = lane >> 3, j = lane & 7;      // pair build: lanes 16..31 write unused entries
-            uint32_t inf = kBitNever;
   #pragma unroll
-            for (int tt = 0; tt < kSlots; ++tt)
-              if (tt == t && tt < n_slots) inf = row_info(s, d, tile_of[tt] * TM + pw + kProducerWarps * j);
-            sts_u32(tbl + lane * 4, (inf & 63u) == kBitNever ? 1u : ((inf >> 6) << 2));
+          for (int t = 0; t < kSlots; ++t) {
   #pragma unroll
-            for (int tt = 0; tt < kSlots; ++tt)
-              if (tt < n_slots && (tile_of[tt] + 1) * TM > d - s.has_bias) clean &= ~(1u << tt);
+            for (int i = 0; i < 2; ++i) {
+              const uint32_t inf = t < n_slots ? row_info(s, d, tile_of[t] * TM + pw + kProducerWarps * (4 * i + vec_rsub)) : kBitNever;
+              off[t][i] = (inf & 63u) == kBitNever ? 1u : ((inf >> 6) << 2);
+            }
+            if (t < n_slots && (tile_of[t] + 1) * TM > d - s.has_bias) clean &= ~(1u << t);
           }
-          __syncwarp();
-          const int64_t img = (int64_t)s.c * s.h * s.w;
+          const int64_t img = (int64_t)s.c * s.kw * s.h * s.w;
           for (uint32_t k0 = item.k_begin; k0 < k_end32; k0 += BK) {
             umma::mbar_wait_a(empty_a + 8 * stage, phase ^ 1);
-            const uint32_t st = smem_base + stage * kStageBytes + pw * 128 + lane_off;
-            const uint32_t k = k0 + lane;
-            const bool kin = k < k_end32;
+            const uint32_t st = smem_base + stage * kStageBytes;
+            const uint32_t k = k0 + 4 * vec_kq;           // this lane's four padded pixels: k .. k+3
+            const bool kin = k < k_end32;                 // item ends are multiples of 4
             const bool full_stage = k0 + BK <= k_end32;
             const uint32_t n = fast_div(k, s.mul_s, s.sh_s);
             const uint32_t r = k - n * uS;
             const uint32_t oy = fast_div(r, s.mul_w, s.sh_w), ox = r - oy * uow;
-            // lanes past the end of the item read image 0's window (in range) and are zeroed below
+            // lanes past the end of the item read image 0 (in range) and are zero-filled below
             const char* src = reinterpret_cast<const char*>(s.data) +
-                              ((kin ? (int64_t)n * img : 0) + (int64_t)(oy * s.sh) * s.w + ox * s.sw) * 4;
+                              ((kin ? (int64_t)n * img : 0) + (int64_t)(oy * s.sh) * s.w + ox) * 4;
   #pragma unroll
             for (int t = 0; t < kSlots; ++t) {
               if (t >= n_slots) break;
-              uint32_t o[kRowsPerWarp];
-              lds_v4(tbl + t * 32, o[0], o[1], o[2], o[3]);
-              lds_v4(tbl + t * 32 + 16, o[4], o[5], o[6], o[7]);
               const uint32_t dst = st + slot_of[t] * kTileBytes;
-              if (full_stage && ((clean >> t) & 1u)) {
   #pragma unroll
-                for (int j = 0; j < kRowsPerWarp; ++j) cp_async4(dst + j * (kProducerWarps * 128), src + o[j]);
-              } else {
-  #pragma unroll
-                for (int j = 0; j < kRowsPerWarp; ++j)
-                  cp_async4_zfill(dst + j * (kProducerWarps * 128), src + (o[j] & ~3u), (kin && !(o[j] & 1u)) ? 4u : 0u);
+              for (int i = 0; i < 2; ++i) {
+                const int rr = pw + kProducerWarps * (4 * i + vec_rsub);
+                const uint32_t da = dst + rr * 128 + ((vec_kq ^ (rr & 7)) << 4);
+                const uint32_t o = off[t][i];
+                if (slot_of[t] == bias_slot && rr == bias_row) continue;     // written below, not zero-filled
+                if (full_stage && ((clean >> t) & 1u)) cp_async16(da, src + o);
+                else cp_async16_zfill(da, src + (o & ~3u), (kin && !(o & 1u)) ? 16u : 0u);
               }
             }
+            // the bias feature is the constant 1 wherever the X row exists (not on the pitch padding)
             if (bias_slot >= 0) {
-              sts_f32(smem_base + stage * kStageBytes + bias_slot * kTileBytes + bias_row * 128 + lane_off,
-                      kin ? 1.f : 0.f);
+              const uint32_t kb = k0 + lane;
+              const uint32_t nb_ = fast_div(kb, s.mul_s, s.sh_s);
+              const uint32_t rb = kb - nb_ * uS;
+              const uint32_t xb = rb - fast_div(rb, s.mul_w, s.sh_w) * uow;
+              sts_f32(st + bias_slot * kTileBytes + bias_row * 128 + (uint32_t)((((lane >> 2) ^ (bias_row & 7)) << 4) | ((lane & 3) << 2)),
+                      (kb < k_end32 && xb < (uint32_t)s.ow_valid) ? 1.f : 0.f);
               umma::fence_proxy_async_smem();
             }
             cp_async_arrive(full_a + 8 * stage);
@@ -414,7 +423,7 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
               for (int t = 0; t < kSlots; ++t)
   #pragma unroll
                 for (int j = 0; j < kRowsPerWarp; ++j)
-                  if (t < n_slots) {
+                  if (t < n_slots && !(slot_of[t] == bias_slot && pw + kProducerWarps * j == bias_row)) {
                     const uint32_t inf = info[t][j];
                     const bool ok = wide ? row_valid<true>(inf, mlo, mhi) : row_valid<false>(inf, mnarrow, 0u);
                     cp_async4_zfill(st + slot_of[t] * kTileBytes + j * (kProducerWarps * 128), src + ((uint64_t)(inf >> 6) << 2),
@@ -472,7 +481,7 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
           const uint32_t d_tmem = tmem_base + acc * 256;
           bool first = true;
           for (uint32_t k0 = item.k_begin; k0 < item.k_end; k0 += BK) {
-            umma::mbar_wait_acquire_cluster_a(full_a + 8 * stage, phase);
+            umma::mbar_wait_a(full_a + 8 * stage, phase);
             umma::tc_fence_after();
             const uint32_t sbase = umma::smem_u32(smem + stage * kStageBytes);
             const uint64_t da = umma::make_kmajor_sw128_desc(sbase);
@@ -488,8 +497,13 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
           if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         } else {
           for (uint32_t k0 = item.k_begin; k0 < item.k_end; k0 += BK) {
-            umma::mbar_wait_a(full_a + 8 * stage, phase);    // this CTA's copies of the stage have landed
-            umma::mbar_arrive_leader_release_a(full_a + 8 * stage);
+            // This CTA's copies of the stage have landed in its shared memory (the local barrier says
+            // so); tell the leader with a plain remote arrive.  No cluster-scope release/acquire pair:
+            // nobody READS the data through the generic proxy on the other side - the pair's tensor
+            // cores read it in place - and ptxas turns release.cluster into MEMBAR.GPU + ERRBAR per
+            // stage (and acquire.cluster into an L1 invalidate), which made the relay the bottleneck.
+            umma::mbar_wait_a(full_a + 8 * stage, phase);
+            umma::mbar_arrive_leader_a(full_a + 8 * stage);
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
         }
@@ -512,25 +526,34 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
         if (lane == 0) {
           umma::mbar_wait(tempty, acc_phase ^ 1);            // all four warps have drained TMEM
           umma::tc_fence_after();
-          bool first = true;
+          // Per item: everything about the (up to two) MMAs of a k step except the stage offset.  Row
+          // tile m runs against column tiles n0..nj-1 in ONE instruction (N = 128 or 256); on the
+          // diagonal the column tiles are the row tiles and products below the diagonal are skipped.
+          uint32_t idesc_m[2], a_lo[2], b_lo[2], d_tm[2];
+          const uint32_t lo0 = umma::kmajor_sw128_desc_lo(umma::smem_u32(smem));
+#pragma unroll
+          for (int m = 0; m < 2; ++m) {
+            const int n0 = diag ? m : 0;
+            idesc_m[m] = umma::make_idesc_tf32(TM, (item.nj - n0) * TM);
+            a_lo[m] = lo0 + ((m * kTileBytes) >> 4);
+            b_lo[m] = lo0 + ((((diag ? 0 : 2) + n0) * kTileBytes) >> 4);
+            d_tm[m] = tmem_base + m * 256 + n0 * TM;
+          }
+          const bool two = item.mi > 1;
+          uint32_t acc_flag = 0;
           for (uint32_t k0 = item.k_begin; k0 < item.k_end; k0 += BK) {
             umma::mbar_wait_a(full_a + 8 * stage, phase);
             umma::tc_fence_after();
-            const uint32_t sbase = umma::smem_u32(smem + stage * kStageBytes);
-            for (int m = 0; m < item.mi; ++m) {
-              // row tile m against column tiles n0..nj-1 in ONE instruction (N = 128 or 256); on the
-              // diagonal the column tiles are the row tiles and products below the diagonal are skipped
-              const int n0 = diag ? m : 0;
-              const int ncols = (item.nj - n0) * TM;
-              const uint64_t da = umma::make_kmajor_sw128_desc(sbase + m * kTileBytes);
-              const uint64_t db = umma::make_kmajor_sw128_desc(sbase + ((diag ? 0 : 2) + n0) * kTileBytes);
-              const uint32_t idesc = umma::make_idesc_tf32(TM, ncols);
-              const uint32_t d_tmem = tmem_base + m * 256 + n0 * TM;
+            const uint32_t soff = (uint32_t)stage * (kStageBytes >> 4);
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k)
+              umma::mma_tf32_ss_lohi(d_tm[0], a_lo[0] + soff + 2 * k, b_lo[0] + soff + 2 * k, idesc_m[0], k == 0 ? acc_flag : 1u);
+            if (two) {
 #pragma unroll
               for (int k = 0; k < BK / UMMA_K; ++k)
-                umma::mma_tf32_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, (first && k == 0) ? 0u : 1u);
+                umma::mma_tf32_ss_lohi(d_tm[1], a_lo[1] + soff + 2 * k, b_lo[1] + soff + 2 * k, idesc_m[1], k == 0 ? acc_flag : 1u);
             }
-            first = false;
+            acc_flag = 1u;
             umma::tc_commit(&empty[stage]);
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
@@ -653,7 +676,7 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
 // longest first.  Large factors go to the CTA-pair kernel, which always computes the full 256 x 256
 // block (a good deal on factors of many tiles, a waste on one- or two-tile factors).
 void plan_syrk_tc(FactorPlan* plan) {
-  constexpr int64_t kChunk = 2048;     // rows of X per item: ~64 stages of 4 tile products
+  static const int64_t kChunk = getenv("KFB_SYRK_CHUNK") ? atoll(getenv("KFB_SYRK_CHUNK")) : 4096;     // rows of X per item: ~128 stages of 4 tile products (2048: 3.57 ms, 4096: 3.33, 8192: 3.40 on the ResNet-50 batch)
   const int pair_min_tiles = syrk_pair_mode();
   std::vector<TcItem> pair_items, single_items;
   for (size_t ji = 0; ji < plan->jobs.size(); ++ji) {

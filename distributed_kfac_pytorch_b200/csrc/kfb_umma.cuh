@@ -168,6 +168,28 @@ __device__ __forceinline__ void mma_tf32_ss(uint32_t d_tmem, uint64_t a_desc, ui
       : "memory");
 }
 
+// The same with the two descriptors given as (low word, shared high word): the low word is the only
+// part that changes from stage to stage and k step to k step, so an issue loop keeps it in one
+// 32-bit register and adds to it.  desc_hi / desc_lo match make_kmajor_sw128_desc.
+__host__ __device__ constexpr uint32_t kmajor_sw128_desc_hi() { return (uint32_t)(1024 >> 4) | (1u << 14) | (2u << 29); }
+__device__ __forceinline__ uint32_t kmajor_sw128_desc_lo(uint32_t smem_addr) {
+  return ((smem_addr & 0x3FFFF) >> 4) | (1u << 16);
+}
+__device__ __forceinline__ void mma_tf32_ss_lohi(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t idesc,
+                                                 uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      ".reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "mov.b64 da, {%1, %5};\n\t"
+      "mov.b64 db, {%2, %5};\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %3, p;\n\t"
+      "}" ::"r"(d_tmem),
+      "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(accumulate), "r"(kmajor_sw128_desc_hi())
+      : "memory");
+}
+
 // ---- CTA-pair (cta_group::2) variants ------------------------------------------------------------
 // In a 2-CTA cluster the shared::cta window address of the odd CTA differs from the even CTA's in
 // one bit; clearing it turns "my barrier" into "the same barrier in the pair's leader".
@@ -198,6 +220,9 @@ __device__ __forceinline__ void tma_load_3d_pair_a(uint32_t smem_dst, const CUte
       "[%2];" ::"r"(smem_dst),
       "l"(reinterpret_cast<uint64_t>(map)), "r"(bar & kPeerBitMask), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_leader_a(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar & kPeerBitMask) : "memory");
 }
 // "my half of this stage has landed": release at cluster scope on the leader's copy of the barrier,
 // matched by the leader's acquire.cluster wait
