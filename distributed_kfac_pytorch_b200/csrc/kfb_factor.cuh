@@ -78,6 +78,10 @@ struct PadJob {
   int kw, ow_valid;
   int sy, sx, pad_h, pad_w;
   uint32_t mul_wp, sh_wp, mul_hp, sh_hp, mul_kw, sh_kw;   // x / wp, x / hp, x / kw by multiply-high (magic_div)
+  uint32_t mul_wq, sh_wq;                                  // x / (wp/4)
+  int variant;           // 0: one thread per 4 output floats; 1: (sx,kw) = (1,3), 2: (2,3), 3: (2,7): one thread
+                         // reads a source row segment once and writes the 4-pixel group of all kw planes
+  int64_t quads;         // variants 1-3: planes * hp * wp/4 threads
   int64_t total;         // planes * kw * hp * wp (< 2^31)
 };
 
