@@ -372,6 +372,20 @@ __device__ __forceinline__ void pad_group(const PadJob& p, uint32_t q) {
   }
 }
 
+// Variant 4: dst[c][n*wp + s] = src[n][c][s]; hp = images, so (row = e0 / wp) = c*images + n.
+template <typename T>
+__device__ __forceinline__ void pad_transpose(const PadJob& p, uint32_t e0) {
+  const uint32_t row = p.mul_wp ? (__umulhi(e0, p.mul_wp) >> p.sh_wp) : e0;
+  const int x0 = (int)(e0 - row * (uint32_t)p.wp);
+  const uint32_t c = p.mul_hp ? (__umulhi(row, p.mul_hp) >> p.sh_hp) : row;
+  const uint32_t n = row - c * (uint32_t)p.hp;
+  const T* srow = reinterpret_cast<const T*>(p.src) + ((size_t)n * p.channels + c) * p.ow_valid;
+  float v[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) v[i] = x0 + i < p.ow_valid ? pad_load(srow + x0 + i, p.dtype) : 0.f;
+  *reinterpret_cast<float4*>(p.dst + e0) = make_float4(v[0], v[1], v[2], v[3]);     // wp % 4 == 0
+}
+
 // Staging copies for the tensor-core SYRK (PadJob).  HBM-bound: reads the capture once, writes kw x
 // (about) its size.
 __global__ void __launch_bounds__(256) pad_kernel(const PadJob* __restrict__ pads, const int* __restrict__ start, int n_pads) {
@@ -383,10 +397,12 @@ __global__ void __launch_bounds__(256) pad_kernel(const PadJob* __restrict__ pad
   const PadJob& p = pads[lo];
   const uint32_t t = (uint32_t)(blockIdx.x - start[lo]) * 256 + threadIdx.x;
   const bool f32 = p.dtype == KFB_F32;
-  if (p.variant == 0) {
+  if (p.variant == 0 || p.variant == 4) {
     const uint32_t e0 = t * 4;
     if (e0 >= (uint32_t)p.total) return;
-    if (f32) pad_quad<float>(p, e0); else pad_quad<unsigned short>(p, e0);
+    if (p.variant == 4) { if (f32) pad_transpose<float>(p, e0); else pad_transpose<unsigned short>(p, e0); }
+    else if (f32) pad_quad<float>(p, e0);
+    else pad_quad<unsigned short>(p, e0);
     return;
   }
   if (t >= (uint32_t)p.quads) return;
@@ -577,6 +593,34 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
           aligned = true;       // staging copies start on 256-byte boundaries
         }
       }
+      {
+        // NCHW operands TMA cannot take as they are: stage an fp32 [channels][images * padded pixels]
+        // copy (PadJob variant 4), which TMA reads as one "image" of K' = images * wp pixels
+        const int64_t S0 = (int64_t)ds.oh * ds.ow;
+        const bool tma_ok = ds.dtype == KFB_F32 && (S0 & 3) == 0 && S0 >= BK && aligned;
+        const int64_t images = ds.K / S0, wp = (S0 + 3) / 4 * 4;
+        if (ds.kind == KFB_SEG_NCHW && !tma_ok && stage_mode() && tma_mode() && plan->seg_pad.back() < 0 &&
+            images * wp >= BK && (int64_t)ds.c * images * wp < ((int64_t)1 << 31)) {
+          PadJob pj;
+          memset(&pj, 0, sizeof(pj));
+          pj.src = ds.data; pj.dtype = ds.dtype; pj.variant = 4;
+          pj.channels = ds.c; pj.hp = (int)images; pj.wp = (int)wp; pj.ow_valid = (int)S0; pj.kw = 1;
+          pj.total = (int64_t)ds.c * images * wp;
+          magic_div(pj.wp, &pj.mul_wp, &pj.sh_wp);
+          magic_div(pj.hp, &pj.mul_hp, &pj.sh_hp);
+          plan->seg_pad.back() = (int)plan->pads.size();
+          plan->pad_off.push_back(plan->stage_floats);
+          plan->stage_floats += align_up((size_t)pj.total, 64);
+          plan->pads.push_back(pj);
+          ds.dtype = KFB_F32;
+          ds.h = 1; ds.w = (int)(images * wp);
+          ds.oh = 1; ds.ow = ds.w;
+          ds.K = images * wp;
+          magic_div(ds.K, &ds.mul_s, &ds.sh_s);
+          magic_div(ds.ow, &ds.mul_w, &ds.sh_w);
+          aligned = true;
+        }
+      }
       // fp32 NCHW operands whose image rows are 16-byte multiples are fetched by TMA (3-D map
       // (pixel, channel, image), box 32 x 128 x 1); everything else is gathered by the producer warps
       const int64_t S = (int64_t)ds.oh * ds.ow;
@@ -615,7 +659,7 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
   int pad_blocks = 0;
   for (const PadJob& pj : plan->pads) {
     plan->pad_start.push_back(pad_blocks);
-    pad_blocks += (int)(pj.variant ? ceil_div64(pj.quads, 256) : ceil_div64(pj.total, 1024));
+    pad_blocks += (int)((pj.variant >= 1 && pj.variant <= 3) ? ceil_div64(pj.quads, 256) : ceil_div64(pj.total, 1024));
   }
   plan->pad_start.push_back(pad_blocks);
   plan->off_pads = off;      off = align_up(off + plan->pads.size() * sizeof(PadJob), 256);

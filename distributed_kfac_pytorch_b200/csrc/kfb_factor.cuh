@@ -69,6 +69,10 @@ __device__ __forceinline__ float load_elem(const void* base, int dtype, int64_t 
 // gather moves 16 bytes per lane and needs no border tests.
 // 1x1 strided convs: kw = 1, sy/sx = stride, hp x wp = oh x ow: the dense sub-sampled image, which
 // then is an ordinary NCHW operand.
+// Variant 4 - NCHW operands TMA cannot take as they are (16-bit captures, image rows that are not
+// 16-byte multiples such as 7x7 maps, misaligned views): fp32 copy with images and channels swapped,
+//   dst[c][n*wp + s] = src[n][c][s]  (s < ow_valid = h*w of the capture; wp = that rounded up to 4),
+// which is a plain 2-D [channels][rows of X] matrix for TMA, with no per-image block padding.
 struct PadJob {
   const void* src;
   float* dst;
@@ -80,7 +84,9 @@ struct PadJob {
   uint32_t mul_wp, sh_wp, mul_hp, sh_hp, mul_kw, sh_kw;   // x / wp, x / hp, x / kw by multiply-high (magic_div)
   uint32_t mul_wq, sh_wq;                                  // x / (wp/4)
   int variant;           // 0: one thread per 4 output floats; 1: (sx,kw) = (1,3), 2: (2,3), 3: (2,7): one thread
-                         // reads a source row segment once and writes the 4-pixel group of all kw planes
+                         // reads a source row segment once and writes the 4-pixel group of all kw planes;
+                         // 4: NCHW capture -> [channels][images * wp] (see below)
+  int channels;          // variant 4
   int64_t quads;         // variants 1-3: planes * hp * wp/4 threads
   int64_t total;         // planes * kw * hp * wp (< 2^31)
 };
