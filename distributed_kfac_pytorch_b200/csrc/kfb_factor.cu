@@ -6,6 +6,7 @@
 // shapes the tensor-core kernel does not take) and the finalize / pack / unpack kernels.
 // The tcgen05 SYRK lives in kfb_syrk_tc.cu and writes the same scratch convention.
 #include <algorithm>
+#include <cstdlib>
 #include <mutex>
 #include <vector>
 
@@ -441,6 +442,10 @@ int run_tri(const kfb_tri_job* jobs, int n_jobs, float scale, bool unpack, cudaS
 // planning (host)
 // ============================================================================================
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+static int64_t fused_max_rows() {
+  const char* e = getenv("KFB_SYRK_FUSE_MAX_ROWS");
+  return e ? atoll(e) : kFusedMaxRows;
+}
 
 // Division by an invariant divisor d (1 <= d < 2^31) of any x < 2^31 as a multiply-high and a shift:
 // p = 31 + ceil(log2 d), m = floor(2^p / d) + 1 gives floor(x*m / 2^p) = floor(x / d) because
@@ -633,7 +638,7 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
     }
     // short-K single-segment jobs (the 7x7-map layers: the LARGEST factors) are one work item per
     // block: their SYRK epilogue fuses scale + running average + mirror + triangle export
-    dj.fused = (tc && j.n_segments == 1 && k_total <= kFusedMaxRows) ? 1 : 0;
+    dj.fused = (tc && j.n_segments == 1 && k_total <= fused_max_rows()) ? 1 : 0;
     dj.scratch_off = plan->scratch_floats;
     if (!dj.fused) plan->scratch_floats += align_up((size_t)dj.ld_scratch * j.d, 64);
     plan->item_start.push_back(items);
@@ -682,7 +687,7 @@ std::vector<int64_t> g_plan_sig;
 
 void signature(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool tc, std::vector<int64_t>* sig) {
   sig->clear();
-  sig->push_back(n_jobs); sig->push_back(num_sms); sig->push_back(tc); sig->push_back(tma_mode()); sig->push_back(stage_mode()); sig->push_back(syrk_pair_mode());
+  sig->push_back(n_jobs); sig->push_back(num_sms); sig->push_back(tc); sig->push_back(tma_mode()); sig->push_back(stage_mode()); sig->push_back(syrk_pair_mode()); sig->push_back(fused_max_rows());
   for (int i = 0; i < n_jobs; ++i) {
     const kfb_factor_job& j = jobs[i];
     sig->push_back(j.d); sig->push_back(j.n_segments); sig->push_back(j.ld_state);
