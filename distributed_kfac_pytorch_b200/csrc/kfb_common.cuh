@@ -61,6 +61,7 @@ KFB_HIDDEN int require_context(Context** out);  // KFB_OK or error if kfb_init w
 KFB_HIDDEN int mma_mode();                      // 0 SIMT, 1 tcgen05
 KFB_HIDDEN int syrk_pair_mode();                // factor SYRK: factors of at least this many 128-wide tiles per side go to the CTA-pair (cta_group::2) kernel; 0 (default): none.  env KFB_SYRK_2CTA=<tiles>
 KFB_HIDDEN int stage_mode();                    // factor SYRK: 1 (default) im2col operands are read from zero-padded fp32 staging copies; env KFB_SYRK_STAGE=0: in place
+KFB_HIDDEN void set_stage_override(int v);       // this thread: -1 follow the environment, 0 / 1 force staging off / on
 KFB_HIDDEN int tma_mode();                      // factor SYRK: 1 (default) feeds eligible NCHW operands by TMA; env KFB_SYRK_TMA=0: gathers only
 
 static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }

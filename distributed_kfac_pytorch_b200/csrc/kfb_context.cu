@@ -40,7 +40,10 @@ int syrk_pair_mode() {
   const char* e = getenv("KFB_SYRK_2CTA");
   return e ? atoi(e) : 0;
 }
+static thread_local int g_stage_override = -1;
+void set_stage_override(int v) { g_stage_override = v; }
 int stage_mode() {
+  if (g_stage_override >= 0) return g_stage_override;
   const char* e = getenv("KFB_SYRK_STAGE");
   return !(e && e[0] == '0');
 }

@@ -55,8 +55,20 @@ int kfb_factor_update_static(const kfb_factor_job* jobs, int32_t n_jobs, float a
   KFB_CUDA(cudaGetDevice(&device));
   KFB_REQUIRE(device == ctx->device, "current device %d is not the device of the kfb context (%d)", device,
               ctx->device);
-  const size_t need = factor_workspace_bytes(jobs, n_jobs, ctx);
+  size_t need = factor_workspace_bytes(jobs, n_jobs, ctx);
   if (need == 0) return KFB_ERR_INVALID;      // the planner has set the message
+  // The fp32 staging copies of the tensor-core SYRK are a speed-up, not a requirement: if they do not
+  // fit the built-in array, plan this call without them (captures are then gathered in place).
+  struct StageGuard {
+    bool on = false;
+    ~StageGuard() { if (on) set_stage_override(-1); }
+  } guard;
+  if (need > (size_t)KFB_STATIC_SCRATCH_BYTES) {
+    set_stage_override(0);
+    guard.on = true;
+    need = factor_workspace_bytes(jobs, n_jobs, ctx);
+    if (need == 0) return KFB_ERR_INVALID;
+  }
   if (need > (size_t)KFB_STATIC_SCRATCH_BYTES)
     KFB_FAIL(KFB_ERR_WORKSPACE,
              "kfb_factor_update_static: these %d job(s) need %zu bytes of scratch but the built-in array holds "

@@ -88,3 +88,32 @@ def test_static_scratch_rejects_oversized_jobs():
         ops.factor_update_static([job], 0.9)
     torch.cuda.synchronize()
     assert float(st.abs().sum()) == 0.0       # refused before anything ran
+
+
+def test_static_scratch_drops_staging_copies_that_do_not_fit():
+    """The tensor-core SYRK normally reads im2col captures through fp32 staging copies kept in the
+    workspace (about 3x the capture for a 3x3 conv).  They are an optimisation: when they do not fit
+    the built-in array the no-alloc entry point plans the call without them instead of refusing it."""
+    N.set_ops(None)
+    ops = N.get_ops()
+    ops._enter(torch.zeros(1, device=DEV))
+    ops.set_mma_mode(1)
+    x = torch.randn(8, 64, 56, 56, generator=torch.Generator().manual_seed(3)).to(DEV)   # 6.4 MB capture
+    S = 56 * 56
+    d = 64 * 9
+
+    def job(state):
+        seg = N.Segment(N.KFB_SEG_IM2COL, x, 8, 64, 1.0 / (S * S * 8.0 * S), h=56, w=56, kernel=(3, 3), stride=(1, 1),
+                        padding=(1, 1))
+        return N.FactorJob(d, [seg], state, True, True, None)
+
+    _, ref = alloc2d(d, d, DEV, zero=True)
+    _, got = alloc2d(d, d, DEV, zero=True)
+    ops.factor_update([job(ref)], 0.95)
+    need = ops.lib.kfb_factor_workspace_bytes(ops._factor_cjobs([job(ref)])[0], 1)
+    assert need > ops.static_scratch_bytes()          # with staging it would not fit
+    ops.factor_update_static([job(got)], 0.95)
+    torch.cuda.synchronize()
+    scale = ref.abs().max().item()
+    torch.testing.assert_close(got, ref, rtol=1e-4, atol=1e-5 * scale)
+    assert torch.equal(got, got.t())
