@@ -113,6 +113,19 @@ __global__ void __launch_bounds__(256) grad_kernel(const __grid_constant__ GradB
     if (vg != 0.f) nu = fminf(1.f, sqrtf(kl_clip / fabsf(vg)));
   }
   float dot = 0.f;
+  // weight-only layers whose matrix rows are unpadded 16-byte multiples (every ResNet conv but the
+  // first): matrix and gradient are the same flat array, moved 16 bytes per thread
+  if (kMode == kWrite && j.nw == j.da && j.ld == j.da && (j.da & 3) == 0 && (((uintptr_t)j.wg | (uintptr_t)j.v) & 15) == 0) {
+#pragma unroll
+    for (int u = 0; u < kElemsPerBlock / 1024; ++u) {
+      const int64_t e = e0 + (int64_t)(u * 256 + threadIdx.x) * 4;
+      if (e >= total) break;
+      float4 v = *reinterpret_cast<const float4*>(j.v + e);
+      v.x *= nu; v.y *= nu; v.z *= nu; v.w *= nu;
+      *reinterpret_cast<float4*>(j.wg + e) = v;
+    }
+    return;
+  }
 #pragma unroll
   for (int u = 0; u < kElemsPerBlock / 256; ++u) {
     int64_t e = e0 + u * 256 + threadIdx.x;
