@@ -589,12 +589,27 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
               const bool row_ok = i < d;
               if (row_ok) {
                 const float* orow = job.state + (int64_t)i * job.ld_state + jb;
+                if (!job.seed_identity && jb + 31 < d && (((uintptr_t)orow) & 15) == 0) {
+                  // this thread's 32 old values are one 128-byte line: eight 16-byte loads (a scalar
+                  // load per value costs 32 cache wavefronts per instruction, one per lane's row)
+                  float4 o[8];
 #pragma unroll
-                for (int e = 0; e < 32; ++e) {
-                  const int j = jb + e;
-                  float old = 0.f;
-                  if (j < d) old = job.seed_identity ? (i == j ? 1.f : 0.f) : orow[e];
-                  r[e] = __float_as_uint((old * ratio + __uint_as_float(r[e]) * weight) * one_m);
+                  for (int g = 0; g < 8; ++g) o[g] = *reinterpret_cast<const float4*>(orow + 4 * g);
+#pragma unroll
+                  for (int g = 0; g < 8; ++g) {
+                    r[4 * g] = __float_as_uint((o[g].x * ratio + __uint_as_float(r[4 * g]) * weight) * one_m);
+                    r[4 * g + 1] = __float_as_uint((o[g].y * ratio + __uint_as_float(r[4 * g + 1]) * weight) * one_m);
+                    r[4 * g + 2] = __float_as_uint((o[g].z * ratio + __uint_as_float(r[4 * g + 2]) * weight) * one_m);
+                    r[4 * g + 3] = __float_as_uint((o[g].w * ratio + __uint_as_float(r[4 * g + 3]) * weight) * one_m);
+                  }
+                } else {
+#pragma unroll
+                  for (int e = 0; e < 32; ++e) {
+                    const int j = jb + e;
+                    float old = 0.f;
+                    if (j < d) old = job.seed_identity ? (i == j ? 1.f : 0.f) : orow[e];
+                    r[e] = __float_as_uint((old * ratio + __uint_as_float(r[e]) * weight) * one_m);
+                  }
                 }
                 if (job.write_state) {
                   float* srow = job.state + (int64_t)i * job.ld_state + jb;
