@@ -144,6 +144,20 @@ __device__ __forceinline__ void cp_async_arrive(uint32_t bar) {
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
 }
 
+// 256-bit global accesses (sm_100: LDG.256 / STG.256), 32-byte aligned
+__device__ __forceinline__ void ldg_v8(const float* p, float4& a, float4& b) {
+  asm volatile("ld.global.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+               : "l"(p)
+               : "memory");
+}
+__device__ __forceinline__ void stg_v8(float* p, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1,
+                                       uint32_t b2, uint32_t b3) {
+  asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0),
+               "r"(b1), "r"(b2), "r"(b3)
+               : "memory");
+}
+
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
@@ -593,8 +607,13 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
                   // this thread's 32 old values are one 128-byte line: eight 16-byte loads (a scalar
                   // load per value costs 32 cache wavefronts per instruction, one per lane's row)
                   float4 o[8];
+                  if ((((uintptr_t)orow) & 31) == 0) {
 #pragma unroll
-                  for (int g = 0; g < 8; ++g) o[g] = *reinterpret_cast<const float4*>(orow + 4 * g);
+                    for (int g = 0; g < 8; g += 2) ldg_v8(orow + 4 * g, o[g], o[g + 1]);
+                  } else {
+#pragma unroll
+                    for (int g = 0; g < 8; ++g) o[g] = *reinterpret_cast<const float4*>(orow + 4 * g);
+                  }
 #pragma unroll
                   for (int g = 0; g < 8; ++g) {
                     r[4 * g] = __float_as_uint((o[g].x * ratio + __uint_as_float(r[4 * g]) * weight) * one_m);
@@ -613,6 +632,12 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
                 }
                 if (job.write_state) {
                   float* srow = job.state + (int64_t)i * job.ld_state + jb;
+                  if (jb + 31 < d && (((uintptr_t)srow) & 31) == 0) {
+#pragma unroll
+                    for (int g = 0; g < 8; g += 2)
+                      stg_v8(srow + 4 * g, r[4 * g], r[4 * g + 1], r[4 * g + 2], r[4 * g + 3], r[4 * g + 4], r[4 * g + 5],
+                             r[4 * g + 6], r[4 * g + 7]);
+                  } else
 #pragma unroll
                   for (int g = 0; g < 8; ++g) {
                     const int j = jb + 4 * g;
