@@ -222,7 +222,7 @@ __global__ void __launch_bounds__(256) finalize_kernel(const DevJob* __restrict_
     int i = bi * 32 + li, j = bj * 32 + tx;
     float v = 0.f;
     if (i < d && j < d && j >= i) {
-      float f = job.scratch[(int64_t)i * job.ld_scratch + j];
+      float f = job.scratch[job.native ? native_index(job.T128, i, j) : (int64_t)i * job.ld_scratch + j];
       float old = job.seed_identity ? (i == j ? 1.f : 0.f) : job.state[(int64_t)i * job.ld_state + j];
       v = (old * ratio + f) * one_m;
       if (job.tri_out) job.tri_out[(int64_t)i * d - ((int64_t)i * (i - 1)) / 2 + (j - i)] = v;
@@ -640,7 +640,10 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
     // block: their SYRK epilogue fuses scale + running average + mirror + triangle export
     dj.fused = (tc && j.n_segments == 1 && k_total <= fused_max_rows()) ? 1 : 0;
     dj.scratch_off = plan->scratch_floats;
-    if (!dj.fused) plan->scratch_floats += align_up((size_t)dj.ld_scratch * j.d, 64);
+    dj.T128 = ceil_div(j.d, 128);
+    dj.native = (tc && !dj.fused) ? 1 : 0;
+    if (dj.native) plan->scratch_floats += (size_t)dj.T128 * dj.T128 * 128 * 128;
+    else if (!dj.fused) plan->scratch_floats += align_up((size_t)dj.ld_scratch * j.d, 64);
     plan->item_start.push_back(items);
     plan->fin_start.push_back(fins);
     if (!tc) items += dj.n_pairs * chunks;

@@ -46,6 +46,11 @@ struct DevJob {
   int n_chunks;          // split-K chunks over all segments
   int T32;               // 32-wide blocks per side for finalize
   int use_tc;            // 1: handled by the tcgen05 SYRK
+  int native;            // 1: the scratch accumulator is laid out the way the tensor-core epilogue holds it (a thread
+                         // owns an accumulator row): [128x128 tile (row-major grid of T128^2)][32-row quadrant q]
+                         // [32-col chunk c][4-col group g][row lane][4], so one red.v4 of a warp is 512 contiguous
+                         // bytes instead of 32 lines; finalize reads whole 32x32 blocks = one 4 KB chunk
+  int T128;              // 128-wide tiles per side
   int fused;             // 1: one K chunk, one segment: the SYRK epilogue applies the running average
                          //    itself and writes the state - no scratch, no reds, no finalize pass
 };
@@ -90,6 +95,12 @@ struct PadJob {
   int64_t quads;         // variants 1-3: planes * hp * wp/4 threads
   int64_t total;         // planes * kw * hp * wp (< 2^31)
 };
+
+// float index of element (i, j) in a DevJob::native scratch
+__host__ __device__ __forceinline__ int64_t native_index(int T128, int i, int j) {
+  const int64_t chunk = ((int64_t)((i >> 7) * T128 + (j >> 7)) * 16 + ((i >> 5) & 3) * 4 + ((j >> 5) & 3));
+  return chunk * 1024 + ((((j >> 2) & 7) * 32 + (i & 31)) << 2) + (j & 3);
+}
 
 struct TcItem {            // one unit of tensor-core SYRK work: a 2x2 block of 128-wide tiles
   int job, seg;

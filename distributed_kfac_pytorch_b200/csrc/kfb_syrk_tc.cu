@@ -668,17 +668,19 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
               continue;
             }
             if (i < d && jb + 31 >= i) {
-              float* row = job.scratch + (int64_t)i * job.ld_scratch + jb;
+              // scratch in the accumulator's own layout (DevJob::native): the 32 lanes of one red.v4
+              // are 512 contiguous bytes
+              float* cb = job.scratch + (((int64_t)((item.a0 + m) * job.T128 + (item.b0 + nn)) * 16 + q * 4 + c) << 10) + (lane << 2);
 #pragma unroll
               for (int g = 0; g < 8; ++g) {
                 const int j = jb + 4 * g;
                 if (j + 3 < d && j >= i) {
-                  red_add_v4(row + 4 * g, __uint_as_float(r[4 * g]) * weight, __uint_as_float(r[4 * g + 1]) * weight,
+                  red_add_v4(cb + g * 128, __uint_as_float(r[4 * g]) * weight, __uint_as_float(r[4 * g + 1]) * weight,
                              __uint_as_float(r[4 * g + 2]) * weight, __uint_as_float(r[4 * g + 3]) * weight);
                 } else {
 #pragma unroll
                   for (int e = 0; e < 4; ++e)
-                    if (j + e < d && j + e >= i) atomicAdd(row + 4 * g + e, __uint_as_float(r[4 * g + e]) * weight);
+                    if (j + e < d && j + e >= i) atomicAdd(cb + g * 128 + e, __uint_as_float(r[4 * g + e]) * weight);
                 }
               }
             }
