@@ -639,6 +639,9 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
     // short-K single-segment jobs (the 7x7-map layers: the LARGEST factors) are one work item per
     // block: their SYRK epilogue fuses scale + running average + mirror + triangle export
     dj.fused = (tc && j.n_segments == 1 && k_total <= fused_max_rows()) ? 1 : 0;
+    // a fused job's packed triangle is exported from its finished state by the (coalesced) pack kernel
+    // after the SYRK rather than row by row from the epilogue's registers
+    if (dj.fused && j.write_state) dj.tri_out = nullptr;
     dj.scratch_off = plan->scratch_floats;
     dj.T128 = ceil_div(j.d, 128);
     dj.native = (tc && !dj.fused) ? 1 : 0;
@@ -721,7 +724,8 @@ static int cached_plan(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool
       const kfb_factor_job& j = jobs[i];
       KFB_REQUIRE(j.state, "factor job %d: null state", i);
       DevJob& dj = g_plan.jobs[i];
-      dj.state = j.state; dj.seed_identity = j.seed_identity; dj.write_state = j.write_state; dj.tri_out = j.tri_out;
+      dj.state = j.state; dj.seed_identity = j.seed_identity; dj.write_state = j.write_state;
+      dj.tri_out = (dj.fused && j.write_state) ? nullptr : j.tri_out;
       for (int k = 0; k < j.n_segments; ++k) {
         KFB_REQUIRE(j.segments[k].data, "factor job %d segment %d: null data", i, k);
         DevSegment& ds = g_plan.segs[dj.seg_start + k];
@@ -755,7 +759,17 @@ int factor_update_with(const kfb_factor_job* jobs, int n_jobs, float alpha, Cont
   if (rc) return rc;
   rc = launch_syrk(*plan, workspace, ctx, alpha, stream);
   if (rc) return rc;
-  return launch_finalize(*plan, workspace, alpha, stream);
+  rc = launch_finalize(*plan, workspace, alpha, stream);
+  if (rc) return rc;
+  std::vector<kfb_tri_job> deferred;
+  for (int i = 0; i < n_jobs; ++i)
+    if (plan->jobs[i].fused && jobs[i].write_state && jobs[i].tri_out) {
+      kfb_tri_job t;
+      t.tri = jobs[i].tri_out; t.state = jobs[i].state; t.ld_state = jobs[i].ld_state; t.d = jobs[i].d;
+      deferred.push_back(t);
+    }
+  if (!deferred.empty()) return run_tri(deferred.data(), (int)deferred.size(), 1.f, false, stream);
+  return KFB_OK;
 }
 
 size_t factor_workspace_bytes(const kfb_factor_job* jobs, int n_jobs, Context* ctx) {
