@@ -315,6 +315,15 @@ def run_ours(args):
         'stages_ms': {'factor_update_call': factor_ms, 'precondition_call': precond_ms,
                       'syevd_per_inverse_step': syevd_ms_total / n_inv_steps},
     }
+    if dist_on:
+        # every rank's own stage times (the step is as slow as the slowest rank: the allocator's n^3
+        # cost model is parity contract, syevd's real cost is closer to linear in n)
+        mine = torch.tensor([syevd_ms_total / n_inv_steps, factor_ms or 0.0, precond_ms or 0.0], device=device)
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        torch.distributed.all_gather(allr, mine)
+        out['stages_ms_per_rank'] = {'syevd_per_inverse_step': [round(float(t[0]), 2) for t in allr],
+                                     'factor_update_call': [round(float(t[1]), 3) for t in allr],
+                                     'precondition_call': [round(float(t[2]), 3) for t in allr]}
     pk = peaks()
     tf32_peak = pk['bf16_sustained'] / 2.0
     if precond_ms:
