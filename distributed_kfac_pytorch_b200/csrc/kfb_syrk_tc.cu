@@ -1,28 +1,30 @@
 // Factor SYRK on the 5th-generation tensor cores:  F += w * X^T X  for one 256x256 block (2x2
-// tiles of 128) of the upper triangle and one K chunk per work item, X read IN PLACE from the
-// captured NCHW tensors (implicit im2col: the unfolded matrix of kfac/layers/conv.py:50-70 is
-// never materialised).  Blocking 2x2 halves the operand gathering per FLOP (4 tiles feed 4
-// tile products instead of 2 tiles per product) and the shared-memory traffic per MMA.
+// tiles of 128) of the upper triangle and one K chunk per work item.  X is the im2col-unfolded
+// activation (kfac/layers/conv.py:50-70) or the NCHW output gradient viewed as (N*S) x C; the
+// unfolded matrix is never materialised.  Blocking 2x2 halves the operand traffic per FLOP (4 tiles
+// feed 4 tile products instead of 2 tiles per product) and the shared-memory traffic per MMA.
 //
 //   warps 0-3   epilogue: tcgen05.ld -> x weight -> red.global.add.v4.f32 into the job's scratch
+//               (laid out the way the accumulators are held, DevJob::native), or the fused finish
 //   warp  0     lane 0 is also the MMA issuer: tcgen05.mma.kind::tf32, M=128, N=256 (or 128), K=8;
 //               the block's four fp32 accumulators fill all 512 TMEM columns, so issuing and
 //               draining alternate anyway; a diagonal block loads its two tiles once for both
 //               operands and skips the lower-left product.  (20 warps = 5 per scheduler leave 96
 //               registers per thread; a 21st warp would cap every thread at 80.)
-//   warps 4-19  producers: gather X^T tiles (128 features x 32 rows of X, K-major) from global
-//               memory straight into the 128B-swizzled UMMA shared-memory layout
-//               - NCHW operands with 16-byte alignable rows: 128-bit loads/stores
-//               - im2col operands: read from a zero-padded fp32 staging copy (kfb_factor.cu, PadJob),
-//                 one 4-byte cp.async per element, coalesced along the output row; the copies of a
-//                 whole stage are in flight per lane and report to the stage's mbarrier themselves
-//                 (cp.async.mbarrier.arrive), so the producers never wait for data
-//               - the same from the capture in place (KFB_SYRK_STAGE=0, NCHW operands with odd row
-//                 lengths): cp.async with zero fill under a per-lane validity bitmask over (ky,kx)
-//               - fp32 NCHW operands with 16-byte image rows and >= 32 pixels per image skip the
-//                 gather: one producer lane issues a TMA box (32 pixels x 128 channels x 1 image,
-//                 SWIZZLE_128B) per tile and stage; K runs over per-image 32-row blocks, the tail
-//                 of an image's last block is zero-filled by the TMA unit
+//   warps 4-19  producers: bring X^T tiles (128 features x 32 rows of X, K-major, 128-byte swizzle)
+//               into shared memory, never through registers unless the element type forces it:
+//               - fp32 NCHW operands with 16-byte image rows and >= 32 pixels per image: one lane
+//                 issues a TMA box (32 pixels x 128 channels x 1 image) per tile and stage; K runs
+//                 over per-image 32-pixel blocks, the tail of an image's last block is zero-filled
+//                 by the TMA unit.  NCHW operands TMA cannot read (7x7 maps, 16-bit captures) are
+//                 first copied to fp32 [channels][images x pixels] (kfb_factor.cu, PadJob variant 4)
+//               - kxk convs: from the per-kx stride-compacted zero-padded staging planes (PadJob):
+//                 one 16-byte cp.async.cg per lane (four output pixels of one tap), a whole stage per
+//                 lane in flight, completion reported by cp.async.mbarrier.arrive - no border masks,
+//                 no waiting for data
+//               - fallback, capture in place (KFB_SYRK_STAGE=0 / shapes the staging refuses): 4-byte
+//                 cp.async with zero fill under a per-lane validity bitmask over (ky,kx); 16-bit
+//                 captures in place are widened in registers
 // Operands stay fp32 in shared memory; kind::tf32 reads the top 19 bits, so no conversion pass.
 #include <algorithm>
 #include <cstdlib>
@@ -58,8 +60,7 @@ struct Cfg {
   static constexpr int kFirstProducer = kPair ? 5 : 4;         // first producer warp
   static constexpr int kThreads = 32 * (kFirstProducer + kProducerWarps);
   static constexpr int kBarOff = kStages * kStageBytes;
-  static constexpr int kTableOff = kBarOff + 256;              // 16 warps x 32 row offsets
-  static constexpr int kSmemBytes = kBarOff + 1024 + 256 + kProducerWarps * 128;
+  static constexpr int kSmemBytes = kBarOff + 1024 + 256;       // 1 KB alignment slack + barriers
 };
 
 // A tile row (= one feature of X) is described by ONE packed word: (element offset << 6) | bit,
@@ -114,22 +115,13 @@ __device__ __forceinline__ int snake_item(int round, int total) {
 __device__ __forceinline__ void sts_f32(uint32_t addr, float v) {
   asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
 }
-__device__ __forceinline__ void sts_u32(uint32_t addr, uint32_t v) {
-  asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
-}
-__device__ __forceinline__ void lds_v4(uint32_t addr, uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d) {
-  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(addr) : "memory");
-}
 __device__ __forceinline__ void sts_v4(uint32_t addr, float4 v) {
   asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
-// Asynchronous 4-byte global -> shared copies (LDGSTS): no register staging, so a lane keeps a whole
-// stage (32 elements) in flight instead of waiting for every batch of loads before it may store.
-// src_bytes = 0 writes a zero without touching global memory (borders, padding rows, K tails).
-__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
-}
+// Asynchronous global -> shared copies (LDGSTS): no register staging, so a lane keeps a whole stage
+// in flight instead of waiting for every batch of loads before it may store.  src_bytes = 0 writes
+// zeros without touching global memory (borders, padding rows, K tails).
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
 }
@@ -168,7 +160,7 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
                                                                         const TcItem* __restrict__ items, int n_items, float alpha,
                                                                         const CUtensorMap* __restrict__ tmaps) {
   using C = Cfg<kPair>;
-  constexpr int kStages = C::kStages, kStageBytes = C::kStageBytes, kSlots = C::kSlots, kTableOff = C::kTableOff;
+  constexpr int kStages = C::kStages, kStageBytes = C::kStageBytes, kSlots = C::kSlots;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint64_t* full = (uint64_t*)(smem + C::kBarOff);
