@@ -5,6 +5,7 @@
 #include <stdlib.h>
 
 #include <algorithm>
+#include <cmath>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -176,12 +177,35 @@ struct BatchPlan {
   size_t group_off = 0, total = 0;
 };
 
-// measured on B200 (tools/try_syev_batched.py): the batched solver wins for n <= 512 and, with
-// enough matrices to amortise over, up to n = 1024; above that syevd per matrix is faster
+// Which same-size groups go to cusolverDnXsyevBatched.  Measured on B200 (tools/sweep_syev_batched.py,
+// tools/bench_syevd.py): the batched solver's time is almost flat in the batch count (it fills the GPU
+// whatever the count: b0 + b1*count), syevd's is ~linear in n and per matrix, and the two do not
+// overlap well (the batched grids hold the SMs the lanes' microsecond kernels wait for), so the batch
+// total is close to  sum(batched groups) + sum(lane work) / 1.33.  A group is batched when that is
+// cheaper than leaving its matrices on the lanes.  ResNet-50 on one GPU: 64..512 and 1024 (19 of them)
+// batched, 576 x3, 1152 x4, 2048 x7, 2304 x6, 4608 x3 on the lanes; on eight GPUs the per-rank groups
+// are small and e.g. two 512s (16 ms batched, 8 ms on a lane) stay on the lanes.
+double interp_loglog(int d, const double* tab) {
+  static const double kD[10] = {64, 128, 256, 512, 576, 1024, 1152, 2048, 2304, 4608};
+  if (d <= kD[0]) return tab[0] * d / kD[0];
+  for (int i = 1; i < 10; ++i)
+    if (d <= kD[i]) {
+      const double t = (std::log((double)d) - std::log(kD[i - 1])) / (std::log(kD[i]) - std::log(kD[i - 1]));
+      return std::exp(std::log(tab[i - 1]) + t * (std::log(tab[i]) - std::log(tab[i - 1])));
+    }
+  return tab[9] * std::pow(d / kD[9], 2.0);
+}
 bool batched_wins(int d, size_t count) {
-  static const int big_max = []() { const char* e = getenv("KFB_SYEV_BATCH_MAX_D"); return e ? atoi(e) : 1024; }();
+  static const double kSingle[10] = {0.82, 1.92, 2.17, 5.3, 6.4, 11.3, 13.6, 25.0, 31.0, 88.7};        // syevd, ms
+  static const double kB0[10] = {0.35, 0.70, 3.4, 16.2, 25.6, 44.5, 55.0, 123.3, 143.0, 440.0};         // batched, ms
+  static const double kB1[10] = {0.001, 0.003, 0.025, 0.19, 0.37, 1.1, 1.5, 2.5, 4.6, 6.0};             // + per matrix
+  static const int big_max = []() { const char* e = getenv("KFB_SYEV_BATCH_MAX_D"); return e ? atoi(e) : 0; }();
   static const int big_min_count = []() { const char* e = getenv("KFB_SYEV_BATCH_MIN_COUNT"); return e ? atoi(e) : 8; }();
-  return count >= 2 && (d <= 512 || (d <= big_max && (int)count >= big_min_count));
+  if (count < 2) return false;
+  if (big_max > 0) return d <= 512 || (d <= big_max && (int)count >= big_min_count);   // explicit thresholds
+  const double batched = interp_loglog(d, kB0) + interp_loglog(d, kB1) * (double)count;
+  const double lanes = interp_loglog(d, kSingle) * (double)count / 1.33;
+  return batched < lanes;
 }
 
 int make_plan(kfb::Context* ctx, LanePool* pool, const kfb_syevd_job* jobs, int n, BatchPlan* plan) {

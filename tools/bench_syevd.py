@@ -32,7 +32,7 @@ def timed(fn, reps=2):
 def main():
     ops = N.get_ops()
     ops._enter(torch.zeros(1, device=DEV))
-    for d in (64, 128, 256, 512, 576, 1024, 1152, 2048, 2304, 4608):
+    for d in (() if '--batch-only' in sys.argv else (64, 128, 256, 512, 576, 1024, 1152, 2048, 2304, 4608)):
         job = make(d)
         ms = timed(lambda: ops.syevd(*job))
         ms_t = timed(lambda: torch.linalg.eigh(job[0]))
@@ -43,8 +43,9 @@ def main():
     dims = [x for pair in models.resnet_factor_dims('resnet50') for x in pair]
     jobs = [make(d) for d in dims]
     print('resnet50: %d factors, sum d^3 = %.3g' % (len(dims), sum(float(d) ** 3 for d in dims)))
-    print('  one at a time: %.1f ms' % timed(lambda: [ops.syevd(*j) for j in jobs], reps=1))
-    print('  syevd_batch  : %.1f ms' % timed(lambda: ops.syevd_batch(jobs), reps=1))
+    if '--batch-only' not in sys.argv:
+        print('  one at a time: %.1f ms' % timed(lambda: [ops.syevd(*j) for j in jobs], reps=1))
+    print('  syevd_batch  : %.1f ms' % timed(lambda: ops.syevd_batch(jobs), reps=2))
 
 
 if __name__ == '__main__':
