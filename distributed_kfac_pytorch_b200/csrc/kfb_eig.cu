@@ -1,5 +1,6 @@
 // Eigendecomposition (cuSOLVER syevd: the one library call of the path) and the small
 // kernels around it: eigenvalue clip, transpose, outer-product reciprocal.
+#include <cuda.h>
 #include <cusolverDn.h>
 
 #include <stdlib.h>
@@ -129,18 +130,87 @@ struct LanePool {
   Lane grouped;                 // stream/handle for the XsyevBatched groups
   cusolverDnParams_t params = nullptr;
   cudaEvent_t start = nullptr;
+  int n_green = 0;              // lanes [0, n_green) run in green contexts
   bool ready = false;
 };
 LanePool g_pools[64];
 std::mutex g_pool_mu;
+
+// How many syevd lanes to run: KFB_SYEVD_LANES, else three - one host thread per lane next to this
+// process's main thread, fewer when the node's cores are shared with many ranks (LOCAL_WORLD_SIZE,
+// set by torchrun).  With green contexts the lanes also split the SMs, and the large factors need
+// SMs: ResNet-50 on one B200 takes 646 ms on ordinary streams and 560 / 434 / 491 / 608 / 518 / 737
+// ms with 2 / 3 / 4 / 5 / 6 / 8 green-context lanes (64 / 48 / 32 / 24 / 24 / 16 SMs each).
+int lane_count() {
+  static const int n = []() {
+    if (const char* e = getenv("KFB_SYEVD_LANES")) return std::min(kMaxLanes, std::max(1, atoi(e)));
+    int local_world = 1;
+    if (const char* e = getenv("LOCAL_WORLD_SIZE")) local_world = std::max(1, atoi(e));
+    const int cores = (int)std::max(1u, std::thread::hardware_concurrency());
+    return std::min(3, std::max(2, cores / local_world - 1));
+  }();
+  return n;
+}
+
+// Streams for the syevd lanes inside GREEN CONTEXTS (CUDA >= 12.4): each lane gets its own context
+// with a slice of the SMs.  syevd is bound by its host-side panel loop (thousands of microsecond
+// kernels), and launches into ONE context serialise across threads - two lanes on ordinary streams
+// reach 1.33x, more add nothing - while launches into different green contexts do not: 24 syevd of
+// n = 1024 take 271 ms on one stream, 212 ms on four ordinary streams, 94 ms on four green contexts
+// of 32 SMs, 67 ms on eight of 16 SMs (tools/try_green_ctx.py).  Events of the primary context work
+// on these streams.  Returns how many streams were created (0: not available, use ordinary streams).
+int create_green_streams(int device, int num_sms, int want, cudaStream_t* out) {
+  if (getenv("KFB_SYEVD_GREEN") && getenv("KFB_SYEVD_GREEN")[0] == '0') return 0;
+  typedef CUresult (*GetDev)(CUdevice*, int);
+  typedef CUresult (*GetRes)(CUdevice, CUdevResource*, CUdevResourceType);
+  typedef CUresult (*Split)(CUdevResource*, unsigned int*, const CUdevResource*, CUdevResource*, unsigned int, unsigned int);
+  typedef CUresult (*GenDesc)(CUdevResourceDesc*, CUdevResource*, unsigned int);
+  typedef CUresult (*GreenCreate)(CUgreenCtx*, CUdevResourceDesc, CUdevice, unsigned int);
+  typedef CUresult (*GreenStream)(CUstream*, CUgreenCtx, unsigned int, int);
+  void* fn[6] = {};
+  const char* names[6] = {"cuDeviceGet", "cuDeviceGetDevResource", "cuDevSmResourceSplitByCount",
+                          "cuDevResourceGenerateDesc", "cuGreenCtxCreate", "cuGreenCtxStreamCreate"};
+  for (int i = 0; i < 6; ++i) {
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint(names[i], &fn[i], cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess ||
+        !fn[i]) {
+      cudaGetLastError();
+      return 0;
+    }
+  }
+  CUdevice dev;
+  CUdevResource sm;
+  if (((GetDev)fn[0])(&dev, device) != CUDA_SUCCESS) return 0;
+  if (((GetRes)fn[1])(dev, &sm, CU_DEV_RESOURCE_TYPE_SM) != CUDA_SUCCESS) return 0;
+  // equal slices, a multiple of 8 SMs each, at most 64
+  unsigned int per = (unsigned int)std::min(64, std::max(8, (num_sms / std::max(1, want)) & ~7));
+  CUdevResource groups[kMaxLanes], rest;
+  unsigned int n = (unsigned int)std::min(want, kMaxLanes);
+  if (((Split)fn[2])(groups, &n, &sm, &rest, 0, per) != CUDA_SUCCESS || n == 0) return 0;
+  int made = 0;
+  for (unsigned int i = 0; i < n; ++i) {
+    CUdevResourceDesc desc;
+    CUgreenCtx gctx;
+    CUstream st;
+    if (((GenDesc)fn[3])(&desc, &groups[i], 1) != CUDA_SUCCESS) break;
+    if (((GreenCreate)fn[4])(&gctx, desc, dev, CU_GREEN_CTX_DEFAULT_STREAM) != CUDA_SUCCESS) break;
+    if (((GreenStream)fn[5])(&st, gctx, CU_STREAM_NON_BLOCKING, 0) != CUDA_SUCCESS) break;
+    out[made++] = (cudaStream_t)st;          // the green context lives as long as the process
+  }
+  return made;
+}
 
 int get_pool(kfb::Context* ctx, LanePool** out) {
   std::lock_guard<std::mutex> lock(g_pool_mu);
   LanePool& p = g_pools[ctx->device];
   if (!p.ready) {
     KFB_CUDA(cudaEventCreateWithFlags(&p.start, cudaEventDisableTiming));
+    cudaStream_t green[kMaxLanes] = {};
+    p.n_green = create_green_streams(ctx->device, ctx->num_sms, lane_count(), green);
     for (int i = 0; i <= kMaxLanes; ++i) {
       Lane& l = i < kMaxLanes ? p.lanes[i] : p.grouped;
+      if (i < p.n_green) l.stream = green[i];
+      else
       KFB_CUDA(cudaStreamCreateWithFlags(&l.stream, cudaStreamNonBlocking));
       KFB_CUDA(cudaEventCreateWithFlags(&l.done, cudaEventDisableTiming));
       if (cusolverDnCreate(&l.handle) != CUSOLVER_STATUS_SUCCESS)
@@ -195,7 +265,7 @@ double interp_loglog(int d, const double* tab) {
     }
   return tab[9] * std::pow(d / kD[9], 2.0);
 }
-bool batched_wins(int d, size_t count) {
+bool batched_wins(int d, size_t count, double lane_speedup) {
   static const double kSingle[10] = {0.82, 1.92, 2.17, 5.3, 6.4, 11.3, 13.6, 25.0, 31.0, 88.7};        // syevd, ms
   static const double kB0[10] = {0.35, 0.70, 3.4, 16.2, 25.6, 44.5, 55.0, 123.3, 143.0, 440.0};         // batched, ms
   static const double kB1[10] = {0.001, 0.003, 0.025, 0.19, 0.37, 1.1, 1.5, 2.5, 4.6, 6.0};             // + per matrix
@@ -204,7 +274,7 @@ bool batched_wins(int d, size_t count) {
   if (count < 2) return false;
   if (big_max > 0) return d <= 512 || (d <= big_max && (int)count >= big_min_count);   // explicit thresholds
   const double batched = interp_loglog(d, kB0) + interp_loglog(d, kB1) * (double)count;
-  const double lanes = interp_loglog(d, kSingle) * (double)count / 1.33;
+  const double lanes = interp_loglog(d, kSingle) * (double)count / lane_speedup;
   return batched < lanes;
 }
 
@@ -223,7 +293,9 @@ int make_plan(kfb::Context* ctx, LanePool* pool, const kfb_syevd_job* jobs, int 
     size_t j = i;
     while (j < order.size() && jobs[order[j]].d == jobs[order[i]].d) ++j;
     const int d = jobs[order[i]].d;
-    if (batched_wins(d, j - i)) {
+    // measured aggregate speed-up of the lanes: 1.33 on ordinary streams, 2.9 / 4.0 with 4 / 8 green contexts
+    const double lane_speedup = pool->n_green >= 8 ? 4.0 : pool->n_green >= 4 ? 2.9 : pool->n_green >= 3 ? 2.2 : pool->n_green >= 2 ? 1.6 : 1.33;
+    if (batched_wins(d, j - i, lane_speedup)) {
       Group g;
       g.d = d;
       g.idx.assign(order.begin() + i, order.begin() + j);
@@ -245,11 +317,8 @@ int make_plan(kfb::Context* ctx, LanePool* pool, const kfb_syevd_job* jobs, int 
     i = j;
   }
   // longest-processing-time placement of the single solves on the lanes (descending d already)
-  static const int lane_cap = []() {
-    const char* e = getenv("KFB_SYEVD_LANES");     // tuning knob
-    int v = e ? atoi(e) : 2;              // measured: no gain beyond 2 (the launch path serialises)
-    return std::min(kMaxLanes, std::max(1, v));
-  }();
+  // without green contexts more than two lanes add nothing (one context's launch path serialises)
+  const int lane_cap = pool->n_green > 0 ? pool->n_green : std::min(lane_count(), getenv("KFB_SYEVD_LANES") ? kMaxLanes : 2);
   const int n_lanes = std::min<int>(lane_cap, std::max<size_t>(1, singles.size()));
   plan->lanes.assign(n_lanes, {});
   std::vector<double> load(n_lanes, 0.0);
