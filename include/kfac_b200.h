@@ -152,7 +152,11 @@ KFB_API int kfb_syevd(const float* factor, int64_t ld_factor, int32_t d,
 /* Many eigendecompositions at once, still all cuSOLVER: factors of the same size (small and medium
  * ones, where it measures faster) are solved together by cusolverDnXsyevBatched; the rest are
  * spread, longest first, over a small pool of internal worker lanes - one host thread, CUDA stream
- * and cuSOLVER handle each - so that their host-driven panel loops overlap.  Everything starts after
+ * and cuSOLVER handle each - so that their host-driven panel loops overlap.  Where the driver has
+ * green contexts (CUDA >= 12.4) every lane's stream lives in its own green context with an equal
+ * share of the SMs, created the first time the call runs on a device and kept for the life of the
+ * process: launches into one context serialise across threads, launches into different green
+ * contexts do not (KFB_SYEVD_GREEN=0: ordinary streams).  Everything starts after
  * the work already queued on `stream` and `stream` waits for all of it, so to the caller it behaves
  * like one asynchronous call on `stream`.  Results match kfb_syevd job by job (eigenvectors up to
  * sign). */
