@@ -13,7 +13,7 @@ follow the 10-step cadence (1 factor + eigendecomposition step, 9 ordinary steps
   e2e    the same steps through the public API with HOST buffers: every step's inputs (the
          gradients; on factor steps also every layer's activation and output gradient) are
          copied from pinned host memory inside the timed region and the step's result
-         (the device v.g scalar) is read back.
+         (the rewritten gradients of every layer, 102 MB, and the v.g scalar) is read back.
   --impl reference   the CPU oracle (oracle/kfac_oracle.py, a pinned restatement of the
          reference, which is pure Python/torch) on the host cores, same cadence.
 
@@ -56,17 +56,31 @@ def parse_args():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
     ap.add_argument('--no-train', action='store_true')
+    ap.add_argument('--no-comm-methods', action='store_true')
     ap.add_argument('--mma-mode', type=int, default=1)
     return ap.parse_args()
 
 
 def peaks():
+    """Roofline denominators: MEASURED_PEAKS.json (driver-written: HBM, bf16) and the TF32 figure
+    measured the same way on this pool by tools/measure_tf32_peak.py (profiles/r2_tf32_peak.json)."""
     path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
     if os.path.exists(path):
         p = json.load(open(path))
-        return dict(hbm_gbs=p['hbm_gbs'], bf16_burst=p['bf16_tflops'],
-                    bf16_sustained=p.get('bf16_tflops_sustained', p['bf16_tflops']), source='measured')
-    return dict(hbm_gbs=6650.0, bf16_burst=1590.0, bf16_sustained=1400.0, source='fallback')
+        out = dict(hbm_gbs=p['hbm_gbs'], bf16_burst=p['bf16_tflops'],
+                   bf16_sustained=p.get('bf16_tflops_sustained', p['bf16_tflops']), source='measured')
+    else:
+        out = dict(hbm_gbs=6650.0, bf16_burst=1590.0, bf16_sustained=1400.0, source='fallback')
+    tpath = os.path.join(ROOT, 'profiles', 'r2_tf32_peak.json')
+    if os.path.exists(tpath):
+        t = json.load(open(tpath))
+        out.update(tf32_burst=t['tf32_tflops'], tf32_sustained=t['tf32_tflops_sustained'],
+                   tf32_source='measured: cuBLAS TF32 8192^3 on this pool (tools/measure_tf32_peak.py, '
+                               'profiles/r2_tf32_peak.json)')
+    else:
+        out.update(tf32_burst=out['bf16_burst'] / 2, tf32_sustained=out['bf16_sustained'] / 2,
+                   tf32_source='%s bf16 / 2 (no TF32 measurement found)' % out['source'])
+    return out
 
 
 class ClockSampler(object):
@@ -132,6 +146,22 @@ def comm_kwargs(name):
     return {'comm-opt': dict(comm_method=kfac.CommMethod.COMM_OPT),
             'mem-opt': dict(comm_method=kfac.CommMethod.MEM_OPT),
             'hybrid-opt': dict(comm_method=kfac.CommMethod.HYBRID_OPT, grad_worker_fraction=0.5)}[name]
+
+
+def fresh_kfac(args, method, device, world):
+    """A new model (same seed, same weights) with its own KFAC in the given CommMethod; parameter
+    gradients exist (zeros) so that restore_grads() can fill them."""
+    import distributed_kfac_pytorch_b200 as kfac
+    model = build_model(args.model).to(device)
+    kw = dict(KFAC_KW, **comm_kwargs(method))
+    kw['lr'] = KFAC_KW['lr'] * world
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        pre = kfac.KFAC(model, **kw)
+    for p in model.parameters():
+        p.grad = torch.zeros_like(p)
+    return model, pre
 
 
 def capture(model, pre, x, y):
@@ -253,6 +283,8 @@ def run_ours(args):
     ops._enter(torch.zeros(1, device=device))
     ops.set_mma_mode(args.mma_mode)
 
+    parity_world = run_parity_world(kfac, device, rank, world) if dist_on else None
+
     model = build_model(args.model).to(device)
     kw = dict(KFAC_KW, **comm_kwargs(args.comm_method))
     kw['lr'] = KFAC_KW['lr'] * world
@@ -325,7 +357,10 @@ def run_ours(args):
                                      'factor_update_call': [round(float(t[1]), 3) for t in allr],
                                      'precondition_call': [round(float(t[2]), 3) for t in allr]}
     pk = peaks()
-    tf32_peak = pk['bf16_sustained'] / 2.0
+    # both stages are timed per call with the GPU otherwise nearly idle (1965 MHz in the clocks sample),
+    # i.e. "a kernel timed alone": the burst figure is the honest denominator; the sustained one (taken
+    # at ~1.1 GHz under a 4 s power-capped loop) is reported beside it
+    tf32_peak = pk['tf32_burst']
     if precond_ms:
         ach = work['precond_flops'] / (precond_ms * 1e-3) / 1e12
         out['roofline'] = {'kernel': 'precondition GEMM chain (4 grouped stages + pack)', 'bound': 'tensor',
@@ -333,12 +368,14 @@ def run_ours(args):
                            # dram__bytes_read+write summed over the four GEMM launches of one step, ncu
                            # --set full, profiles/r1_tc_kernels_ncu.txt (algorithmic minimum 921.5 MB)
                            'traffic': NCU_TRAFFIC.get(args.model, {}).get('precondition'),
-                           'peak_source': '%s bf16 sustained / 2 (TF32 runs at half the bf16 rate)' % pk['source']}
+                           'peak_source': pk['tf32_source'] + ', burst',
+                           'peak_sustained': pk['tf32_sustained'], 'frac_of_sustained': ach / pk['tf32_sustained']}
     if factor_ms:
         ach = work['syrk_flops'] / (factor_ms * 1e-3) / 1e12
         gbs = work['factor_bytes'] / (factor_ms * 1e-3) / 1e9
         out['roofline_factor'] = {'kernel': 'factor stage: staging copies + SYRK + finalize', 'bound': 'tensor', 'achieved': ach,
                                   'peak': tf32_peak, 'unit': 'TFLOP/s', 'frac': ach / tf32_peak,
+                                  'peak_sustained': pk['tf32_sustained'], 'frac_of_sustained': ach / pk['tf32_sustained'],
                                   'hbm_gbs': gbs, 'hbm_frac': gbs / pk['hbm_gbs'],
                                   'traffic': NCU_TRAFFIC.get(args.model, {}).get('syrk')}
 
@@ -346,13 +383,174 @@ def run_ours(args):
         out['e2e'] = run_e2e(args, pre, caps, grads, device, dist_on)
     if not args.no_train:
         out['train'] = run_train(args, model, pre, x, y, device, dist_on, world)
+    ok = True
+    if dist_on:
+        out['parity_world'] = parity_world
+        ok = ok and parity_world['ok']
+        if not args.no_comm_methods:
+            out['comm_methods'] = run_comm_methods(args, caps, grads, device, world, rank)
+            ok = ok and out['comm_methods']['agree_with_comm_opt']
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        out['cpu_baseline'] = run_cpu_oracle(pre, caps, grads, cycles=1)
+        out['cpu_baseline'], oracle = run_cpu_oracle(pre, caps, grads, cycles=1)
+        out['parity'] = run_parity(args, caps, grads, device, oracle)
+        ok = ok and out['parity']['within_north_star_tol']
     sampler.stop()
     if rank == 0:
         print(json.dumps(out))
+        sys.stdout.flush()
     if dist_on:
         torch.distributed.destroy_process_group()
+    if not ok:
+        sys.stderr.write('bench.py: a parity check failed (see "parity" / "parity_world" / "comm_methods")\n')
+        sys.exit(3)
+
+
+def run_parity_world(kfac, device, rank, world):
+    """Before anything is timed: the N ranks of THIS launch replay the 3-step SmallCNN run that the
+    unmodified reference produced on N gloo ranks (tests/golden/cnn_world{N}.pt) in all three
+    CommMethods - kernels + slab views + NCCL - and compare assignment (bit-exact), factors
+    (rtol 1e-3) and preconditioned gradients (rtol 1e-2 / atol 1e-4), plus agreement across ranks."""
+    sys.path.insert(0, os.path.join(ROOT, 'tests'))
+    import world_replay
+    res = {'N': world, 'methods': {}, 'ok': True}
+    path = os.path.join(world_replay.GOLDEN, 'cnn_world%d.pt' % world)
+    if not os.path.exists(path):
+        return dict(res, ok=False, error='no golden for world %d' % world)
+    gold = world_replay.load_world_golden(world)
+    flags = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        for name, frac in world_replay.METHODS:
+            entry = {}
+            try:
+                rec = world_replay.replay(kfac, name, frac, device, rank)
+                worst_g, worst_f = world_replay.compare(rec, gold[name])
+                mine = torch.cat([w.flatten() for w, _ in rec['steps'][-1]['grads_out']]).to(device)
+                ref = mine.clone()
+                torch.distributed.broadcast(ref, src=0)
+                spread = (mine - ref).abs().max()
+                torch.distributed.all_reduce(spread, op=torch.distributed.ReduceOp.MAX)
+                entry = {'grad_max_abs': worst_g, 'factor_max_abs': worst_f, 'cross_rank_max_abs': spread.item(),
+                         'ok': spread.item() <= 1e-6}
+            except AssertionError as e:
+                entry = {'ok': False, 'error': str(e).splitlines()[0][:200]}
+            flag = torch.tensor([1.0 if entry['ok'] else 0.0], device=device)
+            torch.distributed.all_reduce(flag, op=torch.distributed.ReduceOp.MIN)
+            entry['ok'] = bool(flag.item() > 0.5)
+            res['methods'][name] = entry
+            res['ok'] = res['ok'] and entry['ok']
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = flags
+    return res
+
+
+def run_comm_methods(args, caps, grads, device, world, rank):
+    """configs[2]: the same captures and cadence under MEM_OPT and HYBRID_OPT(0.5) on the ranks of
+    this launch: ms/step (max over ranks) and, at the headline shape, agreement of the rewritten
+    gradients with COMM_OPT's after the first (factor + eigendecomposition) step and an ordinary one
+    (the reference's three strategies yield identical gradients)."""
+    res = {'agree_with_comm_opt': True}
+    snaps = {}
+    for method in ('comm-opt', 'mem-opt', 'hybrid-opt'):
+        model, pre = fresh_kfac(args, method, device, world)
+        snap = []
+        for i in range(2):
+            feed(pre, caps)
+            restore_grads(pre, grads)
+            pre.step()
+            snap.append(torch.cat([l.module.weight.grad.flatten() for l in pre.layers]).clone())
+        snaps[method] = snap
+        if method != 'comm-opt':
+            for i in range(2, CADENCE):
+                feed(pre, caps)
+                restore_grads(pre, grads)
+                pre.step()
+            barrier_sync(True)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(args.steps):
+                feed(pre, caps)
+                restore_grads(pre, grads)
+                pre.step()
+            e1.record()
+            barrier_sync(True)
+            ms = max_over_ranks(e0.elapsed_time(e1), device, True) / args.steps
+            ref = snaps['comm-opt']
+            scale = max(float(r.abs().max()) for r in ref)
+            diff = torch.stack([(a - b).abs().max() for a, b in zip(snap, ref)]).max()
+            # tolerance of north_star's gradient check, against COMM_OPT on the same rank
+            viol = sum(int(((a - b).abs() > 1e-4 + 1e-2 * b.abs()).sum()) for a, b in zip(snap, ref))
+            t = torch.tensor([float(diff), float(viol)], device=device, dtype=torch.float64)
+            torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+            res[method] = {'ms_per_step': ms, 'grad_max_abs_vs_comm_opt': t[0].item(),
+                           'grad_max_abs': scale, 'violations_rtol1e-2_atol1e-4': int(t[1].item())}
+            res['agree_with_comm_opt'] = res['agree_with_comm_opt'] and t[1].item() == 0
+        del model, pre
+        torch.cuda.empty_cache()
+    return res
+
+
+def run_parity(args, caps, grads, device, oracle):
+    """Headline-shape parity (N = 1): a FRESH KFAC runs a factor + eigendecomposition step and an
+    ordinary step on the very captures and gradients the CPU oracle just processed; the rewritten
+    gradients of every layer and the two largest factors are compared with the oracle's."""
+    ok_obj, v_steps = oracle
+    model, pre = fresh_kfac(args, 'comm-opt', device, 1)
+    worst_abs = worst_rel = 0.0
+    viol = total = 0
+    layer_rel = []
+    for step in range(2):
+        feed(pre, caps)
+        restore_grads(pre, grads)
+        pre.step()
+        torch.cuda.synchronize()
+        for l, ref in zip(pre.layers, v_steps[step]):
+            pairs = [(l.module.weight.grad, ref[0])]
+            if l.module.bias is not None:
+                pairs.append((l.module.bias.grad, ref[1]))
+            for got, r in pairs:
+                r = r.to(device)
+                err = (got - r).abs()
+                worst_abs = max(worst_abs, err.max().item())
+                rel = err.max().item() / max(r.abs().max().item(), 1e-30)
+                worst_rel = max(worst_rel, rel)
+                if step == 0:
+                    layer_rel.append(rel)
+                viol += int((err > 1e-4 + 1e-2 * r.abs()).sum())
+                total += r.numel()
+    # factors: largest A and largest G, normalised error |dF_ij| / sqrt(F_ii F_jj) and elementwise rtol 1e-3
+    ia = max(range(len(pre.layers)), key=lambda i: pre.layers[i].state['A'].shape[0])
+    ig = max(range(len(pre.layers)), key=lambda i: pre.layers[i].state['G'].shape[0])
+    # After the first update the state is decay * I + (1 - decay) * F; the identity part is exact, so the
+    # comparison is made on F itself (the SYRK's output), which is what TF32 rounding touches.
+    f_norm = f_miss = 0.0
+    f_dims = []
+    decay = KFAC_KW['factor_decay']
+    for got, ref in ((pre.layers[ia].state['A'], ok_obj.A[ia]), (pre.layers[ig].state['G'], ok_obj.G[ig])):
+        eye = torch.eye(ref.shape[0], device=device)
+        ref = (ref.to(device) - decay * eye) / (1 - decay)
+        got = (got - decay * eye) / (1 - decay)
+        dg = ref.diagonal().clamp_min(1e-30).sqrt()
+        err = (got - ref).abs()
+        f_norm = max(f_norm, (err / (dg[:, None] * dg[None, :])).max().item())
+        f_miss = max(f_miss, ((err > 1e-3 * ref.abs()).float().mean().item()))
+        f_dims.append(ref.shape[0])
+    grad_scale = max(r[0].abs().max().item() for r in v_steps[0])
+    res = {'config': WORKLOAD if args.model == 'resnet50' else args.model, 'checked': 'every layer, steps 0 (factor+eig) and 1',
+           'grad_max_abs': worst_abs, 'grad_max_rel': worst_rel, 'grad_abs_scale': grad_scale,
+           'grad_elements': total, 'grad_violations_rtol1e-2_atol1e-4': viol,
+           'grad_median_layer_rel': statistics.median(layer_rel),
+           'factor_dims': f_dims, 'factor_worst_norm_err': f_norm, 'factor_elementwise_miss_frac_rtol1e-3': f_miss,
+           'mma_mode': _native_mode(),
+           'within_north_star_tol': bool(viol == 0 and f_norm <= 1e-3)}
+    del model, pre
+    torch.cuda.empty_cache()
+    return res
+
+
+def _native_mode():
+    from distributed_kfac_pytorch_b200 import _native
+    return _native.get_ops().get_mma_mode()
 
 
 def run_e2e(args, pre, caps, grads, device, dist_on):
@@ -362,6 +560,10 @@ def run_e2e(args, pre, caps, grads, device, dist_on):
     bytes_grads = sum(w.numel() * 4 + (0 if b is None else b.numel() * 4) for w, b in grads)
     bytes_caps = sum(sum(t.numel() * 4 for t in a) + sum(t.numel() * 4 for t in g) for a, g in caps)
     result = torch.zeros(1).pin_memory()
+    # the step's result is the rewritten .grad of every registered module: it is read back to pinned
+    # host memory every step, together with the v.g scalar
+    host_out = [(torch.empty_like(w).pin_memory(), None if b is None else torch.empty_like(b).pin_memory())
+                for w, b in host_grads]
     h2d = [0]
 
     def one_step():
@@ -378,7 +580,11 @@ def run_e2e(args, pre, caps, grads, device, dist_on):
         h2d[0] += bytes_grads
         feed(pre, caps)
         pre.step()
-        result.copy_(pre._vg_acc, non_blocking=True)   # the step's scalar result, D2H
+        for l, (ow, ob) in zip(pre.layers, host_out):
+            ow.copy_(l.module.weight.grad, non_blocking=True)
+            if ob is not None:
+                ob.copy_(l.module.bias.grad, non_blocking=True)
+        result.copy_(pre._vg_acc, non_blocking=True)
 
     for _ in range(CADENCE):
         one_step()
@@ -392,7 +598,8 @@ def run_e2e(args, pre, caps, grads, device, dist_on):
     barrier_sync(dist_on)
     ms = max_over_ranks(e0.elapsed_time(e1), device, dist_on)
     return {'value': ms / args.steps, 'unit': 'ms/step', 'h2d_bytes_per_step': h2d[0] // args.steps,
-            'd2h_bytes_per_step': 4, 'api': 'KFAC.step() with pinned-host activations/gradients'}
+            'd2h_bytes_per_step': bytes_grads + 4,
+            'api': 'KFAC.step() with pinned-host activations/gradients in, rewritten gradients out'}
 
 
 def run_train(args, model, pre, x, y, device, dist_on, world):
@@ -451,7 +658,7 @@ def oracle_specs(modules):
     return specs
 
 
-def time_oracle(specs, caps, grads, steps, warmup):
+def time_oracle(specs, caps, grads, steps, warmup, keep_results=False):
     """Run the CPU oracle along the cadence; returns per-step seconds for the timed steps."""
     from oracle import kfac_oracle as O
     kw = {k: KFAC_KW[k] for k in ('damping', 'factor_decay', 'factor_update_freq', 'inv_update_freq',
@@ -464,12 +671,14 @@ def time_oracle(specs, caps, grads, steps, warmup):
         if ok.steps == 1 and warmup > 1:
             ok.steps = CADENCE * 1000 + 1
     ok.steps = 0
-    times = []
+    times, results = [], []
     for i in range(steps):
         t0 = time.perf_counter()
-        ok.step([caps], grads)
+        v = ok.step([caps], grads)
         times.append(time.perf_counter() - t0)
-    return times
+        if keep_results:
+            results.append(v)
+    return (times, ok, results) if keep_results else times
 
 
 def run_cpu_oracle(pre, caps, grads, cycles=1):
@@ -479,11 +688,11 @@ def run_cpu_oracle(pre, caps, grads, cycles=1):
     ccaps = [([t.cpu() for t in a], [t.cpu() for t in g]) for a, g in caps]
     cgrads = [(w.cpu(), None if b is None else b.cpu()) for w, b in grads]
     # bounded sample: one factor+eigendecomposition step and one ordinary step, amortised
-    t = time_oracle(specs, ccaps, cgrads, steps=2, warmup=0)
+    t, ok, results = time_oracle(specs, ccaps, cgrads, steps=2, warmup=0, keep_results=True)
     amort = (t[0] + (CADENCE - 1) * t[1]) / CADENCE
-    return {'value': amort * 1e3, 'unit': 'ms/step', 'cores': cores, 'kind': 'port',
+    return ({'value': amort * 1e3, 'unit': 'ms/step', 'cores': cores, 'kind': 'port',
             'sample': '1 factor+eig step (%.1f s) + 1 ordinary step (%.2f s) of the same ResNet-50 b32 '
-                      'captures, amortised over the %d-step cadence' % (t[0], t[1], CADENCE)}
+                      'captures, amortised over the %d-step cadence' % (t[0], t[1], CADENCE)}, (ok, results))
 
 
 def run_reference(args):

@@ -489,17 +489,17 @@ bool gemm_tc_eligible(const GemmProb& p) {
 }
 
 static int gemm_grouped_tc2(Context* ctx, const GemmProb* probs, int n, float* dot_acc, cudaStream_t stream) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    KFB_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes2));
-    attr_set = true;
-  }
   std::vector<GemmProb> sorted(probs, probs + n);
   std::stable_sort(sorted.begin(), sorted.end(), [](const GemmProb& a, const GemmProb& b) { return a.K > b.K; });
   probs = sorted.data();
   static TcBatch batch;
   static std::mutex mu;
   std::lock_guard<std::mutex> lock(mu);
+  static bool attr_set[64] = {};        // the opt-in to > 48 KB of dynamic shared memory is per device
+  if (!attr_set[ctx->device]) {
+    KFB_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes2));
+    attr_set[ctx->device] = true;
+  }
   for (int base = 0; base < n; base += kTcBatch) {
     batch.n = std::min(kTcBatch, n - base);
     int tiles = 0;
@@ -531,11 +531,6 @@ int gemm_grouped_tc(Context* ctx, const GemmProb* probs, int n, float* dot_acc, 
   // the single-CTA kernel
   static const bool use_pair = []() { const char* e = getenv("KFB_GEMM_2CTA"); return !e || atoi(e) != 0; }();
   if (use_pair) return gemm_grouped_tc2(ctx, probs, n, dot_acc, stream);
-  static bool attr_set = false;
-  if (!attr_set) {
-    KFB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    attr_set = true;
-  }
   // longest tiles first: with the static round-robin tile schedule this is close to LPT
   std::vector<GemmProb> sorted(probs, probs + n);
   std::stable_sort(sorted.begin(), sorted.end(), [](const GemmProb& a, const GemmProb& b) { return a.K > b.K; });
@@ -543,6 +538,11 @@ int gemm_grouped_tc(Context* ctx, const GemmProb* probs, int n, float* dot_acc, 
   static TcBatch batch;   // 32 KB: too large for the stack of some callers; calls are serialised per process
   static std::mutex mu;
   std::lock_guard<std::mutex> lock(mu);
+  static bool attr_set[64] = {};
+  if (!attr_set[ctx->device]) {
+    KFB_CUDA(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    attr_set[ctx->device] = true;
+  }
   for (int base = 0; base < n; base += kTcBatch) {
     batch.n = std::min(kTcBatch, n - base);
     int tiles = 0;

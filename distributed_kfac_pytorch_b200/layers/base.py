@@ -88,10 +88,13 @@ class KFACLayer(object):
 
     # ------------------------------------------------------------------ checkpoint
     def state_dict(self, include_inverses=False):
-        """Layout is contract (kfac/layers/base.py:47-60): full square fp32 A and G."""
-        if include_inverses:
-            return self.state
-        return {'A': self.state['A'], 'G': self.state['G']}
+        """Layout is contract (kfac/layers/base.py:47-60): full square fp32 A and G.  The entries
+        are contiguous copies of the logical shape - the live tensors are views of row-pitch-padded
+        buffers (or of a broadcast slab), which would drag their whole storage into a checkpoint
+        and which the reference's load_state_dict + allreduce could not take."""
+        keys = self.state.keys() if include_inverses else ('A', 'G')
+        return {k: (self.state[k].clone(memory_format=torch.contiguous_format)
+                    if torch.is_tensor(self.state[k]) else self.state[k]) for k in keys}
 
     def load_state_dict(self, state_dict):
         """kfac/layers/base.py:62-75, including the legacy A_factor/G_factor keys."""

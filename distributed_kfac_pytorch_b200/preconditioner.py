@@ -598,17 +598,19 @@ class KFAC(optim.Optimizer):
         rank = comm.backend.rank()
         dev = self.layers[0].state['A'].device
 
+        def floats(r, c):     # c == 0: 1-D vector of r entries stored as one padded row
+            return _round4(r) if c == 0 else r * _round4(c)
+
         def carve(plan):
             slabs = []
             for (src, gid), entries in plan.items():
-                total = sum(r * _round4(c) for _, _, r, c in entries)
+                total = sum(floats(r, c) for _, _, r, c in entries)
                 slab = torch.zeros(total, device=dev, dtype=torch.float32)
                 off = 0
                 for layer, key, r, c in entries:
-                    n = r * _round4(c)
-                    if c == 0:       # 1-D vector stored as one row
-                        layer.state[key] = slab[off:off + _round4(r)][:r]
-                        n = _round4(r)
+                    n = floats(r, c)
+                    if c == 0:
+                        layer.state[key] = slab[off:off + n][:r]
                     else:
                         layer._inject2d(key, slab[off:off + n].view(r, _round4(c)), c)
                     off += n

@@ -14,6 +14,10 @@ the API used at kfac/layers/utils.py:63), and writes
     tests/golden/allocator.json  worker assignments for ResNet-50/152, W = 2, 4, 8
     tests/golden/cnn_variants.pt  SmallCNN with compute_factor_in_hook / accumulate_data / no prediv
     tests/golden/resnet32_single.pt  BASELINE configs[0]: CIFAR ResNet-32, batch 128, 2 steps
+    tests/golden/cnn_world4.pt, cnn_world8.pt   4- and 8-rank gloo, the three CommMethods (rank 0's view)
+    tests/golden/cnn_world2_variants.pt   2-rank gloo: precompute_outer_eigen=False under COMM_OPT and
+                                 HYBRID_OPT, and distribute_layer_factors=True (A and G on different ranks)
+    tests/golden/shared_module.pt   register_shared_module (tied encoder/decoder weight), single process
 
 Nothing here is imported by the product or by the tests; the tests only read the
 files it wrote.
@@ -171,7 +175,7 @@ def gen_lstm_single():
           'losses', [round(s['loss'], 4) for s in rec['steps']])
 
 
-def _world2_worker(rank, world, port, method_name, fraction, out):
+def _world2_worker(rank, world, port, method_name, fraction, out, extra=None):
     import torch.distributed as dist
     os.environ['MASTER_ADDR'] = '127.0.0.1'
     os.environ['MASTER_PORT'] = str(port)
@@ -182,9 +186,10 @@ def _world2_worker(rank, world, port, method_name, fraction, out):
     model = models.make_cnn()
     ddp = torch.nn.parallel.DistributedDataParallel(model)
     opt = torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.9)
+    kw = dict(KFAC_ARGS, inv_update_freq=1, distribute_layer_factors=False)
+    kw.update(extra or {})
     pre = kfac.KFAC(model, comm_method=getattr(kfac.CommMethod, method_name),
-                    grad_worker_fraction=fraction, distribute_layer_factors=False,
-                    **dict(KFAC_ARGS, inv_update_freq=1))
+                    grad_worker_fraction=fraction, **kw)
     steps = []
     for s in range(3):
         x, y = models.cnn_batch(s, rank)
@@ -222,6 +227,79 @@ def gen_cnn_world2():
                 assert torch.equal(w0, w1), name
     torch.save(result, os.path.join(HERE, 'cnn_world2.pt'))
     print('cnn_world2: ok, methods agree bit-for-bit')
+
+
+def gen_cnn_world(world):
+    """The three CommMethods on `world` gloo ranks; rank 0's factors and gradients (every rank ends
+    with the same ones) and the assignment.  bench.py replays this on `world` GPUs over NCCL."""
+    import torch.multiprocessing as mp
+    result = {}
+    for i, (name, frac) in enumerate([('COMM_OPT', 1.0), ('MEM_OPT', 0.0), ('HYBRID_OPT', 0.5)]):
+        tmp = '/tmp/_golden_w%d_%s.pt' % (world, name)
+        mp.spawn(_world2_worker, args=(world, 29631 + 10 * world + i, name, frac, tmp), nprocs=world, join=True)
+        rec = torch.load(tmp, weights_only=False)
+        os.remove(tmp)
+        for st in rec['steps']:
+            del st['grads_in']
+        result[name] = rec
+    for name in ('MEM_OPT', 'HYBRID_OPT'):
+        for s in range(3):
+            for (w0, b0), (w1, b1) in zip(result['COMM_OPT']['steps'][s]['grads_out'],
+                                          result[name]['steps'][s]['grads_out']):
+                assert torch.equal(w0, w1), name
+            for key in ('A', 'G'):
+                for f0, f1 in zip(result['COMM_OPT']['steps'][s][key], result[name]['steps'][s][key]):
+                    assert torch.equal(f0, f1), name
+        result[name]['steps'] = None        # bit-identical to COMM_OPT's: stored once
+    torch.save(result, os.path.join(HERE, 'cnn_world%d.pt' % world))
+    print('cnn_world%d: ok, methods agree bit-for-bit' % world)
+
+
+def gen_cnn_world2_variants():
+    """Constructor switches that only matter with more than one rank: eigenvalues
+    shipped instead of dGdA (precompute_outer_eigen=False) and A / G decomposed on different ranks
+    (distribute_layer_factors=True, kfac/preconditioner.py:638-645)."""
+    import torch.multiprocessing as mp
+    result = {}
+    cases = [('COMM_OPT/no_prediv', 'COMM_OPT', 1.0, dict(precompute_outer_eigen=False)),
+             ('HYBRID_OPT/no_prediv', 'HYBRID_OPT', 0.5, dict(precompute_outer_eigen=False)),
+             ('COMM_OPT/distributed', 'COMM_OPT', 1.0,
+              dict(precompute_outer_eigen=False, distribute_layer_factors=True))]
+    for i, (key, name, frac, extra) in enumerate(cases):
+        tmp = '/tmp/_golden_w2v_%d.pt' % i
+        mp.spawn(_world2_worker, args=(2, 29691 + i, name, frac, tmp, extra), nprocs=2, join=True)
+        rec = torch.load(tmp, weights_only=False)
+        os.remove(tmp)
+        for st in rec['steps']:
+            del st['grads_in']
+        rec['kwargs'] = extra
+        result[key] = rec
+    assert any(a['a_rank'] != a['g_rank'] for a in result['COMM_OPT/distributed']['assign'])
+    torch.save(result, os.path.join(HERE, 'cnn_world2_variants.pt'))
+    print('cnn_world2_variants: ok')
+
+
+def gen_shared_module():
+    """register_shared_module (kfac/preconditioner.py:404-470): two Linear modules that share one
+    weight, the second registered by hand."""
+    torch.set_num_threads(1)
+    model = models.make_tied()
+    opt = torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.9)
+    kw = dict(KFAC_ARGS, inv_update_freq=1, accumulate_data=True)
+    pre = kfac.KFAC(model, **kw)
+    pre.register_shared_module(model.first, model.second)
+    steps = []
+    for s in range(3):
+        x, y = models.tied_batch(s)
+        opt.zero_grad()
+        F.cross_entropy(model(x), y).backward()
+        pre.step()
+        steps.append({'grads_out': [_grads(l) for l in pre.layers],
+                      'A': [l.state['A'].clone() for l in pre.layers],
+                      'G': [l.state['G'].clone() for l in pre.layers]})
+        opt.step()
+    torch.save({'kwargs': kw, 'steps': steps, 'n_layers': len(pre.layers)}, os.path.join(HERE, 'shared_module.pt'))
+    print('shared_module: layers', len(pre.layers))
 
 
 def gen_allocator():
@@ -277,3 +355,11 @@ if __name__ == '__main__':
         gen_allocator()
     if 'world2' in which:
         gen_cnn_world2()
+    if 'world4' in which:
+        gen_cnn_world(4)
+    if 'world8' in which:
+        gen_cnn_world(8)
+    if 'world2v' in which:
+        gen_cnn_world2_variants()
+    if 'shared' in which:
+        gen_shared_module()

@@ -121,6 +121,36 @@ class FixedScaler(object):
         return self.scale
 
 
+class TiedLinear(nn.Linear):
+    """A Linear whose class name K-FAC's registration does not know, so that it is only
+    registered by hand through register_shared_module."""
+
+
+class TiedModel(nn.Module):
+    """Two square Linear modules sharing ONE weight (and bias), then an ordinary classifier."""
+
+    def __init__(self, width=12, classes=10):
+        super().__init__()
+        self.first = TiedLinear(width, width)
+        self.second = TiedLinear(width, width)
+        self.second.weight = self.first.weight
+        self.second.bias = self.first.bias
+        self.fc = nn.Linear(width, classes)
+
+    def forward(self, x):
+        return self.fc(F.relu(self.second(F.relu(self.first(x)))))
+
+
+def make_tied(seed=0):
+    torch.manual_seed(seed)
+    return TiedModel()
+
+
+def tied_batch(step, n=8):
+    g = torch.Generator().manual_seed(4000 + step)
+    return torch.randn(n, 12, generator=g), torch.randint(0, 10, (n,), generator=g)
+
+
 def make_cnn(seed=0):
     torch.manual_seed(seed)
     return SmallCNN()

@@ -79,6 +79,12 @@ def test_state_dict_roundtrip_and_layout(cpu_ops):
         assert set(entry.keys()) == {'A', 'G'}
         assert entry['A'].shape == (layer.state['A'].shape[0],) * 2
         assert entry['A'].dtype == torch.float32
+        for t in entry.values():      # saved tensors are plain contiguous d x d copies, not padded views
+            assert t.is_contiguous() and t.untyped_storage().nbytes() == t.numel() * 4
+    full = pre.state_dict(include_layer_inverses=True)['layers'][1]    # c2: da = 73, pitch-padded inside
+    assert {'QA', 'QG', 'dGdA'} <= set(full.keys())
+    assert all(t.is_contiguous() and t.untyped_storage().nbytes() == t.numel() * t.element_size()
+               for t in full.values() if torch.is_tensor(t))
     # legacy key names are accepted (kfac/layers/base.py:64-68)
     legacy = dict(sd)
     legacy['layers'] = [{'A_factor': e['A'].clone(), 'G_factor': e['G'].clone()} for e in sd['layers']]
@@ -202,70 +208,72 @@ def test_placement_matches_reference_bit_exact():
 
 # ---- two ranks over gloo ----------------------------------------------------------
 
-def _world2_worker(rank, world, port, method_name, fraction, out_path):
+def _world_worker(rank, world, port, method_name, fraction, extra, out_path):
     import torch.distributed as dist
+    import world_replay
     os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port), LOCAL_RANK=str(rank))
     torch.set_num_threads(1)
     dist.init_process_group('gloo', rank=rank, world_size=world)
     _native.set_ops(OracleOps())
     comm.reset_comm_backend()
-    model = models.make_cnn()
-    ddp = torch.nn.parallel.DistributedDataParallel(model)
-    opt = torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.9)
-    with warnings.catch_warnings():
-        warnings.simplefilter('ignore')
-        pre = kfac.KFAC(model, comm_method=getattr(kfac.CommMethod, method_name),
-                        grad_worker_fraction=fraction, distribute_layer_factors=False,
-                        damping=0.003, factor_decay=0.95, factor_update_freq=1,
-                        inv_update_freq=1, kl_clip=0.001, lr=0.1)
-    steps = []
-    for s in range(3):
-        x, y = models.cnn_batch(s, rank)
-        opt.zero_grad()
-        F.cross_entropy(ddp(x), y).backward()
-        pre.step()
-        steps.append({'grads_out': [(l.module.weight.grad.clone(),
-                                     None if l.module.bias is None else l.module.bias.grad.clone())
-                                    for l in pre.layers],
-                      'A': [l.state['A'].clone() for l in pre.layers],
-                      'G': [l.state['G'].clone() for l in pre.layers]})
-        opt.step()
-    assign = [{'a_rank': l.compute_A_inv_rank, 'g_rank': l.compute_G_inv_rank,
-               'grad_ranks': list(l.compute_grad_ranks),
-               'grad_src_group': [(src, list(grp.ranks)) for src, grp in l.broadcast_grad_groups]}
-              for l in pre.layers]
-    held = [sorted(k for k, v in l.state.items() if v is not None) for l in pre.layers]
-    torch.save({'steps': steps, 'assign': assign, 'held': held}, out_path % rank)
+    rec = world_replay.replay(kfac, method_name, fraction, torch.device('cpu'), rank, extra)
+    pre = rec.pop('pre')
+    rec['vec_numel'] = [(l.state['dA'].numel(), l.state['dG'].numel())
+                        if l.state.get('dA') is not None and l.state.get('dG') is not None else None
+                        for l in pre.layers]
+    rec['dims'] = [l._dims() for l in pre.layers]
+    torch.save(rec, out_path % rank)
     dist.barrier()
     dist.destroy_process_group()
 
 
+def _spawn_world(tmp_path, world, port, method, fraction, extra=None):
+    import torch.multiprocessing as mp
+    out = str(tmp_path / 'rank%d.pt')
+    mp.spawn(_world_worker, args=(world, port, method, fraction, extra, out), nprocs=world, join=True)
+    return [torch.load(out % r, weights_only=False) for r in range(world)]
+
+
+@pytest.mark.parametrize('world', [2, 4])
 @pytest.mark.parametrize('idx,method,fraction', [(0, 'COMM_OPT', 1.0), (1, 'MEM_OPT', 0.0),
                                                  (2, 'HYBRID_OPT', 0.5)])
-def test_world2_gloo_matches_reference(tmp_path, idx, method, fraction):
-    import torch.multiprocessing as mp
-    gold = load_golden('cnn_world2.pt')[method]
-    out = str(tmp_path / 'rank%d.pt')
-    mp.spawn(_world2_worker, args=(2, 29711 + idx, method, fraction, out), nprocs=2, join=True)
-    ranks = [torch.load(out % r, weights_only=False) for r in range(2)]
+def test_world_gloo_matches_reference(tmp_path, world, idx, method, fraction):
+    import world_replay
+    gold = world_replay.load_world_golden(world)[method]
+    ranks = _spawn_world(tmp_path, world, 29711 + 10 * world + idx, method, fraction)
     for r in ranks:
-        assert r['assign'] == gold['assign']          # worker-to-layer assignment: bit-exact
-        for s in range(3):
-            for i in range(6):
-                torch.testing.assert_close(r['steps'][s]['A'][i], gold['steps'][s]['A'][i], **FACTOR_TOL)
-                torch.testing.assert_close(r['steps'][s]['G'][i], gold['steps'][s]['G'][i], **FACTOR_TOL)
-                torch.testing.assert_close(r['steps'][s]['grads_out'][i][0],
-                                           gold['steps'][s]['grads_out'][i][0], **GRAD_TOL)
-    # both ranks end with the same gradients
-    for i in range(6):
-        torch.testing.assert_close(ranks[0]['steps'][2]['grads_out'][i][0],
-                                   ranks[1]['steps'][2]['grads_out'][i][0], rtol=1e-5, atol=1e-7)
+        world_replay.compare(r, gold)     # assignment bit-exact, factors / gradients within tolerance
+    # every rank ends with the same gradients
+    for r in ranks[1:]:
+        for i in range(6):
+            torch.testing.assert_close(ranks[0]['steps'][2]['grads_out'][i][0],
+                                       r['steps'][2]['grads_out'][i][0], rtol=1e-5, atol=1e-7)
     if method == 'MEM_OPT':
         # only the inverse rank holds a layer's eigenvectors (memory story of SURVEY §8c)
         for i, a in enumerate(gold['assign']):
-            for rank in range(2):
+            for rank in range(world):
                 has = 'QA' in ranks[rank]['held'][i]
                 assert has == (rank == a['a_rank'])
+
+
+@pytest.mark.parametrize('idx,key,method,fraction', [(0, 'COMM_OPT/no_prediv', 'COMM_OPT', 1.0),
+                                                     (1, 'HYBRID_OPT/no_prediv', 'HYBRID_OPT', 0.5),
+                                                     (2, 'COMM_OPT/distributed', 'COMM_OPT', 1.0)])
+def test_world2_switches_match_reference(tmp_path, idx, key, method, fraction):
+    """Eigenvalues travelling instead of dGdA (precompute_outer_eigen=False: the 1-D entries of the
+    fused inverse slab) and A / G decomposed on different ranks (distribute_layer_factors=True,
+    kfac/preconditioner.py:638-645)."""
+    import world_replay
+    gold = load_golden('cnn_world2_variants.pt')[key]
+    ranks = _spawn_world(tmp_path, 2, 29761 + idx, method, fraction, gold['kwargs'])
+    for r in ranks:
+        world_replay.compare(r, gold)
+        n_held = 0
+        for (da, dg), vec in zip(r['dims'], r['vec_numel']):
+            if vec is not None:           # this rank is a gradient worker of the layer
+                assert vec == (da, dg)    # dA / dG views carved out of the slab have their full length
+                n_held += 1
+        assert n_held > 0
 
 
 # ---- SURVEY §8f rank 2/3 switches: in-hook factors, accumulated micro-batches, no prediv -------
