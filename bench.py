@@ -494,7 +494,7 @@ def run_parity(args, caps, grads, device, oracle):
     """Headline-shape parity (N = 1): a FRESH KFAC runs a factor + eigendecomposition step and an
     ordinary step on the very captures and gradients the CPU oracle just processed; the rewritten
     gradients of every layer and the two largest factors are compared with the oracle's."""
-    ok_obj, v_steps = oracle
+    ok_obj, v_steps, ccaps = oracle
     model, pre = fresh_kfac(args, 'comm-opt', device, 1)
     worst_abs = worst_rel = 0.0
     viol = total = 0
@@ -521,20 +521,25 @@ def run_parity(args, caps, grads, device, oracle):
     # factors: largest A and largest G, normalised error |dF_ij| / sqrt(F_ii F_jj) and elementwise rtol 1e-3
     ia = max(range(len(pre.layers)), key=lambda i: pre.layers[i].state['A'].shape[0])
     ig = max(range(len(pre.layers)), key=lambda i: pre.layers[i].state['G'].shape[0])
-    # After the first update the state is decay * I + (1 - decay) * F; the identity part is exact, so the
-    # comparison is made on F itself (the SYRK's output), which is what TF32 rounding touches.
+    # After the first update the state is decay * I + (1 - decay) * F with F ~ 1e-4 or less: on the
+    # diagonal F sits below fp32's resolution next to 0.95 in BOTH implementations, off the diagonal the
+    # state is (1 - decay) * F exactly scaled.  So F (the SYRK's output, what TF32 rounding touches) is
+    # compared off the diagonal, against the oracle's raw factor of the same captures:
+    # |dF_ij| <= 1e-3 sqrt(F_ii F_jj) (the normalised tolerance of the tests), plus the fraction of
+    # entries that miss the elementwise rtol 1e-3.
     f_norm = f_miss = 0.0
     f_dims = []
     decay = KFAC_KW['factor_decay']
-    for got, ref in ((pre.layers[ia].state['A'], ok_obj.A[ia]), (pre.layers[ig].state['G'], ok_obj.G[ig])):
-        eye = torch.eye(ref.shape[0], device=device)
-        ref = (ref.to(device) - decay * eye) / (1 - decay)
-        got = (got - decay * eye) / (1 - decay)
-        dg = ref.diagonal().clamp_min(1e-30).sqrt()
-        err = (got - ref).abs()
+    for key, idx in (('A', ia), ('G', ig)):
+        spec = ok_obj.specs[idx]
+        raw = (spec.A(ccaps[idx][0]) if key == 'A' else spec.G(ccaps[idx][1])).to(device).double()
+        got = pre.layers[idx].state[key].double() / (1 - decay)
+        dg = raw.diagonal().clamp_min(1e-300).sqrt()
+        err = (got - raw).abs()
+        err.fill_diagonal_(0.0)
         f_norm = max(f_norm, (err / (dg[:, None] * dg[None, :])).max().item())
-        f_miss = max(f_miss, ((err > 1e-3 * ref.abs()).float().mean().item()))
-        f_dims.append(ref.shape[0])
+        f_miss = max(f_miss, ((err > 1e-3 * raw.abs()).double().mean().item()))
+        f_dims.append(raw.shape[0])
     grad_scale = max(r[0].abs().max().item() for r in v_steps[0])
     res = {'config': WORKLOAD if args.model == 'resnet50' else args.model, 'checked': 'every layer, steps 0 (factor+eig) and 1',
            'grad_max_abs': worst_abs, 'grad_max_rel': worst_rel, 'grad_abs_scale': grad_scale,
@@ -692,7 +697,7 @@ def run_cpu_oracle(pre, caps, grads, cycles=1):
     amort = (t[0] + (CADENCE - 1) * t[1]) / CADENCE
     return ({'value': amort * 1e3, 'unit': 'ms/step', 'cores': cores, 'kind': 'port',
             'sample': '1 factor+eig step (%.1f s) + 1 ordinary step (%.2f s) of the same ResNet-50 b32 '
-                      'captures, amortised over the %d-step cadence' % (t[0], t[1], CADENCE)}, (ok, results))
+                      'captures, amortised over the %d-step cadence' % (t[0], t[1], CADENCE)}, (ok, results, ccaps))
 
 
 def run_reference(args):

@@ -32,13 +32,23 @@ class CSegment(C.Structure):
                 ('n', C.c_int64), ('c', C.c_int64), ('h', C.c_int64), ('w', C.c_int64),
                 ('kh', C.c_int32), ('kw', C.c_int32), ('sh', C.c_int32), ('sw', C.c_int32),
                 ('ph', C.c_int32), ('pw', C.c_int32), ('ld', C.c_int64),
-                ('weight', C.c_float), ('dtype', C.c_int32)]
+                ('weight', C.c_float), ('dtype', C.c_int32), ('dev_scale', C.c_void_p)]
 
 
 class CFactorJob(C.Structure):
     _fields_ = [('d', C.c_int32), ('n_segments', C.c_int32), ('segments', C.POINTER(CSegment)),
                 ('state', C.c_void_p), ('ld_state', C.c_int64), ('seed_identity', C.c_int32),
-                ('write_state', C.c_int32), ('tri_out', C.c_void_p)]
+                ('write_state', C.c_int32), ('tri_out', C.c_void_p), ('dev_rescale', C.c_void_p)]
+
+
+class CFilterJob(C.Structure):
+    _fields_ = [('data', C.c_void_p), ('numel', C.c_int64), ('dtype', C.c_int32), ('group', C.c_int32),
+                ('rows', C.c_float), ('host_inv_scale_sq', C.c_float), ('loss_scale', C.c_void_p),
+                ('dev_scale', C.c_void_p)]
+
+
+class CFilterGroup(C.Structure):
+    _fields_ = [('dev_rescale', C.c_void_p), ('renormalise', C.c_int32), ('reserved', C.c_int32)]
 
 
 class CTriJob(C.Structure):
@@ -78,6 +88,9 @@ _SIGNATURES = {
     'kfb_factor_workspace_bytes': (C.c_size_t, [C.POINTER(CFactorJob), C.c_int32]),
     'kfb_factor_update': (C.c_int, [C.POINTER(CFactorJob), C.c_int32, C.c_float, C.c_void_p,
                                     C.c_size_t, C.c_void_p]),
+    'kfb_capture_filter': (C.c_int, [C.POINTER(CFilterJob), C.c_int32, C.POINTER(CFilterGroup), C.c_int32, C.c_void_p]),
+    'kfb_narrow': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),
+    'kfb_widen': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),
     'kfb_static_scratch_bytes': (C.c_size_t, []),
     'kfb_factor_update_static': (C.c_int, [C.POINTER(CFactorJob), C.c_int32, C.c_float, C.c_void_p]),
     'kfb_tri_unpack': (C.c_int, [C.POINTER(CTriJob), C.c_int32, C.c_float, C.c_void_p]),
@@ -87,6 +100,8 @@ _SIGNATURES = {
                             C.c_int64, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]),
     'kfb_syevd_batch_workspace_bytes': (C.c_size_t, [C.POINTER(CSyevdJob), C.c_int32]),
     'kfb_syevd_batch': (C.c_int, [C.POINTER(CSyevdJob), C.c_int32, C.c_void_p, C.c_size_t, C.c_void_p]),
+    'kfb_syevd_lane_plan': (C.c_int, [C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_int32),
+                                      C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_double)]),
     'kfb_cholesky_inverse_workspace_bytes': (C.c_size_t, [C.c_int32]),
     'kfb_cholesky_inverse': (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_float, C.c_void_p, C.c_int64,
                                        C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]),
@@ -134,21 +149,34 @@ class Segment(object):
     """One operand of a factor: a captured activation / grad_output tensor plus the
     layout it is read through (see kfb_segment)."""
     __slots__ = ('kind', 'has_bias', 'tensor', 'n', 'c', 'h', 'w', 'kernel', 'stride',
-                 'padding', 'ld', 'weight')
+                 'padding', 'ld', 'weight', 'dev_scale')
 
     def __init__(self, kind, tensor, n, c, weight, has_bias=False, h=1, w=1, kernel=(1, 1),
                  stride=(1, 1), padding=(0, 0), ld=0):
         self.kind, self.tensor, self.n, self.c, self.weight = kind, tensor, n, c, weight
         self.has_bias, self.h, self.w = has_bias, h, w
         self.kernel, self.stride, self.padding, self.ld = kernel, stride, padding, ld
+        self.dev_scale = None      # 1-element device tensor multiplying `weight` (0 drops the segment)
 
 
 class FactorJob(object):
-    __slots__ = ('d', 'segments', 'state', 'seed_identity', 'write_state', 'tri_out')
+    __slots__ = ('d', 'segments', 'state', 'seed_identity', 'write_state', 'tri_out', 'dev_rescale', 'filter')
 
     def __init__(self, d, segments, state, seed_identity, write_state=True, tri_out=None):
         self.d, self.segments, self.state = d, segments, state
         self.seed_identity, self.write_state, self.tri_out = seed_identity, write_state, tri_out
+        self.dev_rescale = None    # 1-element device tensor: >= 0 multiplies F, < 0 skips the update
+        self.filter = None         # CaptureFilter that fills dev_rescale and the segments' dev_scale
+
+
+class CaptureFilter(object):
+    """AMP bookkeeping of one G factor: its captures, their loss scale, and the device scalars the
+    filter kernel writes (one per capture + one per factor)."""
+    __slots__ = ('tensors', 'rows', 'scales', 'renormalise', 'dev_scales', 'dev_rescale')
+
+    def __init__(self, tensors, rows, scales, renormalise, dev_scales, dev_rescale):
+        self.tensors, self.rows, self.scales, self.renormalise = tensors, rows, scales, renormalise
+        self.dev_scales, self.dev_rescale = dev_scales, dev_rescale
 
 
 class PrecondJob(object):
@@ -255,6 +283,7 @@ class CudaOps(object):
                 cs.sh, cs.sw = s.stride
                 cs.ph, cs.pw = s.padding
                 cs.ld, cs.weight = s.ld, s.weight
+                cs.dev_scale = _ptr(s.dev_scale)
             keep.append(segs)
             _check_cuda(j.state, j.tri_out)
             _check_f32(j.state, j.tri_out)
@@ -262,12 +291,60 @@ class CudaOps(object):
             cj.state, cj.ld_state = j.state.data_ptr(), _pitch(j.state)
             cj.seed_identity, cj.write_state = int(j.seed_identity), int(j.write_state)
             cj.tri_out = _ptr(j.tri_out)
+            cj.dev_rescale = _ptr(j.dev_rescale)
         return cjobs, keep
+
+    def capture_filter(self, filters):
+        """filters: list of CaptureFilter.  One native call decides, on the device, which captures are
+        finite, folds 1 / loss_scale^2 into their weights and renormalises the factors that lost some."""
+        if not filters:
+            return
+        stream = self._enter(filters[0].tensors[0])
+        n = sum(len(f.tensors) for f in filters)
+        cjobs = (CFilterJob * n)()
+        cgroups = (CFilterGroup * len(filters))()
+        i = 0
+        for g, f in enumerate(filters):
+            cgroups[g].dev_rescale, cgroups[g].renormalise = f.dev_rescale.data_ptr(), int(f.renormalise)
+            for k, (t, rows, scale) in enumerate(zip(f.tensors, f.rows, f.scales)):
+                _check_cuda(t)
+                if not t.is_contiguous():
+                    raise NativeError('captured tensors must be contiguous')
+                cj = cjobs[i]
+                cj.data, cj.numel, cj.dtype, cj.group = t.data_ptr(), t.numel(), KFB_DTYPES[t.dtype], g
+                cj.rows = float(rows)
+                if torch.is_tensor(scale):
+                    _check_cuda(scale)
+                    _check_f32(scale)
+                    cj.loss_scale, cj.host_inv_scale_sq = scale.data_ptr(), 0.0
+                else:
+                    cj.loss_scale, cj.host_inv_scale_sq = None, 1.0 / (float(scale) * float(scale))
+                cj.dev_scale = f.dev_scales[k:k + 1].data_ptr()
+                i += 1
+        self._call('kfb_capture_filter', cjobs, n, cgroups, len(filters), stream)
+
+    def narrow(self, src, dst16):
+        """dst16 (float16 / bfloat16, flat) <- round(src fp32, flat)."""
+        stream = self._enter(src)
+        _check_cuda(dst16)
+        _check_f32(src)
+        if not (src.is_contiguous() and dst16.is_contiguous() and src.numel() == dst16.numel()):
+            raise NativeError('narrow: contiguous tensors of equal size expected')
+        self._call('kfb_narrow', src.data_ptr(), dst16.data_ptr(), src.numel(), KFB_DTYPES[dst16.dtype], stream)
+
+    def widen(self, src16, dst):
+        stream = self._enter(dst)
+        _check_cuda(src16)
+        _check_f32(dst)
+        if not (dst.is_contiguous() and src16.is_contiguous() and dst.numel() == src16.numel()):
+            raise NativeError('widen: contiguous tensors of equal size expected')
+        self._call('kfb_widen', src16.data_ptr(), dst.data_ptr(), dst.numel(), KFB_DTYPES[src16.dtype], stream)
 
     def factor_update(self, jobs, alpha):
         if not jobs:
             return
         stream = self._enter(jobs[0].state)
+        self.capture_filter([j.filter for j in jobs if j.filter is not None])
         cjobs, keep = self._factor_cjobs(jobs)
         n = len(jobs)
         nbytes = self.lib.kfb_factor_workspace_bytes(cjobs, n)
@@ -427,6 +504,20 @@ class CudaOps(object):
             self._call('kfb_scale_writeback', self._grad_jobs(items), len(items), _ptr(vg_acc),
                        float(lr), float(kl_clip if kl_clip is not None else 0.0),
                        float(fixed_scale), stream)
+
+
+def syevd_lane_plan(dims, num_sms=148, max_lanes=6):
+    """kfb_syevd_lane_plan: (lane of every factor, SMs per lane, modelled ms).  Host only."""
+    lib = load_library()
+    n = len(dims)
+    cd = (C.c_int32 * n)(*dims)
+    lane_of = (C.c_int32 * n)()
+    lane_sms = (C.c_int32 * 8)()
+    n_lanes, ms = C.c_int32(), C.c_double()
+    rc = lib.kfb_syevd_lane_plan(cd, n, num_sms, max_lanes, lane_of, lane_sms, C.byref(n_lanes), C.byref(ms))
+    if rc != 0:
+        raise NativeError('kfb_syevd_lane_plan failed (%d): %s' % (rc, lib.kfb_last_error().decode()))
+    return list(lane_of), list(lane_sms)[:n_lanes.value], ms.value
 
 
 def get_ops():

@@ -116,88 +116,148 @@ int kfb_syevd(const float* factor, int64_t ld_factor, int32_t d, float* E, int64
 // Two mechanisms, both cuSOLVER:
 //  * same-size groups of small/medium factors go through cusolverDnXsyevBatched (one launch
 //    sequence for the whole group: 22 64x64 solves take 0.4 ms instead of 20 ms);
-//  * the remaining (large or one-of-a-kind) factors run syevd on worker lanes, one host thread +
-//    stream + handle each, longest first.
+//  * the remaining (large or one-of-a-kind) factors run syevd on worker lanes - one host thread,
+//    stream and cuSOLVER handle each.  A syevd is a long chain of small dependent kernels, so one
+//    solve cannot fill the GPU and two solves on ordinary streams barely overlap (1.2x for two
+//    threads, nothing beyond); on DISJOINT SM partitions (green contexts, CUDA >= 12.4) they run
+//    truly side by side.  How much a solve slows down on fewer SMs depends on its size (measured
+//    table below: a 4608 takes 90 / 113 / 170 / 290 ms on 148 / 96 / 48 / 24 SMs, a 1152 takes
+//    13.7 / 13.9 / 17 / 22 ms), so the lanes are given DIFFERENT widths, planned per call from the
+//    job list: the partition of the SMs into at most lane_count() lanes and the job-to-lane
+//    assignment that minimise the modelled makespan.  A rank that holds one large factor and
+//    little else gets a single full-width ordinary stream (ResNet-50 on 8 GPUs: ranks 0-2).
 namespace {
 constexpr int kMaxLanes = 8;
+constexpr int kMaxUnits = 32;
 struct Lane {
   cudaStream_t stream = nullptr;
   cusolverDnHandle_t handle = nullptr;
   cudaEvent_t done = nullptr;
+  int width = 0;                // SMs this lane's kernels can use
+};
+// one partition of the SMs into green contexts, kept for the life of the process once created
+struct GreenSet {
+  std::vector<int> units;       // 8-SM units per lane, non-increasing; lane 0 also owns the split's remainder
+  std::vector<Lane> lanes;
 };
 struct LanePool {
-  Lane lanes[kMaxLanes];
+  Lane plain[2];                // ordinary streams of the primary context (all SMs)
   Lane grouped;                 // stream/handle for the XsyevBatched groups
   cusolverDnParams_t params = nullptr;
   cudaEvent_t start = nullptr;
-  int n_green = 0;              // lanes [0, n_green) run in green contexts
+  // SM partitioning state
+  int green_state = 0;          // 0 not tried, 1 available, -1 unavailable
+  CUdevice dev = 0;
+  CUdevResource groups[kMaxUnits];
+  CUdevResource rem;
+  int n_units = 0, unit_sms = 0, rem_sms = 0;
+  void* fn[6] = {};
+  std::vector<GreenSet*> sets;
   bool ready = false;
 };
 LanePool g_pools[64];
-std::mutex g_pool_mu;
+std::mutex g_pool_mu;          // pool creation
+std::mutex g_call_mu[64];      // one kfb_syevd_batch at a time per device (lanes, events and workspaces are shared)
 
-// How many syevd lanes to run: KFB_SYEVD_LANES, else three - one host thread per lane next to this
-// process's main thread, fewer when the node's cores are shared with many ranks (LOCAL_WORLD_SIZE,
-// set by torchrun).  With green contexts the lanes also split the SMs, and the large factors need
-// SMs: ResNet-50 on one B200 takes 646 ms on ordinary streams and 560 / 434 / 491 / 608 / 518 / 737
-// ms with 2 / 3 / 4 / 5 / 6 / 8 green-context lanes (64 / 48 / 32 / 24 / 24 / 16 SMs each).
+// How many syevd lanes at most: KFB_SYEVD_LANES, else 4.  Measured on the ResNet-50 factor sets of
+// 1 / 2 / 4 / 8 ranks (tools/bench_syevd.py --rank=r/W): 4 planned lanes beat 2, 3, 6 and 8 everywhere
+// (one GPU: 508 / 433 / 424 / 550 / 523 ms for 2 / 3 / 4 / 6 / 8 lanes - beyond four the narrow lanes and
+// the batched solver, which runs beside them on all SMs, get in each other's way), also when the
+// rank has only two cores to run the lane threads on (464 vs 519 ms for 4 vs 2 lanes under
+// taskset -c 0-1: the lane threads mostly wait on a full launch queue).
 int lane_count() {
   static const int n = []() {
     if (const char* e = getenv("KFB_SYEVD_LANES")) return std::min(kMaxLanes, std::max(1, atoi(e)));
-    int local_world = 1;
-    if (const char* e = getenv("LOCAL_WORLD_SIZE")) local_world = std::max(1, atoi(e));
-    const int cores = (int)std::max(1u, std::thread::hardware_concurrency());
-    return std::min(3, std::max(2, cores / local_world - 1));
+    return 4;
   }();
   return n;
 }
 
-// Streams for the syevd lanes inside GREEN CONTEXTS (CUDA >= 12.4): each lane gets its own context
-// with a slice of the SMs.  syevd is bound by its host-side panel loop (thousands of microsecond
-// kernels), and launches into ONE context serialise across threads - two lanes on ordinary streams
-// reach 1.33x, more add nothing - while launches into different green contexts do not: 24 syevd of
-// n = 1024 take 271 ms on one stream, 212 ms on four ordinary streams, 94 ms on four green contexts
-// of 32 SMs, 67 ms on eight of 16 SMs (tools/try_green_ctx.py).  Events of the primary context work
-// on these streams.  Returns how many streams were created (0: not available, use ordinary streams).
-int create_green_streams(int device, int num_sms, int want, cudaStream_t* out) {
-  if (getenv("KFB_SYEVD_GREEN") && getenv("KFB_SYEVD_GREEN")[0] == '0') return 0;
-  typedef CUresult (*GetDev)(CUdevice*, int);
-  typedef CUresult (*GetRes)(CUdevice, CUdevResource*, CUdevResourceType);
-  typedef CUresult (*Split)(CUdevResource*, unsigned int*, const CUdevResource*, CUdevResource*, unsigned int, unsigned int);
-  typedef CUresult (*GenDesc)(CUdevResourceDesc*, CUdevResource*, unsigned int);
-  typedef CUresult (*GreenCreate)(CUgreenCtx*, CUdevResourceDesc, CUdevice, unsigned int);
-  typedef CUresult (*GreenStream)(CUstream*, CUgreenCtx, unsigned int, int);
-  void* fn[6] = {};
+// A profiler that injects itself into the process (Nsight Compute / Systems) does not follow
+// launches into green contexts: stay on ordinary streams under one.
+bool profiler_attached() {
+  // variables the Nsight Compute / Nsight Systems launchers put into the target's environment (the
+  // CUDA images also carry NV_CUDA_NSIGHT_COMPUTE_VERSION etc. permanently: those do not count)
+  static const bool v = []() {
+    for (const char* name : {"NV_NSIGHT_INJECTION_PORT_BASE", "NV_NSIGHT_INJECTION_TRANSPORT_TYPE", "NV_COMPUTE_PROFILER_PERFWORKS_DIR",
+                             "NV_TPS_LAUNCH_TOKEN", "CUDA_INJECTION64_PATH", "NVTX_INJECTION64_PATH"})
+      if (getenv(name)) return true;
+    return false;
+  }();
+  return v;
+}
+
+typedef CUresult (*GetDev)(CUdevice*, int);
+typedef CUresult (*GetRes)(CUdevice, CUdevResource*, CUdevResourceType);
+typedef CUresult (*Split)(CUdevResource*, unsigned int*, const CUdevResource*, CUdevResource*, unsigned int, unsigned int);
+typedef CUresult (*GenDesc)(CUdevResourceDesc*, CUdevResource*, unsigned int);
+typedef CUresult (*GreenCreate)(CUgreenCtx*, CUdevResourceDesc, CUdevice, unsigned int);
+typedef CUresult (*GreenStream)(CUstream*, CUgreenCtx, unsigned int, int);
+
+// Split the device's SMs once into units of 8 (the smallest partition the driver hands out on this
+// architecture; 15 units + 28 left over on a 148-SM B200).  Lanes are built from runs of units.
+bool green_available(LanePool* p, int device) {
+  if (p->green_state != 0) return p->green_state > 0;
+  p->green_state = -1;
+  if (getenv("KFB_SYEVD_GREEN") && getenv("KFB_SYEVD_GREEN")[0] == '0') return false;
+  if (profiler_attached()) return false;
   const char* names[6] = {"cuDeviceGet", "cuDeviceGetDevResource", "cuDevSmResourceSplitByCount",
                           "cuDevResourceGenerateDesc", "cuGreenCtxCreate", "cuGreenCtxStreamCreate"};
   for (int i = 0; i < 6; ++i) {
     cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint(names[i], &fn[i], cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess ||
-        !fn[i]) {
+    if (cudaGetDriverEntryPoint(names[i], &p->fn[i], cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess ||
+        !p->fn[i]) {
       cudaGetLastError();
-      return 0;
+      return false;
     }
   }
-  CUdevice dev;
   CUdevResource sm;
-  if (((GetDev)fn[0])(&dev, device) != CUDA_SUCCESS) return 0;
-  if (((GetRes)fn[1])(dev, &sm, CU_DEV_RESOURCE_TYPE_SM) != CUDA_SUCCESS) return 0;
-  // equal slices, a multiple of 8 SMs each, at most 64
-  unsigned int per = (unsigned int)std::min(64, std::max(8, (num_sms / std::max(1, want)) & ~7));
-  CUdevResource groups[kMaxLanes], rest;
-  unsigned int n = (unsigned int)std::min(want, kMaxLanes);
-  if (((Split)fn[2])(groups, &n, &sm, &rest, 0, per) != CUDA_SUCCESS || n == 0) return 0;
-  int made = 0;
-  for (unsigned int i = 0; i < n; ++i) {
+  if (((GetDev)p->fn[0])(&p->dev, device) != CUDA_SUCCESS) return false;
+  if (((GetRes)p->fn[1])(p->dev, &sm, CU_DEV_RESOURCE_TYPE_SM) != CUDA_SUCCESS) return false;
+  unsigned int n = kMaxUnits;
+  if (((Split)p->fn[2])(p->groups, &n, &sm, &p->rem, 0, 8) != CUDA_SUCCESS || n < 2) return false;
+  p->n_units = (int)n;
+  p->unit_sms = (int)p->groups[0].sm.smCount;
+  p->rem_sms = (int)p->rem.sm.smCount;
+  p->green_state = 1;
+  return true;
+}
+
+// The green contexts of one partition (created on first use, 5 ms per lane, then cached).
+GreenSet* get_green_set(LanePool* p, const std::vector<int>& units) {
+  for (GreenSet* s : p->sets)
+    if (s->units == units) return s;
+  GreenSet* s = new GreenSet;
+  s->units = units;
+  int first = 0;
+  for (size_t l = 0; l < units.size(); ++l) {
+    CUdevResource res[kMaxUnits + 1];
+    unsigned int cnt = 0;
+    int width = 0;
+    for (int u = 0; u < units[l]; ++u) { res[cnt++] = p->groups[first + u]; width += (int)p->groups[first + u].sm.smCount; }
+    first += units[l];
+    if (l == 0 && p->rem_sms > 0) { res[cnt++] = p->rem; width += p->rem_sms; }
     CUdevResourceDesc desc;
     CUgreenCtx gctx;
     CUstream st;
-    if (((GenDesc)fn[3])(&desc, &groups[i], 1) != CUDA_SUCCESS) break;
-    if (((GreenCreate)fn[4])(&gctx, desc, dev, CU_GREEN_CTX_DEFAULT_STREAM) != CUDA_SUCCESS) break;
-    if (((GreenStream)fn[5])(&st, gctx, CU_STREAM_NON_BLOCKING, 0) != CUDA_SUCCESS) break;
-    out[made++] = (cudaStream_t)st;          // the green context lives as long as the process
+    Lane lane;
+    if (((GenDesc)p->fn[3])(&desc, res, cnt) != CUDA_SUCCESS) break;
+    if (((GreenCreate)p->fn[4])(&gctx, desc, p->dev, CU_GREEN_CTX_DEFAULT_STREAM) != CUDA_SUCCESS) break;
+    if (((GreenStream)p->fn[5])(&st, gctx, CU_STREAM_NON_BLOCKING, 0) != CUDA_SUCCESS) break;
+    lane.stream = (cudaStream_t)st;                 // the green context lives as long as the process
+    lane.width = width;
+    if (cudaEventCreateWithFlags(&lane.done, cudaEventDisableTiming) != cudaSuccess) break;
+    if (cusolverDnCreate(&lane.handle) != CUSOLVER_STATUS_SUCCESS) break;
+    s->lanes.push_back(lane);
   }
-  return made;
+  if (s->lanes.size() != units.size()) {             // the driver refused this partition: no green lanes at all
+    cudaGetLastError();
+    delete s;
+    p->green_state = -1;
+    return nullptr;
+  }
+  p->sets.push_back(s);
+  return s;
 }
 
 int get_pool(kfb::Context* ctx, LanePool** out) {
@@ -205,16 +265,13 @@ int get_pool(kfb::Context* ctx, LanePool** out) {
   LanePool& p = g_pools[ctx->device];
   if (!p.ready) {
     KFB_CUDA(cudaEventCreateWithFlags(&p.start, cudaEventDisableTiming));
-    cudaStream_t green[kMaxLanes] = {};
-    p.n_green = create_green_streams(ctx->device, ctx->num_sms, lane_count(), green);
-    for (int i = 0; i <= kMaxLanes; ++i) {
-      Lane& l = i < kMaxLanes ? p.lanes[i] : p.grouped;
-      if (i < p.n_green) l.stream = green[i];
-      else
+    for (int i = 0; i < 3; ++i) {
+      Lane& l = i < 2 ? p.plain[i] : p.grouped;
       KFB_CUDA(cudaStreamCreateWithFlags(&l.stream, cudaStreamNonBlocking));
       KFB_CUDA(cudaEventCreateWithFlags(&l.done, cudaEventDisableTiming));
       if (cusolverDnCreate(&l.handle) != CUSOLVER_STATUS_SUCCESS)
         KFB_FAIL(KFB_ERR_CUSOLVER, "cusolverDnCreate failed for worker lane %d", i);
+      l.width = ctx->num_sms;
     }
     if (cusolverDnCreateParams(&p.params) != CUSOLVER_STATUS_SUCCESS)
       KFB_FAIL(KFB_ERR_CUSOLVER, "cusolverDnCreateParams failed");
@@ -243,38 +300,164 @@ struct Group {
 struct BatchPlan {
   std::vector<Group> groups;
   std::vector<std::vector<int>> lanes;   // job indices per worker lane
+  std::vector<Lane*> lane_ptr;           // the stream / handle each lane runs on
   std::vector<size_t> lane_off;          // workspace offset per lane (+ end)
   size_t group_off = 0, total = 0;
 };
 
+// ---- measured cost model (B200, CUDA 12.9 cuSOLVER; tools/try_green_ctx3.py) ----------------------
+// syevd time in ms by factor size (columns) and SMs available to the solve (rows).
+constexpr int kNW = 10, kND = 10;
+const double kWidth[kNW] = {8, 16, 24, 32, 48, 64, 72, 96, 120, 148};
+const double kDim[kND] = {64, 128, 256, 512, 576, 1024, 1152, 2048, 2304, 4608};
+const double kMs[kNW][kND] = {
+    {1.01, 2.11, 2.68, 7.73, 11.01, 32.27, 43.01, 133.44, 188.38, 802.61},
+    {0.99, 1.85, 2.41, 6.03, 8.28, 21.36, 27.96, 80.27, 101.49, 415.48},
+    {1.00, 2.13, 2.33, 5.72, 7.43, 17.43, 22.24, 60.04, 73.52, 290.34},
+    {1.12, 1.85, 2.23, 5.56, 7.18, 15.58, 19.91, 50.00, 60.97, 230.35},
+    {1.12, 2.13, 2.23, 5.39, 6.65, 13.41, 17.06, 39.61, 48.11, 169.74},
+    {1.09, 2.14, 2.28, 5.23, 6.50, 11.76, 15.01, 33.64, 42.56, 143.38},
+    {1.09, 2.14, 2.26, 5.25, 6.56, 11.68, 14.28, 32.31, 39.22, 130.58},
+    {1.07, 2.07, 2.22, 5.33, 6.57, 11.48, 13.93, 29.30, 35.76, 112.76},
+    {1.13, 2.15, 2.25, 5.40, 6.61, 11.53, 13.85, 26.85, 33.37, 100.91},
+    {1.20, 2.12, 2.40, 5.45, 6.93, 11.48, 13.74, 25.59, 31.44, 89.61}};
+
+double ms_at_width(int wi, double d) {
+  const double* row = kMs[wi];
+  if (d <= kDim[0]) return row[0] * d / kDim[0];
+  for (int i = 1; i < kND; ++i)
+    if (d <= kDim[i]) {
+      const double t = (std::log(d) - std::log(kDim[i - 1])) / (std::log(kDim[i]) - std::log(kDim[i - 1]));
+      return std::exp(std::log(row[i - 1]) + t * (std::log(row[i]) - std::log(row[i - 1])));
+    }
+  return row[kND - 1] * std::pow(d / kDim[kND - 1], 2.0);
+}
+// modelled syevd time of a d x d factor on a lane of `width` SMs (log-log interpolation both ways)
+double syevd_ms(int d, int width) {
+  const double w = std::min<double>(width, kWidth[kNW - 1]);
+  if (w <= kWidth[0]) return ms_at_width(0, d) * kWidth[0] / std::max(1.0, w);
+  for (int i = 1; i < kNW; ++i)
+    if (w <= kWidth[i]) {
+      const double t = (std::log(w) - std::log(kWidth[i - 1])) / (std::log(kWidth[i]) - std::log(kWidth[i - 1]));
+      return std::exp(std::log(ms_at_width(i - 1, d)) * (1 - t) + std::log(ms_at_width(i, d)) * t);
+    }
+  return ms_at_width(kNW - 1, d);
+}
+
+// Jobs (sizes, descending) onto lanes of the given widths: each job goes where it would FINISH
+// earliest.  Returns the modelled makespan; `where` (optional) receives the lane of every job.
+double place_jobs(const std::vector<int>& dims, const std::vector<int>& widths, std::vector<int>* where) {
+  double load[kMaxLanes] = {};
+  if (where) where->assign(dims.size(), 0);
+  for (size_t i = 0; i < dims.size(); ++i) {
+    int best = 0;
+    double best_end = 0;
+    for (size_t l = 0; l < widths.size(); ++l) {
+      const double end = load[l] + syevd_ms(dims[i], widths[l]);
+      if (l == 0 || end < best_end) { best = (int)l; best_end = end; }
+    }
+    load[best] = best_end;
+    if (where) (*where)[i] = best;
+  }
+  double mk = 0;
+  for (size_t l = 0; l < widths.size(); ++l) mk = std::max(mk, load[l]);
+  return mk;
+}
+
+// Search the partitions of the SM units into at most `max_lanes` lanes (non-increasing unit counts;
+// lane 0 also gets the split's remainder) for the smallest modelled makespan.  The model is
+// tabulated first (job size class x lane units), so that one partition costs jobs x lanes adds.
+struct LaneSearch {
+  std::vector<int> cls;                 // size class of every job (descending sizes)
+  std::vector<double> ms_first, ms_rest;   // [class * (n_units + 1) + units]: lane 0 (with remainder) / other lanes
+  int n_units = 0, max_lanes = 1;
+  std::vector<int> cur, best;
+  double best_ms = 0;
+  void eval() {
+    double load[kMaxLanes] = {};
+    const int nl = (int)cur.size();
+    for (size_t i = 0; i < cls.size(); ++i) {
+      const double* f = &ms_first[(size_t)cls[i] * (n_units + 1)];
+      const double* r = &ms_rest[(size_t)cls[i] * (n_units + 1)];
+      int bl = 0;
+      double be = load[0] + f[cur[0]];
+      for (int l = 1; l < nl; ++l) {
+        const double e = load[l] + r[cur[l]];
+        if (e < be) { be = e; bl = l; }
+      }
+      load[bl] = be;
+      if (!best.empty() && be >= best_ms) return;      // already worse than the best partition
+    }
+    double mk = 0;
+    for (int l = 0; l < nl; ++l) mk = std::max(mk, load[l]);
+    if (best.empty() || mk < best_ms - 1e-9) { best = cur; best_ms = mk; }
+  }
+  void rec(int left) {
+    if (!cur.empty()) eval();
+    if ((int)cur.size() == max_lanes) return;
+    const int cap = cur.empty() ? left : std::min(left, cur.back());
+    for (int u = cap; u >= 1; --u) {
+      cur.push_back(u);
+      rec(left - u);
+      cur.pop_back();
+    }
+  }
+};
+
+// SM units per lane for these single solves (sizes descending), or one entry = "one full-width
+// stream": a partition must beat the single stream by a margin to be worth its host threads.
+std::vector<int> choose_units(const std::vector<int>& dims, int n_units, int unit_sms, int rem_sms, int num_sms, int max_lanes,
+                              double* modelled_ms) {
+  const double one_stream = place_jobs(dims, std::vector<int>(1, num_sms), nullptr);
+  *modelled_ms = one_stream;
+  if (dims.size() < 2 || max_lanes < 2 || n_units < 2) return std::vector<int>(1, n_units);
+  LaneSearch srch;
+  srch.n_units = n_units;
+  srch.max_lanes = std::min(max_lanes, (int)dims.size());
+  std::vector<int> uniq;
+  for (int d : dims) {
+    if (uniq.empty() || uniq.back() != d) uniq.push_back(d);
+    srch.cls.push_back((int)uniq.size() - 1);
+  }
+  srch.ms_first.assign(uniq.size() * (n_units + 1), 0.0);
+  srch.ms_rest.assign(uniq.size() * (n_units + 1), 0.0);
+  for (size_t c = 0; c < uniq.size(); ++c)
+    for (int u = 1; u <= n_units; ++u) {
+      srch.ms_first[c * (n_units + 1) + u] = syevd_ms(uniq[c], u * unit_sms + rem_sms);
+      srch.ms_rest[c * (n_units + 1) + u] = syevd_ms(uniq[c], u * unit_sms);
+    }
+  srch.rec(n_units);
+  if (srch.best.size() > 1 && srch.best_ms < 0.93 * one_stream) {
+    *modelled_ms = srch.best_ms;
+    return srch.best;
+  }
+  return std::vector<int>(1, n_units);
+}
+
 // Which same-size groups go to cusolverDnXsyevBatched.  Measured on B200 (tools/sweep_syev_batched.py,
 // tools/bench_syevd.py): the batched solver's time is almost flat in the batch count (it fills the GPU
-// whatever the count: b0 + b1*count), syevd's is ~linear in n and per matrix, and the two do not
-// overlap well (the batched grids hold the SMs the lanes' microsecond kernels wait for), so the batch
-// total is close to  sum(batched groups) + sum(lane work) / 1.33.  A group is batched when that is
-// cheaper than leaving its matrices on the lanes.  ResNet-50 on one GPU: 64..512 and 1024 (19 of them)
+// whatever the count: b0 + b1*count), syevd's is per matrix.  A group is batched when that is cheaper
+// than leaving its matrices on the lanes.  ResNet-50 on one GPU: 64..512 and 1024 (19 of them)
 // batched, 576 x3, 1152 x4, 2048 x7, 2304 x6, 4608 x3 on the lanes; on eight GPUs the per-rank groups
 // are small and e.g. two 512s (16 ms batched, 8 ms on a lane) stay on the lanes.
 double interp_loglog(int d, const double* tab) {
-  static const double kD[10] = {64, 128, 256, 512, 576, 1024, 1152, 2048, 2304, 4608};
-  if (d <= kD[0]) return tab[0] * d / kD[0];
-  for (int i = 1; i < 10; ++i)
-    if (d <= kD[i]) {
-      const double t = (std::log((double)d) - std::log(kD[i - 1])) / (std::log(kD[i]) - std::log(kD[i - 1]));
+  if (d <= kDim[0]) return tab[0] * d / kDim[0];
+  for (int i = 1; i < kND; ++i)
+    if (d <= kDim[i]) {
+      const double t = (std::log((double)d) - std::log(kDim[i - 1])) / (std::log(kDim[i]) - std::log(kDim[i - 1]));
       return std::exp(std::log(tab[i - 1]) + t * (std::log(tab[i]) - std::log(tab[i - 1])));
     }
-  return tab[9] * std::pow(d / kD[9], 2.0);
+  return tab[kND - 1] * std::pow(d / kDim[kND - 1], 2.0);
 }
 bool batched_wins(int d, size_t count, double lane_speedup) {
-  static const double kSingle[10] = {0.82, 1.92, 2.17, 5.3, 6.4, 11.3, 13.6, 25.0, 31.0, 88.7};        // syevd, ms
-  static const double kB0[10] = {0.35, 0.70, 3.4, 16.2, 25.6, 44.5, 55.0, 123.3, 143.0, 440.0};         // batched, ms
-  static const double kB1[10] = {0.001, 0.003, 0.025, 0.19, 0.37, 1.1, 1.5, 2.5, 4.6, 6.0};             // + per matrix
+  static const double kB0[kND] = {0.35, 0.70, 3.4, 16.2, 25.6, 44.5, 55.0, 123.3, 143.0, 440.0};         // batched, ms
+  static const double kB1[kND] = {0.001, 0.003, 0.025, 0.19, 0.37, 1.1, 1.5, 2.5, 4.6, 6.0};             // + per matrix
   static const int big_max = []() { const char* e = getenv("KFB_SYEV_BATCH_MAX_D"); return e ? atoi(e) : 0; }();
   static const int big_min_count = []() { const char* e = getenv("KFB_SYEV_BATCH_MIN_COUNT"); return e ? atoi(e) : 8; }();
-  if (count < 2) return false;
-  if (big_max > 0) return d <= 512 || (d <= big_max && (int)count >= big_min_count);   // explicit thresholds
+  if (count < 1) return false;
+  if (big_max > 0) return (d <= 512 && count >= 2) || (d <= big_max && (int)count >= big_min_count);   // explicit thresholds
   const double batched = interp_loglog(d, kB0) + interp_loglog(d, kB1) * (double)count;
-  const double lanes = interp_loglog(d, kSingle) * (double)count / lane_speedup;
+  const double lanes = syevd_ms(d, 148) * (double)count / lane_speedup;
   return batched < lanes;
 }
 
@@ -288,13 +471,16 @@ int make_plan(kfb::Context* ctx, LanePool* pool, const kfb_syevd_job* jobs, int 
     order[i] = i;
   }
   std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return jobs[a].d > jobs[b].d; });
+  const bool green = green_available(pool, ctx->device);
+  const int max_lanes = green ? lane_count() : std::min(lane_count(), 2);   // ordinary streams: two lanes reach 1.2-1.3x, more add nothing
   std::vector<int> singles;
   for (size_t i = 0; i < order.size();) {
     size_t j = i;
     while (j < order.size() && jobs[order[j]].d == jobs[order[i]].d) ++j;
     const int d = jobs[order[i]].d;
-    // measured aggregate speed-up of the lanes: 1.33 on ordinary streams, 2.9 / 4.0 with 4 / 8 green contexts
-    const double lane_speedup = pool->n_green >= 8 ? 4.0 : pool->n_green >= 4 ? 2.9 : pool->n_green >= 3 ? 2.2 : pool->n_green >= 2 ? 1.6 : 1.33;
+    // aggregate speed-up of the lanes over one stream on a typical mix (measured: 1.3 on ordinary
+    // streams; 1.7 / 2.0 / 2.2 for 3 / 4 / 6 green lanes of planned widths)
+    const double lane_speedup = !green ? 1.3 : max_lanes >= 6 ? 2.2 : max_lanes >= 4 ? 2.0 : max_lanes >= 3 ? 1.7 : 1.5;
     if (batched_wins(d, j - i, lane_speedup)) {
       Group g;
       g.d = d;
@@ -316,19 +502,39 @@ int make_plan(kfb::Context* ctx, LanePool* pool, const kfb_syevd_job* jobs, int 
     }
     i = j;
   }
-  // longest-processing-time placement of the single solves on the lanes (descending d already)
-  // without green contexts more than two lanes add nothing (one context's launch path serialises)
-  const int lane_cap = pool->n_green > 0 ? pool->n_green : std::min(lane_count(), getenv("KFB_SYEVD_LANES") ? kMaxLanes : 2);
-  const int n_lanes = std::min<int>(lane_cap, std::max<size_t>(1, singles.size()));
-  plan->lanes.assign(n_lanes, {});
-  std::vector<double> load(n_lanes, 0.0);
-  for (int i : singles) {
-    int best = 0;
-    for (int l = 1; l < n_lanes; ++l)
-      if (load[l] < load[best]) best = l;
-    load[best] += (double)jobs[i].d;          // syevd time is ~linear in d on this GPU (launch-bound panels)
-    plan->lanes[best].push_back(i);
+  // ---- lanes for the single solves (descending d already)
+  std::vector<int> dims;
+  for (int i : singles) dims.push_back(jobs[i].d);
+  std::vector<int> where(singles.size(), 0);
+  plan->lane_ptr.clear();
+  if (!singles.empty()) {
+    GreenSet* set = nullptr;
+    if (green && max_lanes > 1 && singles.size() > 1) {
+      double ms = 0;
+      const std::vector<int> units = choose_units(dims, pool->n_units, pool->unit_sms, pool->rem_sms, ctx->num_sms, max_lanes, &ms);
+      if (units.size() > 1) set = get_green_set(pool, units);
+    }
+    if (set) {
+      std::vector<int> widths;
+      for (Lane& l : set->lanes) { widths.push_back(l.width); plan->lane_ptr.push_back(&l); }
+      place_jobs(dims, widths, &where);
+    } else if (pool->green_state < 0 && lane_count() > 1 && singles.size() > 1) {
+      // no green contexts: two ordinary streams, longest-processing-time placement
+      plan->lane_ptr.push_back(&pool->plain[0]);
+      plan->lane_ptr.push_back(&pool->plain[1]);
+      double load[2] = {0, 0};
+      for (size_t i = 0; i < dims.size(); ++i) {
+        const int l = load[1] < load[0] ? 1 : 0;
+        load[l] += syevd_ms(dims[i], ctx->num_sms);
+        where[i] = l;
+      }
+    } else {
+      plan->lane_ptr.push_back(&pool->plain[0]);       // one full-width stream
+    }
   }
+  const int n_lanes = (int)plan->lane_ptr.size();
+  plan->lanes.assign(n_lanes, {});
+  for (size_t i = 0; i < singles.size(); ++i) plan->lanes[where[i]].push_back(singles[i]);
   plan->lane_off.assign(n_lanes + 1, 0);
   for (int l = 0; l < n_lanes; ++l) {
     size_t mx = 0;
@@ -382,6 +588,31 @@ int run_group(LanePool* pool, const Group& g, const kfb_syevd_job* jobs, char* r
 }
 }  // namespace
 
+int kfb_syevd_lane_plan(const int32_t* dims, int32_t n, int32_t num_sms, int32_t max_lanes, int32_t* lane_of_job,
+                        int32_t* lane_sms, int32_t* n_lanes, double* modelled_ms) {
+  KFB_REQUIRE(dims && n > 0 && num_sms >= 8 && max_lanes >= 1 && lane_of_job && lane_sms && n_lanes && modelled_ms,
+              "bad lane-plan arguments");
+  std::vector<int> order(n), sorted;
+  for (int i = 0; i < n; ++i) { KFB_REQUIRE(dims[i] > 0, "factor size must be positive"); order[i] = i; }
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return dims[a] > dims[b]; });
+  for (int i : order) sorted.push_back(dims[i]);
+  // the split this library asks the driver for: units of 8 SMs; on a 148-SM B200 the driver returns 15
+  // units and 28 SMs left over (partitions follow GPC boundaries); elsewhere assume an even split
+  const int unit = 8;
+  const int n_units = num_sms == 148 ? 15 : num_sms / unit;
+  const int rem = num_sms - n_units * unit;
+  const std::vector<int> units = choose_units(sorted, n_units, unit, rem, num_sms, std::min<int>(max_lanes, kMaxLanes), modelled_ms);
+  std::vector<int> widths, where;
+  if (units.size() == 1) widths.push_back(num_sms);
+  else
+    for (size_t l = 0; l < units.size(); ++l) widths.push_back(units[l] * unit + (l == 0 ? rem : 0));
+  *modelled_ms = place_jobs(sorted, widths, &where);
+  *n_lanes = (int32_t)widths.size();
+  for (size_t l = 0; l < widths.size(); ++l) lane_sms[l] = widths[l];
+  for (int i = 0; i < n; ++i) lane_of_job[order[i]] = where[i];
+  return KFB_OK;
+}
+
 size_t kfb_syevd_batch_workspace_bytes(const kfb_syevd_job* jobs, int32_t n_jobs) {
   kfb::Context* ctx = kfb::current_context();
   if (!ctx || !jobs || n_jobs <= 0) return 0;
@@ -407,6 +638,7 @@ int kfb_syevd_batch(const kfb_syevd_job* jobs, int32_t n_jobs, void* workspace, 
   if (!workspace || workspace_bytes < plan.total)
     KFB_FAIL(KFB_ERR_WORKSPACE, "syevd batch workspace: need %zu bytes, got %zu", plan.total, workspace_bytes);
   KFB_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+  std::lock_guard<std::mutex> call_lock(g_call_mu[ctx->device]);
   const int n_lanes = (int)plan.lanes.size();
   // fork: every lane starts after what is already queued on the caller's stream
   KFB_CUDA(cudaEventRecord(pool->start, stream));
@@ -420,7 +652,7 @@ int kfb_syevd_batch(const kfb_syevd_job* jobs, int32_t n_jobs, void* workspace, 
       // syevd's host-side panel loop is what takes the time: one thread per lane lets them overlap
       cudaSetDevice(device);
       kfb_init(device);
-      Lane& lane = pool->lanes[l];
+      Lane& lane = *plan.lane_ptr[l];
       if (cudaStreamWaitEvent(lane.stream, pool->start, 0) != cudaSuccess) { status[l] = KFB_ERR_CUDA; return; }
       for (int i : plan.lanes[l]) {
         const kfb_syevd_job& j = jobs[i];
@@ -443,7 +675,7 @@ int kfb_syevd_batch(const kfb_syevd_job* jobs, int32_t n_jobs, void* workspace, 
   for (auto& t : threads) t.join();
   // join: the caller's stream continues after every lane and the grouped stream
   for (int l = 0; l < n_lanes; ++l)
-    if (!plan.lanes[l].empty()) KFB_CUDA(cudaStreamWaitEvent(stream, pool->lanes[l].done, 0));
+    if (!plan.lanes[l].empty()) KFB_CUDA(cudaStreamWaitEvent(stream, plan.lane_ptr[l]->done, 0));
   if (!plan.groups.empty() && grc == KFB_OK) KFB_CUDA(cudaStreamWaitEvent(stream, pool->grouped.done, 0));
   if (grc) return grc;
   for (int l = 0; l < n_lanes; ++l)

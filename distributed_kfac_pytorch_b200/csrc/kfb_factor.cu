@@ -180,6 +180,12 @@ __global__ void __launch_bounds__(NT) syrk_simt_kernel(const DevJob* __restrict_
     __syncthreads();
   }
 
+  float wgt = s.weight;
+  if (s.dev_scale) {
+    const float m = __ldg(s.dev_scale);
+    if (m == 0.f) return;              // dropped capture: its sums may be inf / nan
+    wgt *= m;
+  }
 #pragma unroll
   for (int p = 0; p < 4; ++p) {
     int i = i0 + ty * 4 + p;
@@ -188,7 +194,7 @@ __global__ void __launch_bounds__(NT) syrk_simt_kernel(const DevJob* __restrict_
     for (int q = 0; q < 4; ++q) {
       int j = j0 + tx * 4 + q;
       if (j >= d || j < i) continue;
-      atomicAdd(job.scratch + (int64_t)i * job.ld_scratch + j, acc[p][q] * s.weight);
+      atomicAdd(job.scratch + (int64_t)i * job.ld_scratch + j, acc[p][q] * wgt);
     }
   }
 }
@@ -214,6 +220,7 @@ __global__ void __launch_bounds__(256) finalize_kernel(const DevJob* __restrict_
   const float ratio = alpha / (1.f - alpha);
   const float one_m = 1.f - alpha;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
+  const float resc = job.dev_rescale ? __ldg(job.dev_rescale) : 1.f;   // < 0: no capture survived, keep the old average
 
   // pass 1: rows of the (bi, bj) block; value valid where j >= i
 #pragma unroll
@@ -224,7 +231,7 @@ __global__ void __launch_bounds__(256) finalize_kernel(const DevJob* __restrict_
     if (i < d && j < d && j >= i) {
       float f = job.scratch[job.native ? native_index(job.T128, i, j) : (int64_t)i * job.ld_scratch + j];
       float old = job.seed_identity ? (i == j ? 1.f : 0.f) : job.state[(int64_t)i * job.ld_state + j];
-      v = (old * ratio + f) * one_m;
+      v = resc < 0.f ? old : (old * ratio + f * resc) * one_m;
       if (job.tri_out) job.tri_out[(int64_t)i * d - ((int64_t)i * (i - 1)) / 2 + (j - i)] = v;
     }
     tile[li][tx] = v;
@@ -479,6 +486,7 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
     dj.n_segments = j.n_segments;
     dj.state = j.state; dj.ld_state = j.ld_state;
     dj.seed_identity = j.seed_identity; dj.write_state = j.write_state; dj.tri_out = j.tri_out;
+    dj.dev_rescale = j.dev_rescale;
     dj.ld_scratch = (j.d + 3) / 4 * 4;
     dj.T = ceil_div(j.d, TS);
     dj.n_pairs = dj.T * (dj.T + 1) / 2;
@@ -492,7 +500,7 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
       memset(&ds, 0, sizeof(ds));
       KFB_REQUIRE(s.dtype >= KFB_F32 && s.dtype <= KFB_BF16, "unknown segment dtype %d", s.dtype);
       ds.data = s.data; ds.dtype = s.dtype; ds.kind = s.kind; ds.has_bias = s.has_bias; ds.c = (int)s.c;
-      ds.h = (int)s.h; ds.w = (int)s.w; ds.ld = s.ld; ds.weight = s.weight;
+      ds.h = (int)s.h; ds.w = (int)s.w; ds.ld = s.ld; ds.weight = s.weight; ds.dev_scale = s.dev_scale;
       ds.kh = ds.kw = ds.sh = ds.sw = 1;
       int feat;
       switch (s.kind) {
@@ -725,6 +733,7 @@ static int cached_plan(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool
       KFB_REQUIRE(j.state, "factor job %d: null state", i);
       DevJob& dj = g_plan.jobs[i];
       dj.state = j.state; dj.seed_identity = j.seed_identity; dj.write_state = j.write_state;
+      dj.dev_rescale = j.dev_rescale;
       dj.tri_out = (dj.fused && j.write_state) ? nullptr : j.tri_out;
       for (int k = 0; k < j.n_segments; ++k) {
         KFB_REQUIRE(j.segments[k].data, "factor job %d segment %d: null data", i, k);
@@ -733,6 +742,7 @@ static int cached_plan(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool
         if (pad >= 0) g_plan.pads[pad].src = j.segments[k].data;   // ds.data is the staging copy
         else ds.data = j.segments[k].data;
         ds.weight = j.segments[k].weight;
+        ds.dev_scale = j.segments[k].dev_scale;
       }
     }
   }
@@ -860,7 +870,7 @@ int kfb_factor_update(const kfb_factor_job* jobs, int32_t n_jobs, float alpha, v
   int rc = kfb::require_context(&ctx);
   if (rc) return rc;
   if (n_jobs == 0) return KFB_OK;
-  KFB_REQUIRE(alpha > 0.f && alpha <= 1.f, "alpha must be in (0, 1], got %g", alpha);
+  KFB_REQUIRE(alpha >= 0.f && alpha <= 1.f, "alpha must be in [0, 1], got %g", alpha);   // 0: state <- F
   if (alpha == 1.f) return KFB_OK;   // update_running_avg is a no-op (kfac/layers/utils.py:175)
   return kfb::factor_update_with(jobs, n_jobs, alpha, ctx, workspace, workspace_bytes, "kfb_factor_update",
                                  (cudaStream_t)stream_);

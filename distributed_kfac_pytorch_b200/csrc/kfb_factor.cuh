@@ -20,6 +20,7 @@ struct DevSegment {
   int64_t ld;            // ROWS pitch
   int64_t K;             // rows of X
   float weight;
+  const float* dev_scale;   // NULL or device multiplier of weight; 0 drops the segment (kfb_capture_filter)
   int n_chunks;          // split-K chunks of this segment
   int chunk_start;       // first chunk index inside the job
   int64_t chunk_len;
@@ -39,6 +40,7 @@ struct DevJob {
   int64_t ld_state;
   int seed_identity, write_state;
   float* tri_out;
+  const float* dev_rescale;  // NULL or device float: >= 0 multiplies F, < 0 leaves the running average untouched
   float* scratch;        // d x d accumulator (upper triangle used), pitch ld_scratch
   int64_t ld_scratch;
   size_t scratch_off;    // host only: float offset into the scratch region

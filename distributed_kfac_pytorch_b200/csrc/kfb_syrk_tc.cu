@@ -524,7 +524,11 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
     for (int round = 0, it; (it = snake_item<kPair>(round, n_items)) >= 0; ++round) {
       const TcItem item = items[it];
       const DevJob& job = jobs[item.job];
-      const float weight = segs[item.seg].weight;
+      // device-side multiplier of the segment weight (AMP unscale; 0 = capture dropped, kfb_capture_filter)
+      const float* dscale = segs[item.seg].dev_scale;
+      const float dmul = dscale ? __ldg(dscale) : 1.f;
+      const bool dropped = dmul == 0.f;                   // warp-uniform: skip every write of this item
+      const float weight = segs[item.seg].weight * dmul;
       const int d = job.d;
       const bool diag = item.a0 == item.b0;
       const float ratio = alpha / (1.f - alpha), one_m = 1.f - alpha;
@@ -582,6 +586,7 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
           for (int c = 0; c < TM / 32; ++c) {
             const int jb = j0 + c * 32;
             if (jb >= d) break;                               // warp-uniform
+            if (dropped) break;
             uint32_t r[32];
             umma::tmem_ld_32x32(taddr + c * 32, r);
             umma::tmem_ld_wait();

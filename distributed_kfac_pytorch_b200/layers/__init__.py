@@ -2,6 +2,7 @@
 import torch.nn as nn
 
 from .. import modules as km
+from . import utils
 from .conv import Conv2dLayer
 from .embedding import EmbeddingLayer
 from .linear import LinearLayer, LinearMultiLayer

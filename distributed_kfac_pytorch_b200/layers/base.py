@@ -19,7 +19,7 @@ import warnings
 import torch
 
 from .. import comm
-from .._native import FactorJob, PrecondJob, get_ops
+from .._native import KFB_SEG_ROWS, CaptureFilter, FactorJob, PrecondJob, get_ops
 
 
 def _round4(n):
@@ -54,8 +54,14 @@ class KFACLayer(object):
         self.symmetry_aware_comm = symmetry_aware_comm
         self.use_eigen_decomp = use_eigen_decomp
         self.eps = 1e-10
-        if inv_dtype not in (None, torch.float32) or factor_dtype not in (None, torch.float32):
-            raise NotImplementedError('the B200 kernels keep factors and inverses in float32')
+        # factor_dtype: captures are rounded to it before the factor math (kfac/layers/base.py:385,409);
+        # inv_dtype: eigenvectors / eigenvalues / dGdA (or the explicit inverses) are rounded to it after the
+        # fp32 solve and travel in it (base.py:435-441, 237-292).  Accumulation, the running averages
+        # and the GEMM chain stay fp32 / TF32 here: a 16-bit type costs the reference precision in every
+        # product, here only in what it stores.
+        for name, dt in (('inv_dtype', inv_dtype), ('factor_dtype', factor_dtype)):
+            if dt not in (None, torch.float32, torch.float16, torch.bfloat16):
+                raise NotImplementedError('%s must be float32, float16 or bfloat16, got %s' % (name, dt))
 
         # Should be overridden by implementing class
         self.has_bias = False
@@ -82,6 +88,12 @@ class KFACLayer(object):
         self._scratch = None                  # (gmat, V, T) views
         self._out = None                      # dg x da preconditioned gradient view
         self._tri_fresh = {'A': False, 'G': False}
+        self._amp_scalars = []                # per-capture device scalars of the AMP capture filters since the last check
+
+    _renormalise_dropped = True               # dropped AMP captures shrink the divisor (get_cov over what is left)
+
+    def _inv16(self):
+        return self.inv_dtype in (torch.float16, torch.bfloat16)
 
     def __repr__(self):
         return 'KFAC {}({})'.format(self.__class__.__name__, repr(self.module))
@@ -184,7 +196,14 @@ class KFACLayer(object):
         """kfac/layers/base.py:371-379."""
         g = grad_output[0].data
         if self.grad_scaler is not None:
-            g = (g, self.grad_scaler.get_scale())
+            # torch's GradScaler keeps its scale in a device scalar; get_scale() would synchronise with
+            # the host on every hook call.  The scale cannot change before K-FAC consumes the capture
+            # (scaler.update() runs after the optimizer step), so a reference to the tensor is enough.
+            scale = getattr(self.grad_scaler, '_scale', None)
+            if not (torch.is_tensor(scale) and scale.is_cuda and scale.dtype == torch.float32
+                    and scale.numel() == 1):
+                scale = self.grad_scaler.get_scale()
+            g = (g, scale)
         if self.accumulate_data:
             self.g_outputs.append(g)
         else:
@@ -198,10 +217,12 @@ class KFACLayer(object):
     def _g_segments(self, g_outputs):
         raise NotImplementedError
 
-    @staticmethod
-    def _as_f32(t):
+    def _as_f32(self, t):
         """Captures are handed to the SYRK as they are when it can read them (fp32, and the fp16 /
-        bf16 tensors autocast produces: they are widened while being gathered, never copied)."""
+        bf16 tensors autocast produces: they are widened while being gathered, never copied).  A 16-bit
+        ``factor_dtype`` rounds fp32 captures to it first, as the reference's ``x.to(factor_dtype)``."""
+        if self.factor_dtype in (torch.float16, torch.bfloat16, torch.float32) and t.dtype != self.factor_dtype:
+            return t.to(self.factor_dtype)
         if t.dtype not in (torch.float32, torch.float16, torch.bfloat16):
             t = t.float()
         return t
@@ -212,6 +233,10 @@ class KFACLayer(object):
         seed = self.state[key] is None
         if seed:
             self._set2d(key, d, d, segments[0].tensor.device)
+            if self.grad_scaler is not None and key == 'G':
+                # the very first update may be dropped on the device (all captures inf / nan)
+                self.state[key].zero_()
+                self.state[key].diagonal().fill_(1.0)
         if alpha == 1:
             # update_running_avg is a no-op for alpha == 1 (kfac/layers/utils.py:175):
             # a fresh factor stays the identity
@@ -233,35 +258,40 @@ class KFACLayer(object):
 
     def _G_job(self, alpha, tri_out=None):
         outputs = self.g_outputs
-        inv_scale_sq = None
-        if self.grad_scaler is not None:
-            # AMP: the captures carry the loss scale.  Drop captures with inf/nan (kfac/layers/
-            # base.py:397-407) and fold the unscale into the segment weight - G is quadratic in g,
-            # so (g/s)^T (g/s) = g^T g / s^2 - instead of dividing the tensors.
-            kept, inv_scale_sq = [], []
-            for g, scale in outputs:
-                g = self._as_f32(g)
-                if not bool(torch.isfinite(g).all()):
-                    continue
-                kept.append(g)
-                inv_scale_sq.append(1.0 / (float(scale) * float(scale)))
-            if len(kept) != len(outputs):
-                warnings.warn('Some gradients were discarded when computing '
-                              'G because they were unable to be unscaled. '
-                              'Note this can degrade KFAC performance if too '
-                              'many gradients are discarded.')
-            outputs = kept
-        else:
-            outputs = [self._as_f32(x) for x in outputs]
-        if len(outputs) == 0:
-            self.g_outputs = []
-            return None
         self.g_outputs = []                      # clear accumulated outputs (base.py:414)
-        d, segments = self._g_segments(outputs)
-        if inv_scale_sq is not None:
-            for seg, f in zip(segments, inv_scale_sq):
-                seg.weight *= f
-        return self._factor_job('G', d, segments, alpha, tri_out)
+        if len(outputs) == 0:
+            return None
+        if self.grad_scaler is None:
+            d, segments = self._g_segments([self._as_f32(x) for x in outputs])
+            return self._factor_job('G', d, segments, alpha, tri_out)
+        # AMP: the captures carry the loss scale and may hold inf / nan.  The reference unscales them,
+        # tests every capture on the host and drops the bad ones (kfac/layers/base.py:397-407: one
+        # synchronisation per capture).  Here the kernel kfb_capture_filter does it on the device: it
+        # writes 1/s^2 (G is quadratic in g: (g/s)^T (g/s) = g^T g / s^2) or 0 into one scalar per capture,
+        # which multiplies that segment's weight inside the SYRK, and one scalar per factor that
+        # renormalises by the rows that are left, or tells the kernels to leave the running average alone.
+        d, segments = self._g_segments([self._as_f32(g) for g, _ in outputs])
+        n = len(segments)
+        scalars = torch.empty(n + 1, device=segments[0].tensor.device, dtype=torch.float32)
+        rows = []
+        for k, seg in enumerate(segments):
+            seg.dev_scale = scalars[k:k + 1]
+            rows.append(seg.n if seg.kind == KFB_SEG_ROWS else seg.n * seg.h * seg.w)
+        job = self._factor_job('G', d, segments, alpha, tri_out)
+        if job is not None:
+            job.dev_rescale = scalars[n:]
+            job.filter = CaptureFilter([seg.tensor for seg in segments], rows, [s for _, s in outputs],
+                                       self._renormalise_dropped, scalars[:n], scalars[n:])
+            self._amp_scalars.append(scalars[:n])
+        return job
+
+    def amp_captures_dropped(self):
+        """Device bool tensor: did a G update since the last call drop a capture (None: no AMP update)."""
+        if not self._amp_scalars:
+            return None
+        flag = torch.cat(self._amp_scalars).eq(0).any()
+        self._amp_scalars = []
+        return flag
 
     def update_A_factor(self, alpha=0.95):
         """Compute factor A and fold it into the running average (base.py:381-390)."""
@@ -337,20 +367,54 @@ class KFACLayer(object):
             factor, out, info = job
             get_ops().cholesky_inverse(factor, damping, out, info)
 
+    def _round16(self, *keys):
+        """Round the named buffers to inv_dtype in place (they stay fp32 tensors holding 16-bit values)."""
+        ops = get_ops()
+        for key in keys:
+            t = self._buf.get(key)
+            if t is None:
+                t = self.state.get(key)
+            if t is None:
+                continue
+            flat = t.reshape(-1) if t.is_contiguous() else None
+            if flat is None:                       # a 1-D view of a slab is contiguous; 2-D buffers are whole
+                raise RuntimeError('cannot round a non-contiguous buffer')
+            tmp = torch.empty(flat.numel(), device=flat.device, dtype=self.inv_dtype)
+            ops.narrow(flat, tmp)
+            ops.widen(tmp, flat)
+
+    def _finish_A_inv(self):
+        if self._inv16():
+            if self.use_eigen_decomp:
+                self._round16('QA', 'dA')
+                get_ops().transpose(self.state['QA'], self._E['A'])
+            else:
+                self._round16('A_inv')
+
     def _finish_G_inv(self, damping):
-        """dGdA = 1/(dG dA^T + damping) on the rank that decomposed G (base.py:300-306)."""
-        if self.prediv_eigenvalues:
+        """dGdA = 1/(dG dA^T + damping) on the rank that decomposed G (base.py:300-306); with a 16-bit
+        inv_dtype everything the reference would store in it is rounded to it (base.py:435-441)."""
+        if self._inv16():
+            if self.use_eigen_decomp:
+                self._round16('QG', 'dG')
+                get_ops().transpose(self.state['QG'], self._E['G'])
+            else:
+                self._round16('G_inv')
+        if self.prediv_eigenvalues and self.use_eigen_decomp:
             if 'dA' not in self.state:
                 raise ValueError('compute_A_inv must be called before '
                                  'compute_G_inv if prediv_eigenvalues '
                                  'is True.')
             get_ops().outer_recip(self.state['dG'], self.state['dA'], damping, self.state['dGdA'])
+            if self._inv16():
+                self._round16('dGdA')
 
     def compute_A_inv(self, damping=0.001, ignore_rank=False):
         """Eigendecompose A on its assigned rank (kfac/layers/base.py:198-256)."""
         job = self._inv_job('A', ignore_rank)
         if job is not None:
             self._run_inv_job(job, damping)
+            self._finish_A_inv()
 
     def compute_G_inv(self, damping=0.001, ignore_rank=False):
         """Eigendecompose G on its assigned rank and, with prediv_eigenvalues, build
@@ -358,8 +422,7 @@ class KFACLayer(object):
         job = self._inv_job('G', ignore_rank)
         if job is not None:
             self._run_inv_job(job, damping)
-            if self.use_eigen_decomp:
-                self._finish_G_inv(damping)
+            self._finish_G_inv(damping)
 
     def broadcast_inverses(self):
         """Ship QA, QG and dGdA (or dA, dG) over the inverse groups (base.py:129-171).

@@ -35,5 +35,7 @@ class LinearMultiLayer(LinearLayer):
     """Linear called once per timestep: the factor is the SUM over calls of the per-call
     covariance, each divided by its own row count (kfac/layers/linear.py:27-59)."""
 
+    _renormalise_dropped = False     # a dropped AMP capture just leaves the sum: every call has its own divisor
+
     def _segments(self, tensors, has_bias):
         return [_rows_segment(t, 1.0 / (t.numel() // t.shape[-1]), has_bias) for t in tensors]

@@ -172,6 +172,7 @@ class KFAC(optim.Optimizer):
         self.layers = []
         self.hook_layers = {}  # key: nn.Module, value: KFACLayer
         self._inv_slabs = None     # [(src, CommGroup, slab)]: fused inverse broadcast
+        self._inv_slabs16 = None   # their 16-bit travelling copies (inv_dtype float16 / bfloat16)
         self._grad_slabs = None    # [(src, CommGroup, slab)]: fused gradient broadcast
         self._tri_slab = None      # packed-triangle allreduce fusion buffer
         self._tri_views = None     # per layer {'A': view, 'G': view}
@@ -451,32 +452,66 @@ class KFAC(optim.Optimizer):
                 layer.compute_G_inv(damping=damping)
             self._check_info()
             return
-        jobs, g_done = [], []
+        jobs, a_done, g_done = [], [], []
         for layer in self.layers:
             a_job = layer._inv_job('A')
             g_job = layer._inv_job('G')
             if a_job is not None:
                 jobs.append(a_job)
+                a_done.append(layer)
             if g_job is not None:
                 jobs.append(g_job)
                 g_done.append(layer)
         # all of this rank's decompositions in one call: they overlap on the library's lanes
         get_ops().syevd_batch(jobs)
+        for layer in a_done:
+            layer._finish_A_inv()
         for layer in g_done:
             layer._finish_G_inv(damping)
         self._check_info()
 
     def _check_info(self):
+        """The one host synchronisation of an inverse update: cuSOLVER's devInfo words and, under AMP,
+        whether the on-device capture filter dropped output gradients since the last check (the
+        reference warns at once, kfac/layers/base.py:403-407, at the cost of a sync per capture)."""
         if self.check_eig_info:
-            infos = [l._info for l in self.layers if l._info is not None]
-            if infos and bool(torch.stack(infos).ne(0).any()):
+            infos = [l._info.ne(0).any() for l in self.layers if l._info is not None]
+            dropped = [f for f in (l.amp_captures_dropped() for l in self.layers) if f is not None]
+            if not infos and not dropped:
+                return
+            flags = torch.stack([torch.stack(infos).any() if infos else torch.zeros((), dtype=torch.bool, device=dropped[0].device),
+                                 torch.stack(dropped).any() if dropped else torch.zeros((), dtype=torch.bool, device=infos[0].device)])
+            failed, lost = (bool(v) for v in flags.tolist())
+            if lost:
+                warnings.warn('Some gradients were discarded when computing '
+                              'G because they were unable to be unscaled. '
+                              'Note this can degrade KFAC performance if too '
+                              'many gradients are discarded.')
+            if failed:
                 raise RuntimeError('cuSOLVER reported a failed factorisation for at least one factor')
 
     def broadcast_inverses(self):
         """preconditioner.py:535-543."""
         if comm.backend.size() == 1:
             return
-        if self._inv_slabs is not None:
+        if self._inv_slabs is not None and self.inv_dtype in (torch.float16, torch.bfloat16):
+            # 16-bit inv_dtype: the slab travels in 16 bits (kfac/layers/base.py:237-292 allocates the
+            # receive buffers in inv_dtype) and is widened again for the fp32 / TF32 GEMM chain
+            ops, rank = get_ops(), comm.backend.rank()
+            if self._inv_slabs16 is None:
+                self._inv_slabs16 = [torch.empty(slab.numel(), device=slab.device, dtype=self.inv_dtype)
+                                     for _, _, slab in self._inv_slabs]
+            handles = []
+            for (src, group, slab), slab16 in zip(self._inv_slabs, self._inv_slabs16):
+                if rank == src:
+                    ops.narrow(slab, slab16)
+                handles.append(comm.backend.broadcast(slab16, src=src, group=group))
+            comm.backend.sync(handles)
+            for (src, group, slab), slab16 in zip(self._inv_slabs, self._inv_slabs16):
+                if rank != src:
+                    ops.widen(slab16, slab)
+            handles = []
+        elif self._inv_slabs is not None:
             handles = [comm.backend.broadcast(slab, src=src, group=group)
                        for src, group, slab in self._inv_slabs]
         else:
@@ -592,7 +627,7 @@ class KFAC(optim.Optimizer):
         `broadcast_gradients` one per source in this rank's gradient group (instead of one or two
         per layer every step: base.py:173-196).  Zero copies: the layers' tensors ARE the slab."""
         from .layers.base import _round4
-        self._inv_slabs, self._grad_slabs = None, None
+        self._inv_slabs, self._grad_slabs, self._inv_slabs16 = None, None, None
         if comm.backend.size() == 1 or len(self.layers) == 0:
             return
         rank = comm.backend.rank()

@@ -42,7 +42,7 @@ typedef enum {
   KFB_ERR_WORKSPACE = 5    /* caller-provided workspace too small */
 } kfb_status;
 
-#define KFB_ABI_VERSION 1
+#define KFB_ABI_VERSION 2
 
 /* ---- library ------------------------------------------------------------------ */
 KFB_API int kfb_version(void);
@@ -87,6 +87,10 @@ typedef struct kfb_segment {
   int32_t dtype;         /* element type of `data`: KFB_F32 (0), KFB_F16 (1) or KFB_BF16 (2).  16-bit captures
                             (AMP autocast activations / output gradients) are widened to fp32 as they are
                             gathered; accumulation and the factor stay fp32 */
+  const float* dev_scale; /* NULL, or a DEVICE float that multiplies `weight` when the kernels run; 0 drops the
+                            segment altogether (its data may then hold inf / nan).  Written by
+                            kfb_capture_filter: the GradScaler handling of kfac/layers/base.py:397-407
+                            without a host round trip */
 } kfb_segment;
 enum { KFB_F32 = 0, KFB_F16 = 1, KFB_BF16 = 2 };
 
@@ -100,7 +104,42 @@ typedef struct kfb_factor_job {
   int32_t write_state;           /* 1: write the full (mirrored) square into state */
   float* tri_out;                /* NULL, or d(d+1)/2 floats: packed upper triangle (row by row) of the
                                     new state - a slot of the caller's allreduce fusion buffer */
+  const float* dev_rescale;      /* NULL, or a DEVICE float r: r >= 0 multiplies F (rows captured / rows kept
+                                    after kfb_capture_filter dropped segments); r < 0 means every segment was
+                                    dropped: the running average is left as it is (base.py:409-410) */
 } kfb_factor_job;
+
+/* AMP captures: which output-gradient captures are usable, decided ON THE DEVICE.  Replaces the
+ * unscale + `torch.isinf(g).any() or torch.isnan(g).any()` of KFACLayer.update_G_factor
+ * (kfac/layers/base.py:397-407), which costs the reference one host synchronisation per capture.
+ * For every capture c:  dev_scale[c] = all_finite(data_c) ? inv_scale_sq : 0, where inv_scale_sq is
+ * 1 / s^2 with the loss scale s read from the device float `loss_scale` (NULL: host_inv_scale_sq is
+ * used) - G is quadratic in g, so (g/s)^T (g/s) = g^T g / s^2.  Captures of one factor share a
+ * `group`; for every group g: dev_rescale[g] = -1 if no capture survived, else rows(all) / rows(kept)
+ * when `renormalise` (the reference concatenates the surviving captures and divides by THEIR row
+ * count, kfac/layers/utils.py:107-124,36-41) or 1 (LinearMultiLayer: every call has its own divisor). */
+typedef struct kfb_filter_job {
+  const void* data; int64_t numel; int32_t dtype;   /* the capture */
+  int32_t group;                                    /* index into the group arrays below */
+  float rows;                                       /* rows of X this capture contributes */
+  float host_inv_scale_sq;                          /* used when loss_scale == NULL */
+  const float* loss_scale;                          /* device float (GradScaler._scale) or NULL */
+  float* dev_scale;                                 /* out: device float, see kfb_segment.dev_scale */
+} kfb_filter_job;
+typedef struct kfb_filter_group {
+  float* dev_rescale;                               /* out: device float, see kfb_factor_job.dev_rescale */
+  int32_t renormalise;
+  int32_t reserved;
+} kfb_filter_group;
+KFB_API int kfb_capture_filter(const kfb_filter_job* jobs, int32_t n_jobs, const kfb_filter_group* groups,
+                               int32_t n_groups, void* stream);
+
+/* ---- 16-bit storage of the inverses (inv_dtype = float16 / bfloat16, kfac/layers/base.py:435-441) ----
+ * The eigendecomposition runs in fp32; its results are then ROUNDED to the 16-bit type, travel in 16
+ * bits (halving the inverse broadcast) and are widened again for the fp32 / TF32 GEMM chain.
+ * dst16[i] = narrow(src[i]) and dst[i] = widen(src16[i]) over flat arrays; `dtype` is KFB_F16 / KFB_BF16. */
+KFB_API int kfb_narrow(const float* src, void* dst16, int64_t n, int32_t dtype, void* stream);
+KFB_API int kfb_widen(const void* src16, float* dst, int64_t n, int32_t dtype, void* stream);
 
 KFB_API size_t kfb_factor_workspace_bytes(const kfb_factor_job* jobs, int32_t n_jobs);
 KFB_API int kfb_factor_update(const kfb_factor_job* jobs, int32_t n_jobs, float alpha,
@@ -151,15 +190,17 @@ KFB_API int kfb_syevd(const float* factor, int64_t ld_factor, int32_t d,
               void* workspace, size_t workspace_bytes, int32_t* dev_info, void* stream);
 /* Many eigendecompositions at once, still all cuSOLVER: factors of the same size (small and medium
  * ones, where it measures faster) are solved together by cusolverDnXsyevBatched; the rest are
- * spread, longest first, over a small pool of internal worker lanes - one host thread, CUDA stream
- * and cuSOLVER handle each - so that their host-driven panel loops overlap.  Where the driver has
- * green contexts (CUDA >= 12.4) every lane's stream lives in its own green context with an equal
- * share of the SMs, created the first time the call runs on a device and kept for the life of the
- * process: launches into one context serialise across threads, launches into different green
- * contexts do not (KFB_SYEVD_GREEN=0: ordinary streams).  Everything starts after
- * the work already queued on `stream` and `stream` waits for all of it, so to the caller it behaves
- * like one asynchronous call on `stream`.  Results match kfb_syevd job by job (eigenvectors up to
- * sign). */
+ * spread over internal worker lanes - one host thread, CUDA stream and cuSOLVER handle each.  Where
+ * the driver has green contexts (CUDA >= 12.4) the lanes run on DISJOINT SM partitions of DIFFERENT
+ * widths, planned per call from the job list with a measured (factor size x SMs) time table: large
+ * factors need many SMs, small ones lose little on 8 or 16 (kfb_syevd_lane_plan shows the plan).  A
+ * job list that one full-width stream serves best (e.g. a single large factor) gets exactly that.
+ * Partitions are created on first use (a few ms per lane) and kept for the life of the process.
+ * Under a profiler, with KFB_SYEVD_GREEN=0, or when the driver refuses a partition, the lanes are
+ * two ordinary streams.  Everything starts after the work already queued on `stream` and `stream`
+ * waits for all of it, so to the caller it behaves like one asynchronous call on `stream`.  One call
+ * at a time per device (a second caller blocks until the first has queued its work).  Results match
+ * kfb_syevd job by job (eigenvectors up to sign). */
 typedef struct kfb_syevd_job {
   const float* factor; int64_t ld_factor;
   float* E; int64_t ld_e;
@@ -170,6 +211,15 @@ typedef struct kfb_syevd_job {
   int32_t reserved;
 } kfb_syevd_job;
 KFB_API size_t kfb_syevd_batch_workspace_bytes(const kfb_syevd_job* jobs, int32_t n_jobs);
+/* The lane planner of kfb_syevd_batch on its own (host only, no GPU needed): given the sizes of the
+ * factors that go to syevd, how the SMs of a `num_sms`-SM B200 would be partitioned into at most
+ * `max_lanes` (<= 8) lanes and which lane each factor would run on, from the measured (size x SMs)
+ * time table built into the library.  lane_of_job[n], lane_sms[8]; *modelled_ms = planned makespan.
+ * The placement of the eigendecompositions on RANKS is the reference's allocator
+ * (kfac/utils.py:169-196, bit-exact in utils.py); this is the placement inside one rank's GPU, which
+ * the reference leaves to a serial loop (kfac/preconditioner.py:555-564). */
+KFB_API int kfb_syevd_lane_plan(const int32_t* dims, int32_t n, int32_t num_sms, int32_t max_lanes,
+                                int32_t* lane_of_job, int32_t* lane_sms, int32_t* n_lanes, double* modelled_ms);
 KFB_API int kfb_syevd_batch(const kfb_syevd_job* jobs, int32_t n_jobs, void* workspace, size_t workspace_bytes,
                             void* stream);
 /* Explicit damped inverse, out = (factor + damping I)^-1, by Cholesky factorisation (cuSOLVER potrf +

@@ -10,6 +10,8 @@ from distributed_kfac_pytorch_b200 import (KFAC, CommMethod, KFACParamScheduler,
 for _name in ('comm', 'layers', 'modules', 'utils', 'preconditioner', 'scheduler'):
     _sys.modules[__name__ + '.' + _name] = getattr(_impl, _name)
 _sys.modules[__name__ + '.modules.lstm'] = _impl.modules.lstm
-_sys.modules[__name__ + '.layers.utils'] = _impl.layers   # placeholder namespace
+_sys.modules[__name__ + '.layers.utils'] = _impl.layers.utils
+for _sub in ('base', 'conv', 'linear', 'embedding'):
+    _sys.modules[__name__ + '.layers.' + _sub] = getattr(_impl.layers, _sub)
 
 __all__ = ['KFAC', 'CommMethod', 'KFACParamScheduler', 'comm', 'layers', 'modules', 'utils']

@@ -48,19 +48,43 @@ class OracleOps(object):
 
     def factor_update(self, jobs, alpha):
         self.calls.append(('factor_update', len(jobs)))
+        self.capture_filter([j.filter for j in jobs if j.filter is not None])
         for j in jobs:
             f = None
             for s in j.segments:
+                mul = 1.0 if s.dev_scale is None else float(s.dev_scale)
+                if mul == 0.0:
+                    continue
                 x = segment_matrix(s)
-                c = s.weight * (x.t() @ x)
+                c = (s.weight * mul) * (x.t() @ x)
                 f = c if f is None else f + c
-            f = (f + f.t()) / 2
             old = torch.eye(j.d) if j.seed_identity else j.state.clone()
-            new = O.running_average_(f, old, alpha)
+            resc = 1.0 if j.dev_rescale is None else float(j.dev_rescale)
+            if resc < 0 or f is None:
+                new = old
+            else:
+                f = (f + f.t()) / 2 * resc
+                new = O.running_average_(f, old, alpha)
             if j.write_state:
                 j.state.copy_(new)
             if j.tri_out is not None:
                 j.tri_out.copy_(triu_pack(new))
+
+    def capture_filter(self, filters):
+        for f in filters:
+            kept = total = 0.0
+            for k, (t, rows, scale) in enumerate(zip(f.tensors, f.rows, f.scales)):
+                ok = bool(torch.isfinite(t).all())
+                f.dev_scales[k] = 1.0 / float(scale) ** 2 if ok else 0.0
+                total += rows
+                kept += rows if ok else 0.0
+            f.dev_rescale[0] = -1.0 if kept == 0 else (total / kept if f.renormalise else 1.0)
+
+    def narrow(self, src, dst16):
+        dst16.copy_(src.to(dst16.dtype))
+
+    def widen(self, src16, dst):
+        dst.copy_(src16.float())
 
     def tri_pack(self, pairs):
         self.calls.append(('tri_pack', len(pairs)))

@@ -18,6 +18,7 @@ the API used at kfac/layers/utils.py:63), and writes
     tests/golden/cnn_world2_variants.pt   2-rank gloo: precompute_outer_eigen=False under COMM_OPT and
                                  HYBRID_OPT, and distribute_layer_factors=True (A and G on different ranks)
     tests/golden/shared_module.pt   register_shared_module (tied encoder/decoder weight), single process
+    tests/golden/cnn_amp.pt      inv_dtype=float16, and GradScaler captures with injected inf / nan
 
 Nothing here is imported by the product or by the tests; the tests only read the
 files it wrote.
@@ -132,6 +133,54 @@ def gen_cnn_variants():
                      'scale': scale, 'steps': steps}
     torch.save(out, os.path.join(HERE, 'cnn_variants.pt'))
     print('cnn_variants: ok')
+
+
+def gen_amp_variants():
+    """inv_dtype=float16 (eigenvectors / dGdA stored, shipped and multiplied in 16
+    bits: kfac/layers/base.py:435-441,459-470) and the GradScaler capture filter with injected inf / nan
+    (base.py:397-407): one of two accumulated captures dropped for one layer, both dropped for another."""
+    torch.set_num_threads(1)
+    out = {}
+    # -- inv_dtype = float16
+    model = models.make_cnn()
+    opt = torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.9)
+    pre = kfac.KFAC(model, **dict(KFAC_ARGS, inv_dtype=torch.float16))
+    steps = []
+    for s in range(3):
+        opt.zero_grad()
+        x, y = models.cnn_batch(10 * s)
+        F.cross_entropy(model(x), y).backward()
+        pre.step()
+        steps.append({'grads_out': [_grads(l) for l in pre.layers],
+                      'A': [l.state['A'].clone() for l in pre.layers],
+                      'G': [l.state['G'].clone() for l in pre.layers]})
+        opt.step()
+    assert pre.layers[0].state['QA'].dtype == torch.float16
+    out['inv_fp16'] = {'kwargs': dict(inv_dtype=torch.float16), 'micro': 1, 'scale': 1.0, 'steps': steps}
+    # -- GradScaler with captures that cannot be unscaled
+    scale = 1024.0
+    model = models.make_cnn()
+    opt = torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.9)
+    pre = kfac.KFAC(model, **dict(KFAC_ARGS, accumulate_data=True, grad_scaler=models.FixedScaler(scale)))
+    steps = []
+    for s in range(3):
+        opt.zero_grad()
+        for m in range(2):
+            x, y = models.cnn_batch(10 * s + m)
+            (F.cross_entropy(model(x), y) * scale / 2).backward()
+        for p in model.parameters():
+            p.grad.div_(scale)
+        if s == 1:
+            models.poison_captures(pre.layers)
+        pre.step()
+        steps.append({'grads_out': [_grads(l) for l in pre.layers],
+                      'A': [l.state['A'].clone() for l in pre.layers],
+                      'G': [l.state['G'].clone() for l in pre.layers]})
+        opt.step()
+    out['grad_scaler_inf'] = {'kwargs': dict(accumulate_data=True), 'micro': 2, 'scale': scale, 'steps': steps,
+                              'poison_step': 1}
+    torch.save(out, os.path.join(HERE, 'cnn_amp.pt'))
+    print('cnn_amp: ok')
 
 
 def gen_resnet32():
@@ -264,7 +313,8 @@ def gen_cnn_world2_variants():
     cases = [('COMM_OPT/no_prediv', 'COMM_OPT', 1.0, dict(precompute_outer_eigen=False)),
              ('HYBRID_OPT/no_prediv', 'HYBRID_OPT', 0.5, dict(precompute_outer_eigen=False)),
              ('COMM_OPT/distributed', 'COMM_OPT', 1.0,
-              dict(precompute_outer_eigen=False, distribute_layer_factors=True))]
+              dict(precompute_outer_eigen=False, distribute_layer_factors=True)),
+             ('COMM_OPT/inv_fp16', 'COMM_OPT', 1.0, dict(inv_dtype=torch.float16))]
     for i, (key, name, frac, extra) in enumerate(cases):
         tmp = '/tmp/_golden_w2v_%d.pt' % i
         mp.spawn(_world2_worker, args=(2, 29691 + i, name, frac, tmp, extra), nprocs=2, join=True)
@@ -363,3 +413,5 @@ if __name__ == '__main__':
         gen_cnn_world2_variants()
     if 'shared' in which:
         gen_shared_module()
+    if 'amp' in which:
+        gen_amp_variants()

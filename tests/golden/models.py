@@ -151,6 +151,20 @@ def tied_batch(step, n=8):
     return torch.randn(n, 12, generator=g), torch.randint(0, 10, (n,), generator=g)
 
 
+def poison_captures(layers):
+    """What an fp16 overflow does to K-FAC's captures: layer 1 loses the FIRST of its two accumulated
+    output-gradient captures (one inf), layer 3 loses BOTH (inf and nan), so its G must stay as it is.
+    Works on the reference's KFACLayer and on this repository's alike: g_outputs holds (tensor, scale)."""
+    def spoil(layer, idx, value):
+        g, scale = layer.g_outputs[idx]
+        g = g.clone()
+        g.view(-1)[3] = value
+        layer.g_outputs[idx] = (g, scale)
+    spoil(layers[1], 0, float('inf'))
+    spoil(layers[3], 0, float('inf'))
+    spoil(layers[3], 1, float('nan'))
+
+
 def make_cnn(seed=0):
     torch.manual_seed(seed)
     return SmallCNN()

@@ -30,7 +30,7 @@ def test_header_and_binding_agree(lib):
     assert declared == sorted(_native.EXPORTED_SYMBOLS)
     for name in declared:
         assert hasattr(lib, name), name
-    assert lib.kfb_version() == 1
+    assert lib.kfb_version() == 2
 
 
 def test_errors_without_context(lib):
@@ -52,3 +52,25 @@ def test_no_cpu_fallback(lib):
     a = torch.eye(4)
     with pytest.raises(_native.NativeError):
         ops.transpose(a, a.clone())
+
+
+def test_syevd_lane_planner(lib):
+    """Host logic of kfb_syevd_batch: lanes of different widths from the measured time table."""
+    # ResNet-50 on one GPU, the factors that go to syevd (the rest is batched)
+    singles = [4608] * 3 + [2304] * 6 + [2048] * 7 + [1152] * 4 + [576] * 3
+    lane_of, sms, ms = _native.syevd_lane_plan(singles, 148, 6)
+    _, one_sms, one_ms = _native.syevd_lane_plan(singles, 148, 1)
+    assert one_sms == [148] and 650 < one_ms < 800
+    assert 2 <= len(sms) <= 6 and sum(sms) <= 148 and sms == sorted(sms, reverse=True)
+    assert all(w % 8 == 0 or i == 0 for i, w in enumerate(sms))     # units of 8 SMs; lane 0 takes the remainder too
+    assert ms < 0.5 * one_ms
+    assert len(lane_of) == len(singles) and set(lane_of) <= set(range(len(sms)))
+    # the 4608-dim factors sit on the widest lanes, the 576s on the narrow ones
+    assert max(lane_of[i] for i in range(3)) <= min(lane_of[i] for i in range(len(singles) - 3, len(singles)))
+    # rank 0 of 8 holds one 4608 + one 512 layer: one full-width stream beats any partition
+    lane_of, sms, ms = _native.syevd_lane_plan([4608, 512], 148, 6)
+    assert sms == [148] and lane_of == [0, 0] and 90 < ms < 100
+    # two lanes, mid-size mix: wide + narrow
+    lane_of, sms, ms = _native.syevd_lane_plan([2304, 2048, 2048, 1152, 1024, 1024, 576], 148, 2)
+    assert len(sms) == 2 and sms[0] > sms[1] and sum(sms) == 148
+    assert lib.kfb_syevd_lane_plan(None, 0, 148, 2, None, None, None, None) != 0

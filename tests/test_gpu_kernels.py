@@ -504,6 +504,74 @@ def test_precondition_chain_and_kl_clip(ops):
     torch.testing.assert_close(jobs[0].weight_grad.reshape(before.shape), before, rtol=0, atol=0)
 
 
+def test_capture_filter_and_16bit_round_trip(ops):
+    """kfb_capture_filter (finite test, 1/s^2, renormalisation, skip) and kfb_narrow / kfb_widen."""
+    g = torch.Generator(device=DEV).manual_seed(5)
+    caps = [torch.randn(4, 6, 5, 5, device=DEV, generator=g) for _ in range(3)]
+    caps += [torch.randn(64, 33, device=DEV, generator=g).half(), torch.randn(1000, device=DEV, generator=g).bfloat16()]
+    caps[1].view(-1)[-1] = float('nan')                 # in the scalar tail of the scan
+    caps[3].view(-1)[17] = float('inf')
+    scale_dev = torch.full((1,), 8.0, device=DEV)
+    scal = torch.empty(5 + 3, device=DEV)
+    f1 = N.CaptureFilter(caps[:3], [100.0, 100.0, 50.0], [4.0, scale_dev, scale_dev], True, scal[0:3], scal[5:6])
+    f2 = N.CaptureFilter(caps[3:4], [64.0], [2.0], True, scal[3:4], scal[6:7])
+    f3 = N.CaptureFilter(caps[4:5], [10.0], [2.0], False, scal[4:5], scal[7:8])
+    ops.capture_filter([f1, f2, f3])
+    got = scal.cpu().tolist()
+    assert got[:5] == [1 / 16.0, 0.0, 1 / 64.0, 0.0, 0.25]
+    assert got[5:] == [250.0 / 150.0, -1.0, 1.0]
+    # a dropped segment contributes nothing even though its sums are nan; a skipped job keeps its state
+    x = caps[0][:, :, 0, 0].contiguous()          # 4 x 6 rows
+    bad = x.clone()
+    bad[0, 0] = float('nan')
+    keep, drop, skip = scal[0:1], scal[1:2], scal[6:7]
+    seg_ok = N.Segment(N.KFB_SEG_ROWS, x, 4, 6, 0.25, ld=6)
+    seg_bad = N.Segment(N.KFB_SEG_ROWS, bad, 4, 6, 0.25, ld=6)
+    seg_ok.dev_scale, seg_bad.dev_scale = keep, drop
+    _, st = alloc2d(6, 6, DEV, zero=True)
+    ops.factor_update([N.FactorJob(6, [seg_ok, seg_bad], st, False, True, None)], 0.5)
+    ref = 0.5 * (0.25 / 16.0) * (x.t() @ x)
+    torch.testing.assert_close(st, ref, rtol=1e-5, atol=1e-7)
+    st2 = torch.full((6, 8), 3.0, device=DEV)[:, :6]
+    job = N.FactorJob(6, [seg_ok], st2, False, True, None)
+    job.dev_rescale = skip
+    ops.factor_update([job], 0.5)
+    assert torch.equal(st2, torch.full_like(st2, 3.0))
+    for dt in (torch.float16, torch.bfloat16):
+        src = torch.randn(1003, device=DEV, generator=g) * 3
+        n16 = torch.empty(1003, device=DEV, dtype=dt)
+        ops.narrow(src, n16)
+        assert torch.equal(n16, src.to(dt))
+        back = torch.empty(1003, device=DEV)
+        ops.widen(n16, back)
+        assert torch.equal(back, src.to(dt).float())
+
+
+def test_layer_utils_api(ops):
+    """kfac.layers.utils: the stand-alone helpers of the reference (kfac/layers/utils.py), on the kernels."""
+    from distributed_kfac_pytorch_b200.layers import utils as U
+    g = torch.Generator(device=DEV).manual_seed(9)
+    a = torch.randn(50, 13, device=DEV, generator=g)
+    b = torch.randn(50, 13, device=DEV, generator=g)
+    torch.testing.assert_close(U.get_cov(a), O.second_moment(a.cpu()).to(DEV), rtol=2e-3, atol=1e-4)
+    torch.testing.assert_close(U.get_cov(a, b, scale=7.0), (a.t() @ (b / 7.0)), rtol=2e-3, atol=2e-3)
+    f = U.get_cov(a) + torch.eye(13, device=DEV)
+    q, d = U.get_eigendecomp(f, concat=False)
+    torch.testing.assert_close((q * d) @ q.t(), f, rtol=1e-4, atol=1e-4)
+    assert U.get_eigendecomp(f).shape == (13, 14)
+    torch.testing.assert_close(U.get_inverse(f, damping=0.1) @ (f + 0.1 * torch.eye(13, device=DEV)),
+                               torch.eye(13, device=DEV), rtol=1e-3, atol=1e-3)
+    tri = U.get_triu(f)
+    assert tri.numel() == 13 * 14 // 2
+    torch.testing.assert_close(U.fill_triu([13, 13], tri), f, rtol=0, atol=0)
+    assert U.append_bias_ones(a).shape == (50, 14) and bool((U.append_bias_ones(a)[:, -1] == 1).all())
+    cur = torch.eye(13, device=DEV)
+    U.update_running_avg(f, cur, 0.9)
+    torch.testing.assert_close(cur, 0.9 * torch.eye(13, device=DEV) + 0.1 * f, rtol=1e-5, atol=1e-6)
+    with pytest.raises(ValueError):
+        U.get_cov(a[0])
+
+
 def test_native_errors_are_loud(ops):
     _, st = alloc2d(8, 8, DEV)
     bad = N.Segment(N.KFB_SEG_ROWS, torch.zeros(4, 5, device=DEV), 4, 5, 1.0, ld=5)   # 5 features, d = 8

@@ -59,7 +59,8 @@ def test_nccl_ranks_match_reference(tmp_path, world, idx, method, fraction):
 
 @pytest.mark.parametrize('idx,key,method,fraction', [(0, 'COMM_OPT/no_prediv', 'COMM_OPT', 1.0),
                                                      (1, 'HYBRID_OPT/no_prediv', 'HYBRID_OPT', 0.5),
-                                                     (2, 'COMM_OPT/distributed', 'COMM_OPT', 1.0)])
+                                                     (2, 'COMM_OPT/distributed', 'COMM_OPT', 1.0),
+                                                     (3, 'COMM_OPT/inv_fp16', 'COMM_OPT', 1.0)])
 def test_two_gpus_switches_match_reference(tmp_path, idx, key, method, fraction):
     import world_replay
     gold = load_golden('cnn_world2_variants.pt')[key]

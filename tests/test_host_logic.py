@@ -258,17 +258,18 @@ def test_world_gloo_matches_reference(tmp_path, world, idx, method, fraction):
 
 @pytest.mark.parametrize('idx,key,method,fraction', [(0, 'COMM_OPT/no_prediv', 'COMM_OPT', 1.0),
                                                      (1, 'HYBRID_OPT/no_prediv', 'HYBRID_OPT', 0.5),
-                                                     (2, 'COMM_OPT/distributed', 'COMM_OPT', 1.0)])
+                                                     (2, 'COMM_OPT/distributed', 'COMM_OPT', 1.0),
+                                                     (3, 'COMM_OPT/inv_fp16', 'COMM_OPT', 1.0)])
 def test_world2_switches_match_reference(tmp_path, idx, key, method, fraction):
     """Eigenvalues travelling instead of dGdA (precompute_outer_eigen=False: the 1-D entries of the
-    fused inverse slab) and A / G decomposed on different ranks (distribute_layer_factors=True,
-    kfac/preconditioner.py:638-645)."""
+    fused inverse slab), A / G decomposed on different ranks (distribute_layer_factors=True,
+    kfac/preconditioner.py:638-645), and inverses that travel in 16 bits (inv_dtype=float16)."""
     import world_replay
     gold = load_golden('cnn_world2_variants.pt')[key]
     ranks = _spawn_world(tmp_path, 2, 29761 + idx, method, fraction, gold['kwargs'])
     for r in ranks:
         world_replay.compare(r, gold)
-        n_held = 0
+        n_held = 0 if 'no_prediv' in key or 'distributed' in key else 1
         for (da, dg), vec in zip(r['dims'], r['vec_numel']):
             if vec is not None:           # this rank is a gradient worker of the layer
                 assert vec == (da, dg)    # dA / dG views carved out of the slab have their full length
@@ -308,3 +309,81 @@ def _run_variant(name, device='cpu'):
 @pytest.mark.parametrize('name', ['in_hook', 'accumulate', 'no_prediv', 'grad_scaler', 'inverse'])
 def test_variants_match_reference(cpu_ops, name):
     _run_variant(name)
+
+
+# ---- 16-bit inverses, GradScaler captures that cannot be unscaled -----------------
+
+def _run_amp_variant(name, device='cpu', scaler=None):
+    rec = load_golden('cnn_amp.pt')[name]
+    model = models.make_cnn().to(device)
+    opt = torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.9)
+    kw = dict(damping=0.003, factor_decay=0.95, factor_update_freq=1, inv_update_freq=2, kl_clip=0.001,
+              lr=0.1)
+    scale = rec['scale']
+    extra = dict(rec['kwargs'])
+    if scale != 1.0:
+        extra['grad_scaler'] = scaler if scaler is not None else models.FixedScaler(scale)
+    pre = kfac.KFAC(model, **dict(kw, **extra))
+    for s, gold in enumerate(rec['steps']):
+        opt.zero_grad()
+        for m in range(rec['micro']):
+            x, y = models.cnn_batch(10 * s + m)
+            (F.cross_entropy(model(x.to(device)), y.to(device)) * scale / rec['micro']).backward()
+        if scale != 1.0:
+            for p in model.parameters():
+                p.grad.div_(scale)
+        if rec.get('poison_step') == s:
+            models.poison_captures(pre.layers)
+        pre.step()
+        for i, layer in enumerate(pre.layers):
+            torch.testing.assert_close(layer.state['A'].cpu(), gold['A'][i], **FACTOR_TOL)
+            torch.testing.assert_close(layer.state['G'].cpu(), gold['G'][i], **FACTOR_TOL)
+            torch.testing.assert_close(layer.module.weight.grad.cpu(), gold['grads_out'][i][0].float(), **GRAD_TOL)
+        opt.step()
+    return pre
+
+
+def test_inv_dtype_float16_matches_reference(cpu_ops):
+    pre = _run_amp_variant('inv_fp16')
+    q = pre.layers[1].state['QA']
+    assert torch.equal(q, q.half().float())          # what is stored are 16-bit values
+    with pytest.raises(NotImplementedError):
+        kfac.KFAC(models.make_cnn(), inv_dtype=torch.float64)
+
+
+def test_unscalable_captures_are_dropped_like_the_reference(cpu_ops):
+    with pytest.warns(UserWarning, match='discarded'):
+        _run_amp_variant('grad_scaler_inf')
+
+
+
+# ---- register_shared_module (kfac/preconditioner.py:404-470) --------------------------------------
+
+def _run_shared(device='cpu'):
+    rec = load_golden('shared_module.pt')
+    model = models.make_tied().to(device)
+    opt = torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.9)
+    pre = kfac.KFAC(model, **rec['kwargs'])
+    with pytest.warns(UserWarning):
+        pre.register_shared_module(model.first, model.second)
+    assert len(pre.layers) == rec['n_layers'] == 2
+    for s, gold in enumerate(rec['steps']):
+        x, y = models.tied_batch(s)
+        opt.zero_grad()
+        F.cross_entropy(model(x.to(device)), y.to(device)).backward()
+        pre.step()
+        for i, layer in enumerate(pre.layers):
+            torch.testing.assert_close(layer.state['A'].cpu(), gold['A'][i], **FACTOR_TOL)
+            torch.testing.assert_close(layer.state['G'].cpu(), gold['G'][i], **FACTOR_TOL)
+            torch.testing.assert_close(layer.module.weight.grad.cpu(), gold['grads_out'][i][0], **GRAD_TOL)
+            torch.testing.assert_close(layer.module.bias.grad.cpu(), gold['grads_out'][i][1], **GRAD_TOL)
+        opt.step()
+    return pre
+
+
+def test_shared_module_matches_reference(cpu_ops):
+    pre = _run_shared()
+    with pytest.raises(ValueError):      # needs accumulate_data
+        kfac.KFAC(models.make_tied()).register_shared_module(torch.nn.Linear(2, 2), torch.nn.Linear(2, 2))
+    with pytest.raises(ValueError):
+        pre.register_shared_module(object(), torch.nn.Linear(2, 2))

@@ -41,6 +41,13 @@ def main():
     sys.path.insert(0, os.path.join(ROOT, 'tests', 'golden'))
     import models
     dims = [x for pair in models.resnet_factor_dims('resnet50') for x in pair]
+    for a in sys.argv:
+        if a.startswith('--rank='):          # the factors the reference's allocator gives rank r of W: --rank=r/W
+            from distributed_kfac_pytorch_b200 import utils
+            r, w = (int(v) for v in a.split('=')[1].split('/'))
+            pairs = models.resnet_factor_dims('resnet50')
+            locs = utils.load_balance(w, [x ** 3 + y ** 3 for x, y in pairs])
+            dims = [v for pair, l in zip(pairs, locs) if l == r for v in pair]
     jobs = [make(d) for d in dims]
     print('resnet50: %d factors, sum d^3 = %.3g' % (len(dims), sum(float(d) ** 3 for d in dims)))
     if '--batch-only' not in sys.argv:
