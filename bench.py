@@ -45,6 +45,14 @@ NCU_TRAFFIC = {'resnet50': {'precondition': int((631.684 + 66.406 + 326.271 + 59
                             'syrk': int(0.516594e9 + 841.322e6 + 5.494764e9 + 546.571e6)}}
 
 
+def workload_name(model):
+    if model == 'resnet50':
+        return WORKLOAD
+    if model == 'lstm_lm':
+        return 'lstm_lm_2x650_seq35_b20_kfac_comm_opt_freq10'
+    return '%s_224_b32_kfac_comm_opt_freq10' % model
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
@@ -128,17 +136,52 @@ class ClockSampler(object):
 
 
 # ------------------------------------------------------------------------------ workload
+LSTM_LM = dict(ntoken=10000, nhid=650, seq=35, batch=20)     # BASELINE.json configs[3]
+
+
 def build_model(name):
-    import torchvision
     torch.manual_seed(0)
+    if name == 'lstm_lm':
+        # the shape of examples/torch_language_model.py's model (2 x 650 hidden, tied sizes): an embedding,
+        # two K-FAC-friendly LSTM layers (kfac.modules.LSTM, built from nn.Linear) and a decoder
+        import distributed_kfac_pytorch_b200 as kfac
+        c = LSTM_LM
+
+        class LM(torch.nn.Module):
+            def __init__(self):
+                super().__init__()
+                self.encoder = torch.nn.Embedding(c['ntoken'], c['nhid'])
+                self.layers = torch.nn.ModuleList([kfac.modules.LSTM(c['nhid'], c['nhid'], batch_first=False)
+                                                   for _ in range(2)])
+                self.decoder = torch.nn.Linear(c['nhid'], c['ntoken'])
+
+            def forward(self, tokens):
+                x = self.encoder(tokens)
+                for layer in self.layers:
+                    x, _ = layer(x)
+                return self.decoder(x).view(-1, c['ntoken'])
+        return LM()
+    import torchvision
     return getattr(torchvision.models, name)()
 
 
-def synthetic_batch(rank, device):
+def synthetic_batch(rank, device, name='resnet50'):
     g = torch.Generator().manual_seed(100 + rank)
+    if name == 'lstm_lm':
+        c = LSTM_LM
+        x = torch.randint(0, c['ntoken'], (c['seq'], c['batch']), generator=g)
+        y = torch.randint(0, c['ntoken'], (c['seq'] * c['batch'],), generator=g)
+        return x.to(device), y.to(device)
     x = torch.randn(BATCH, 3, 224, 224, generator=g)
     y = torch.randint(0, 1000, (BATCH,), generator=g)
     return x.to(device), y.to(device)
+
+
+def model_kwargs(name):
+    """K-FAC arguments that belong to the model family."""
+    if name == 'lstm_lm':
+        return dict(batch_first=False, accumulate_data=True, skip_layers=['linear', 'embedding'])
+    return {}
 
 
 def comm_kwargs(name):
@@ -154,6 +197,7 @@ def fresh_kfac(args, method, device, world):
     import distributed_kfac_pytorch_b200 as kfac
     model = build_model(args.model).to(device)
     kw = dict(KFAC_KW, **comm_kwargs(method))
+    kw.update(model_kwargs(args.model))
     kw['lr'] = KFAC_KW['lr'] * world
     import warnings
     with warnings.catch_warnings():
@@ -171,6 +215,8 @@ def capture(model, pre, x, y):
     loss = torch.nn.functional.cross_entropy(model(x), y)
     loss.backward()
     caps = [(list(l.a_inputs), list(l.g_outputs)) for l in pre.layers]
+    for l in pre.layers:       # the captures are replayed through feed(); start every layer empty
+        l.a_inputs, l.g_outputs = [], []
     grads = []
     for l in pre.layers:
         grads.append((l.module.weight.grad.detach().clone(),
@@ -185,18 +231,19 @@ def algorithmic_work(pre, caps, rank=0):
     in_bytes = state_bytes = 0
     for l, (a_list, g_list) in zip(pre.layers, caps):
         da, dg = l._weight_dims()
-        a, g = a_list[0], g_list[0]
-        if a.dim() == 4:
-            oh, ow = l._out_hw(a.shape[2], a.shape[3])
-            ka = a.shape[0] * oh * ow
-            kg = g.shape[0] * g.shape[2] * g.shape[3]
-        else:
-            ka = a.numel() // a.shape[-1]
-            kg = g.numel() // g.shape[-1]
+        ka = kg = 0
+        for a, g in zip(a_list, g_list):          # several captures with accumulate_data (LSTM: one per timestep)
+            if a.dim() == 4:
+                oh, ow = l._out_hw(a.shape[2], a.shape[3])
+                ka += a.shape[0] * oh * ow
+                kg += g.shape[0] * g.shape[2] * g.shape[3]
+            else:
+                ka += a.numel() // a.shape[-1]
+                kg += g.numel() // g.shape[-1]
+            in_bytes += (a.numel() + g.numel()) * 4
         syrk += ka * da * (da + 1) + kg * dg * (dg + 1)
         if l.compute_grad_ranks is None or rank in l.compute_grad_ranks:
             precond += 4 * dg * da * (da + dg)      # only the layers THIS rank preconditions
-        in_bytes += (a.numel() + g.numel()) * 4
         state_bytes += 2 * 4 * (da * (da + 1) // 2 + dg * (dg + 1) // 2)   # read + write the triangle
     return dict(syrk_flops=syrk, precond_flops=precond, factor_bytes=in_bytes + state_bytes)
 
@@ -287,9 +334,10 @@ def run_ours(args):
 
     model = build_model(args.model).to(device)
     kw = dict(KFAC_KW, **comm_kwargs(args.comm_method))
+    kw.update(model_kwargs(args.model))
     kw['lr'] = KFAC_KW['lr'] * world
     pre = kfac.KFAC(model, **kw)
-    x, y = synthetic_batch(rank, device)
+    x, y = synthetic_batch(rank, device, args.model)
     caps, grads = capture(model, pre, x, y)
     if dist_on:   # K-FAC expects gradients already averaged over ranks (DDP's job)
         for w, b in grads:
@@ -338,10 +386,11 @@ def run_ours(args):
         'ms_per_step': ms_total / args.steps, 'higher_is_better': False, 'scaling': 'weak',
         'vs_baseline': None, 'dtype': 'tf32' if ops.get_mma_mode() == 1 else 'f32',
         'data': 'synthetic', 'impl': 'ours',
-        'config': {'workload': WORKLOAD if args.model == 'resnet50' else args.model,
-                   'comm_method': args.comm_method, 'batch_per_gpu': BATCH, 'layers': len(pre.layers),
+        'config': {'workload': workload_name(args.model),
+                   'comm_method': args.comm_method, 'batch_per_gpu': LSTM_LM['batch'] if args.model == 'lstm_lm' else BATCH,
+                   'layers': len(pre.layers),
                    'cadence': '1 factor+eig step per %d' % CADENCE,
-                   'l2': 'inputs larger than L2 (captures 2.8 GB, eigenvectors 1.2 GB per GPU)',
+                   'l2': 'inputs larger than L2 (ResNet-50: captures 2.8 GB, eigenvectors 1.2 GB per GPU)',
                    'mma_mode': ops.get_mma_mode()},
         'clocks': clocks, 'gpu_launches': launches,
         'stages_ms': {'factor_update_call': factor_ms, 'precondition_call': precond_ms,
@@ -381,7 +430,7 @@ def run_ours(args):
 
     if not args.no_e2e:
         out['e2e'] = run_e2e(args, pre, caps, grads, device, dist_on)
-    if not args.no_train:
+    if not args.no_train and args.model != 'lstm_lm':
         out['train'] = run_train(args, model, pre, x, y, device, dist_on, world)
     ok = True
     if dist_on:
@@ -541,7 +590,7 @@ def run_parity(args, caps, grads, device, oracle):
         f_miss = max(f_miss, ((err > 1e-3 * raw.abs()).double().mean().item()))
         f_dims.append(raw.shape[0])
     grad_scale = max(r[0].abs().max().item() for r in v_steps[0])
-    res = {'config': WORKLOAD if args.model == 'resnet50' else args.model, 'checked': 'every layer, steps 0 (factor+eig) and 1',
+    res = {'config': workload_name(args.model), 'checked': 'every layer, steps 0 (factor+eig) and 1',
            'grad_max_abs': worst_abs, 'grad_max_rel': worst_rel, 'grad_abs_scale': grad_scale,
            'grad_elements': total, 'grad_violations_rtol1e-2_atol1e-4': viol,
            'grad_median_layer_rel': statistics.median(layer_rel),
@@ -651,11 +700,13 @@ def run_train(args, model, pre, x, y, device, dist_on, world):
 
 
 # ------------------------------------------------------------------------------ CPU arms
-def oracle_specs(modules):
+def oracle_specs(modules, multi=False):
     from oracle import kfac_oracle as O
     specs = []
     for m in modules:
-        if isinstance(m, torch.nn.Conv2d):
+        if multi:
+            specs.append(O.LayerSpec('linear_multi', m.weight.shape, m.bias is not None, batch_first=False))
+        elif isinstance(m, torch.nn.Conv2d):
             specs.append(O.LayerSpec('conv2d', m.weight.shape, m.bias is not None, m.kernel_size,
                                      m.stride, m.padding))
         else:
@@ -689,7 +740,7 @@ def time_oracle(specs, caps, grads, steps, warmup, keep_results=False):
 def run_cpu_oracle(pre, caps, grads, cycles=1):
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    specs = oracle_specs([l.module for l in pre.layers])
+    specs = oracle_specs([l.module for l in pre.layers], multi=pre.layers[0].__class__.__name__ == 'LinearMultiLayer')
     ccaps = [([t.cpu() for t in a], [t.cpu() for t in g]) for a, g in caps]
     cgrads = [(w.cpu(), None if b is None else b.cpu()) for w, b in grads]
     # bounded sample: one factor+eigendecomposition step and one ordinary step, amortised

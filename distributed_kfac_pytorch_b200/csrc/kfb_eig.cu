@@ -455,7 +455,7 @@ bool batched_wins(int d, size_t count, double lane_speedup) {
   static const int big_max = []() { const char* e = getenv("KFB_SYEV_BATCH_MAX_D"); return e ? atoi(e) : 0; }();
   static const int big_min_count = []() { const char* e = getenv("KFB_SYEV_BATCH_MIN_COUNT"); return e ? atoi(e) : 8; }();
   if (count < 1) return false;
-  if (big_max > 0) return (d <= 512 && count >= 2) || (d <= big_max && (int)count >= big_min_count);   // explicit thresholds
+  if (big_max > 0) return d <= big_max && (int)count >= (d <= 128 ? 1 : d <= 512 ? 2 : big_min_count);   // explicit thresholds
   const double batched = interp_loglog(d, kB0) + interp_loglog(d, kB1) * (double)count;
   const double lanes = syevd_ms(d, 148) * (double)count / lane_speedup;
   return batched < lanes;

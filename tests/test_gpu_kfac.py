@@ -435,3 +435,23 @@ def test_autocast_training_step_matches_oracle(mode, amp_dtype):
         assert_factor_close(l.state['A'], oracle.A[i])
         assert_factor_close(l.state['G'], oracle.G[i])
         torch.testing.assert_close(l.module.weight.grad.cpu(), ref[i][0], rtol=1e-2, atol=1e-4)
+
+
+@pytest.mark.parametrize('fp16', [False, True], ids=['fp32', 'amp'])
+def test_reference_example_script_runs_unmodified(tmp_path, fp16):
+    """the reference's examples/torch_cifar10_resnet.py (its own argument parsing,
+    DDP wrapping, training engine, optimizer / KFAC / scheduler construction and checkpointing) runs
+    against this package through the `kfac` alias; only the dataset is synthetic (no network) and the
+    missing third-party torchsummary is stubbed - see tools/run_reference_example.py."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, os.path.join(root, 'tools', 'run_reference_example.py'), '--log-dir', str(tmp_path),
+           '--iters', '6'] + (['--fp16'] if fp16 else [])
+    res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    if res.returncode == 77:
+        pytest.skip('the reference examples are not on this box')
+    assert res.returncode == 0, res.stdout[-3000:]
+    assert 'EXAMPLE OK: 32 K-FAC layers' in res.stdout, res.stdout[-2000:]
+    assert 'step 6' in res.stdout
