@@ -747,8 +747,8 @@ def run_cpu_oracle(pre, caps, grads, cycles=1):
     t, ok, results = time_oracle(specs, ccaps, cgrads, steps=2, warmup=0, keep_results=True)
     amort = (t[0] + (CADENCE - 1) * t[1]) / CADENCE
     return ({'value': amort * 1e3, 'unit': 'ms/step', 'cores': cores, 'kind': 'port',
-            'sample': '1 factor+eig step (%.1f s) + 1 ordinary step (%.2f s) of the same ResNet-50 b32 '
-                      'captures, amortised over the %d-step cadence' % (t[0], t[1], CADENCE)}, (ok, results, ccaps))
+            'sample': '1 factor+eig step (%.1f s) + 1 ordinary step (%.2f s) on the same captures and gradients '
+                      'as the GPU run, amortised over the %d-step cadence' % (t[0], t[1], CADENCE)}, (ok, results, ccaps))
 
 
 def run_reference(args):

@@ -671,8 +671,9 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
   plan->off_segs = off;   off = align_up(off + plan->segs.size() * sizeof(DevSegment), 256);
   plan->off_items = off;  off = align_up(off + plan->item_start.size() * sizeof(int), 256);
   plan->off_fin = off;    off = align_up(off + plan->fin_start.size() * sizeof(int), 256);
-  plan_syrk_tc(plan);
+  plan_syrk_tc(plan, num_sms);
   plan->off_tc_items = off; off = align_up(off + plan->tc_items.size() * sizeof(TcItem), 256);
+  plan->off_cta_first = off; off = align_up(off + plan->cta_first.size() * sizeof(int), 256);
   plan->off_tmaps = off;    off = align_up(off + plan->tmaps.size() * sizeof(CUtensorMap), 256);
   // staging copies: blocks of 256 threads x 4 floats
   int pad_blocks = 0;
@@ -701,7 +702,7 @@ std::vector<int64_t> g_plan_sig;
 
 void signature(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool tc, std::vector<int64_t>* sig) {
   sig->clear();
-  sig->push_back(n_jobs); sig->push_back(num_sms); sig->push_back(tc); sig->push_back(tma_mode()); sig->push_back(stage_mode()); sig->push_back(syrk_pair_mode()); sig->push_back(fused_max_rows());
+  sig->push_back(n_jobs); sig->push_back(num_sms); sig->push_back(tc); sig->push_back(tma_mode()); sig->push_back(stage_mode()); sig->push_back(syrk_pair_mode()); sig->push_back(fused_max_rows()); sig->push_back(getenv("KFB_SYRK_STREAMK") ? atoi(getenv("KFB_SYRK_STREAMK")) : 0);
   for (int i = 0; i < n_jobs; ++i) {
     const kfb_factor_job& j = jobs[i];
     sig->push_back(j.d); sig->push_back(j.n_segments); sig->push_back(j.ld_state);
@@ -817,6 +818,8 @@ int upload_plan(FactorPlan* plan, void* workspace, cudaStream_t stream) {
   KFB_CUDA(cudaMemcpyAsync(ws + plan->off_fin, plan->fin_start.data(), plan->fin_start.size() * sizeof(int), cudaMemcpyHostToDevice, stream));
   if (!plan->tc_items.empty())
     KFB_CUDA(cudaMemcpyAsync(ws + plan->off_tc_items, plan->tc_items.data(), plan->tc_items.size() * sizeof(TcItem), cudaMemcpyHostToDevice, stream));
+  if (!plan->cta_first.empty())
+    KFB_CUDA(cudaMemcpyAsync(ws + plan->off_cta_first, plan->cta_first.data(), plan->cta_first.size() * sizeof(int), cudaMemcpyHostToDevice, stream));
   if (!plan->tmaps.empty())
     KFB_CUDA(cudaMemcpyAsync(ws + plan->off_tmaps, plan->tmaps.data(), plan->tmaps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice, stream));
   KFB_CUDA(cudaMemsetAsync(scratch, 0, plan->scratch_floats * sizeof(float), stream));

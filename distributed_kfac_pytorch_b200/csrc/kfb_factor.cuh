@@ -115,6 +115,8 @@ struct FactorPlan {
   std::vector<TcItem> tc_items;          // [0, n_pair_items): CTA-pair kernel; the rest: single-CTA kernel
   int n_pair_items = 0;
   size_t off_tc_items = 0;
+  std::vector<int> cta_first;            // single-CTA kernel, stream-K shares: items [cta_first[c], cta_first[c+1]) belong to CTA c
+  size_t off_cta_first = 0;
   std::vector<DevJob> jobs;
   std::vector<DevSegment> segs;
   std::vector<int> item_start, fin_start;
@@ -132,7 +134,7 @@ struct FactorPlan {
 };
 
 KFB_HIDDEN int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_tc, FactorPlan* plan);
-KFB_HIDDEN void plan_syrk_tc(FactorPlan* plan);
+KFB_HIDDEN void plan_syrk_tc(FactorPlan* plan, int num_sms);
 KFB_HIDDEN int upload_plan(FactorPlan* plan, void* workspace, cudaStream_t stream);
 KFB_HIDDEN int refresh_tmaps(FactorPlan* plan, Context* ctx);
 KFB_HIDDEN void bind_workspace(FactorPlan* plan, void* workspace);

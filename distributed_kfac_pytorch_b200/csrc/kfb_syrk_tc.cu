@@ -109,6 +109,15 @@ __device__ __forceinline__ int snake_item(int round, int total) {
   const int t = round * g + ((round & 1) ? g - 1 - c : c);
   return t < total ? t : -1;
 }
+// The single-CTA build walks a CONTIGUOUS range of the item list instead (cta_first[blockIdx.x] ..
+// cta_first[blockIdx.x + 1]): the host cut the linearised work into one equal share per CTA, so a
+// CTA's consecutive K pieces of one block are one item and the accumulators stay in TMEM across them.
+template <bool kPair>
+__device__ __forceinline__ int next_item(int round, int total, const int* __restrict__ cta_first) {
+  if (kPair || cta_first == nullptr) return snake_item<kPair>(round, total);
+  const int it = cta_first[blockIdx.x] + round;
+  return it < cta_first[blockIdx.x + 1] ? it : -1;
+}
 
 // explicit shared-space stores: through a generic pointer the compiler emits ST.E (generic
 // address translation on every store) instead of STS
@@ -158,7 +167,8 @@ template <bool kPair>
 __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const DevJob* __restrict__ jobs,
                                                                         const DevSegment* __restrict__ segs,
                                                                         const TcItem* __restrict__ items, int n_items, float alpha,
-                                                                        const CUtensorMap* __restrict__ tmaps) {
+                                                                        const CUtensorMap* __restrict__ tmaps,
+                                                                        const int* __restrict__ cta_first) {
   using C = Cfg<kPair>;
   constexpr int kStages = C::kStages, kStageBytes = C::kStageBytes, kSlots = C::kSlots;
   extern __shared__ uint8_t smem_raw[];
@@ -201,7 +211,7 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
     const uint32_t vec_kq = lane & 7, vec_rsub = lane >> 3;
     const uint32_t smem_base = umma::smem_u32(smem);
     int stage = 0; uint32_t phase = 0;
-    for (int round = 0, it; (it = snake_item<kPair>(round, n_items)) >= 0; ++round) {
+    for (int round = 0, it; (it = next_item<kPair>(round, n_items, cta_first)) >= 0; ++round) {
       const TcItem item = items[it];
       const DevSegment s = segs[item.seg];
       const int d = jobs[item.job].d;
@@ -476,7 +486,7 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0;
-      for (int round = 0, it; (it = snake_item<kPair>(round, n_items)) >= 0; ++round) {
+      for (int round = 0, it; (it = next_item<kPair>(round, n_items, cta_first)) >= 0; ++round) {
         const TcItem item = items[it];
         if (leader) {
           const bool diag = item.a0 == item.b0;
@@ -521,7 +531,7 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
     uint32_t acc_phase = 0;
     int acc = 0;
     int stage = 0; uint32_t phase = 0;
-    for (int round = 0, it; (it = snake_item<kPair>(round, n_items)) >= 0; ++round) {
+    for (int round = 0, it; (it = next_item<kPair>(round, n_items, cta_first)) >= 0; ++round) {
       const TcItem item = items[it];
       const DevJob& job = jobs[item.job];
       // device-side multiplier of the segment weight (AMP unscale; 0 = capture dropped, kfb_capture_filter)
@@ -711,11 +721,20 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
 
 }  // namespace
 
-// Build the tensor-core work lists for the jobs marked use_tc: (2x2 tile block, K chunk) items,
-// longest first.  Large factors go to the CTA-pair kernel, which always computes the full 256 x 256
-// block (a good deal on factors of many tiles, a waste on one- or two-tile factors).
-void plan_syrk_tc(FactorPlan* plan) {
-  static const int64_t kChunk = getenv("KFB_SYRK_CHUNK") ? atoll(getenv("KFB_SYRK_CHUNK")) : 4096;     // rows of X per item: ~128 stages of 4 tile products (2048: 3.57 ms, 4096: 3.33, 8192: 3.40 on the ResNet-50 batch)
+// Build the tensor-core work lists for the jobs marked use_tc.
+//
+// Default: (2x2 tile block, K chunk of up to 4096 rows) items, longest first, handed out boustrophedon.
+// KFB_SYRK_STREAMK=1 (single-CTA kernel only): the work of all jobs is laid out as one sequence of
+// units - a 2x2 tile block of one segment over its whole K - measured in tile products, and cut into ONE
+// CONTIGUOUS SHARE PER CTA: a CTA's piece of a unit is a single item, however long, so its accumulators
+// stay in TMEM for the whole piece and are drained once (about 5 drains per CTA instead of 20 on
+// ResNet-50).  Parity-tested, and measured SLOWER: 3.81 ms against 2.78 ms for the whole ResNet-50 factor
+// stage - the units differ too much in speed per tile product (TMA-fed, gathered, fused-finish) for equal
+// shares of tile products to take equal time, and contiguous shares give one CTA a run of like units;
+// the short chunks of the default schedule even that out.  Kept behind the switch for that record.
+void plan_syrk_tc(FactorPlan* plan, int num_sms) {
+  static const int64_t kChunk = getenv("KFB_SYRK_CHUNK") ? atoll(getenv("KFB_SYRK_CHUNK")) : 4096;     // pair kernel: rows of X per item
+  const bool stream_k = getenv("KFB_SYRK_STREAMK") && getenv("KFB_SYRK_STREAMK")[0] == '1';    // opt-in, see above
   const int pair_min_tiles = syrk_pair_mode();
   std::vector<TcItem> pair_items, single_items;
   for (size_t ji = 0; ji < plan->jobs.size(); ++ji) {
@@ -723,16 +742,18 @@ void plan_syrk_tc(FactorPlan* plan) {
     if (!j.use_tc) continue;
     const int T = ceil_div(j.d, TM);          // 128-wide tiles per side
     const int TB = ceil_div(T, 2);            // 256-wide blocks per side
-    std::vector<TcItem>& out = (pair_min_tiles > 0 && T >= pair_min_tiles) ? pair_items : single_items;
+    const bool pair = pair_min_tiles > 0 && T >= pair_min_tiles;
+    std::vector<TcItem>& out = pair ? pair_items : single_items;
     for (int si = 0; si < j.n_segments; ++si) {
       const DevSegment& s = plan->segs[j.seg_start + si];
       // TMA segments iterate the per-image padded matrix: nb blocks of 32 rows per image
       const int64_t K = s.tma >= 0 ? (s.K / ((int64_t)s.oh * s.ow)) * s.nb * BK : s.K;
-      const int64_t nch = j.fused ? 1 : std::max<int64_t>(1, ceil_div64(K, kChunk));
+      const bool whole = j.fused || (stream_k && !pair);      // one unit per block; cut later
+      const int64_t nch = whole ? 1 : std::max<int64_t>(1, ceil_div64(K, kChunk));
       const int64_t len = ceil_div64(ceil_div64(K, nch), BK) * BK;
-      for (int64_t k = 0; k < K; k += len)
-        for (int bi = 0; bi < TB; ++bi)
-          for (int bj = bi; bj < TB; ++bj) {
+      for (int bi = 0; bi < TB; ++bi)
+        for (int bj = bi; bj < TB; ++bj)
+          for (int64_t k = 0; k < K; k += len) {
             TcItem it;
             it.job = (int)ji; it.seg = j.seg_start + si;
             it.a0 = 2 * bi; it.b0 = 2 * bj;
@@ -742,17 +763,64 @@ void plan_syrk_tc(FactorPlan* plan) {
           }
     }
   }
-  auto cost = [](const TcItem& a) {
-    int64_t units = a.a0 == a.b0 ? (a.mi * (a.mi + 1)) / 2 : a.mi * a.nj;
-    return (int64_t)(a.k_end - a.k_begin) * units;
-  };
+  auto units_of = [](const TcItem& a) { return (int64_t)(a.a0 == a.b0 ? (a.mi * (a.mi + 1)) / 2 : a.mi * a.nj); };
+  auto cost = [&](const TcItem& a) { return (int64_t)(a.k_end - a.k_begin) * units_of(a); };
   auto by_cost = [&](const TcItem& a, const TcItem& b) { return cost(a) > cost(b); };
   auto by_len = [](const TcItem& a, const TcItem& b) { return a.k_end - a.k_begin > b.k_end - b.k_begin; };
   std::stable_sort(pair_items.begin(), pair_items.end(), by_len);      // a pair always does the full block
-  std::stable_sort(single_items.begin(), single_items.end(), by_cost);
   plan->n_pair_items = (int)pair_items.size();
   plan->tc_items = pair_items;
-  plan->tc_items.insert(plan->tc_items.end(), single_items.begin(), single_items.end());
+  plan->cta_first.clear();
+  if (!stream_k) {
+    std::stable_sort(single_items.begin(), single_items.end(), by_cost);
+    plan->tc_items.insert(plan->tc_items.end(), single_items.begin(), single_items.end());
+    return;
+  }
+  // ---- cut the unit sequence into num_sms shares of equal cost
+  const int G = std::max(1, num_sms);
+  int64_t total = 0;
+  for (const TcItem& u : single_items) total += cost(u);
+  // every item also pays a fixed price (pipeline refill + drain), charged as rows of a full block
+  const int64_t kItemOverhead = 4 * 256;
+  total += (int64_t)single_items.size() * kItemOverhead;
+  const int64_t share = std::max<int64_t>(1, ceil_div64(total, G));
+  const int64_t kMinPiece = 8 * BK;                     // never leave or take a sliver of a unit
+  std::vector<TcItem> cut;
+  plan->cta_first.assign(1, 0);
+  int64_t used = 0;
+  auto close_cta = [&]() {
+    if ((int)plan->cta_first.size() < G) { plan->cta_first.push_back((int)cut.size()); used = 0; }   // the last CTA takes what is left
+  };
+  for (const TcItem& u : single_items) {
+    const int64_t per_row = units_of(u);
+    const bool fused = plan->jobs[u.job].fused != 0;
+    int64_t k = u.k_begin;
+    while (k < (int64_t)u.k_end) {
+      const int64_t left = (int64_t)u.k_end - k;
+      int64_t take = left;
+      if (!fused) {
+        int64_t room = (share - used - kItemOverhead) / per_row;
+        room = room / BK * BK;
+        const bool last_cta = (int)plan->cta_first.size() >= G;
+        if (!last_cta && room < std::min(left, kMinPiece) && used > 0) { close_cta(); continue; }
+        if (!last_cta && room < left) {
+          take = std::max(room, std::min(left, kMinPiece));
+          if (left - take < kMinPiece) take = left;      // do not leave a sliver behind
+        }
+      }
+      TcItem it = u;
+      it.k_begin = (uint32_t)k; it.k_end = (uint32_t)(k + take);
+      cut.push_back(it);
+      used += take * per_row + kItemOverhead;
+      k += take;
+      if (used >= share) close_cta();
+    }
+  }
+  while ((int)plan->cta_first.size() < G + 1) plan->cta_first.push_back((int)cut.size());
+  plan->cta_first.back() = (int)cut.size();
+  // positions in tc_items are offset by the pair items, which come first
+  for (int& f : plan->cta_first) f += plan->n_pair_items;
+  plan->tc_items.insert(plan->tc_items.end(), cut.begin(), cut.end());
 }
 
 int launch_syrk_tc(const FactorPlan& plan, void* workspace, Context* ctx, float alpha, cudaStream_t stream) {
@@ -768,6 +836,7 @@ int launch_syrk_tc(const FactorPlan& plan, void* workspace, Context* ctx, float 
   const DevSegment* segs = (const DevSegment*)(ws + plan.off_segs);
   const TcItem* items = (const TcItem*)(ws + plan.off_tc_items);
   const CUtensorMap* tmaps = (const CUtensorMap*)(ws + plan.off_tmaps);
+  const int* cta_first = plan.cta_first.empty() ? nullptr : (const int*)(ws + plan.off_cta_first);
   const int n_pair = plan.n_pair_items, n_single = (int)plan.tc_items.size() - n_pair;
   if (n_pair > 0) {
     KFB_REQUIRE(ctx->num_sms >= 2, "the CTA-pair SYRK needs at least two SMs");
@@ -782,12 +851,20 @@ int launch_syrk_tc(const FactorPlan& plan, void* workspace, Context* ctx, float 
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    KFB_CUDA(cudaLaunchKernelEx(&cfg, syrk_tc_kernel<true>, jobs, segs, items, n_pair, alpha, tmaps));
+    KFB_CUDA(cudaLaunchKernelEx(&cfg, syrk_tc_kernel<true>, jobs, segs, items, n_pair, alpha, tmaps, (const int*)nullptr));
     count_launch();
   }
   if (n_single > 0) {
-    const int grid = std::min(n_single, ctx->num_sms);
-    syrk_tc_kernel<false><<<grid, Cfg<false>::kThreads, Cfg<false>::kSmemBytes, stream>>>(jobs, segs, items + n_pair, n_single, alpha, tmaps);
+    if (cta_first) {
+      // stream-K shares: one CTA per share (cta_first indexes the whole item array)
+      const int grid = (int)plan.cta_first.size() - 1;
+      syrk_tc_kernel<false><<<grid, Cfg<false>::kThreads, Cfg<false>::kSmemBytes, stream>>>(jobs, segs, items, n_pair + n_single, alpha,
+                                                                                           tmaps, cta_first);
+    } else {
+      const int grid = std::min(n_single, ctx->num_sms);
+      syrk_tc_kernel<false><<<grid, Cfg<false>::kThreads, Cfg<false>::kSmemBytes, stream>>>(jobs, segs, items + n_pair, n_single, alpha,
+                                                                                           tmaps, (const int*)nullptr);
+    }
     KFB_CHECK_LAUNCH();
   }
   return KFB_OK;

@@ -183,6 +183,39 @@ def test_cta_pair_syrk_matches_single_cta(monkeypatch):
             assert_factor_close(state, ref)
 
 
+def test_stream_k_schedule_matches_default(monkeypatch):
+    """KFB_SYRK_STREAMK=1 cuts the SYRK work into one contiguous share per CTA (pieces of arbitrary K
+    length, accumulators kept in TMEM across a piece) instead of fixed K chunks handed out round-robin.
+    Off by default (measured slower on ResNet-50); a batch of jobs large enough to be cut inside units
+    must still give the oracle's factors."""
+    N.set_ops(None)
+    o = N.get_ops()
+    o._enter(torch.zeros(1, device=DEV))
+    o.set_mma_mode(1)
+    gen = torch.Generator().manual_seed(34)
+    xs = [torch.randn(9, 128, 28, 28, generator=gen), torch.randn(6, 70, 14, 14, generator=gen)]
+    gs = [torch.randn(24, 260, 14, 14, generator=gen), torch.randn(2, 16, 56, 56, generator=gen)]
+    refs = [O.factor_ema(O.conv2d_A([x], (3, 3), (1, 1), (1, 1), False), None, 0.95) for x in xs]
+    refs += [O.factor_ema(O.conv2d_G([g]), None, 0.95) for g in gs]
+    for env in ('1', '0'):
+        monkeypatch.setenv('KFB_SYRK_STREAMK', env)
+        jobs, states = [], []
+        for x in xs:
+            d, segs = conv_segments(x, (3, 3), (1, 1), (1, 1), False)
+            states.append(alloc2d(d, d, DEV)[1])
+            jobs.append(N.FactorJob(d, segs, states[-1], True, True, None))
+        for g in gs:
+            n, c, h, w = g.shape
+            S = h * w
+            seg = N.Segment(N.KFB_SEG_NCHW, g.to(DEV), n, c, 1.0 / (S * S * n * S), h=h, w=w)
+            states.append(alloc2d(c, c, DEV)[1])
+            jobs.append(N.FactorJob(c, [seg], states[-1], True, True, None))
+        o.factor_update(jobs, 0.95)
+        torch.cuda.synchronize()
+        for st, ref in zip(states, refs):
+            assert_factor_close(st, ref)
+
+
 def test_nchw_tma_and_gather_paths_agree(monkeypatch):
     """fp32 NCHW operands with 16-byte image rows are fetched by TMA (per-image 32-row blocks, tail
     zero-filled); KFB_SYRK_TMA=0 and a capture that is not 16-byte aligned use the gathering
