@@ -39,10 +39,27 @@ KFAC_KW = dict(damping=0.001, factor_decay=0.95, kl_clip=0.001, lr=0.0125,
                factor_update_freq=CADENCE, inv_update_freq=CADENCE,
                distribute_layer_factors=False)
 WORKLOAD = 'resnet50_224_b32_kfac_comm_opt_freq10'
-# DRAM bytes per launch from the committed ncu capture (profiles/r1_tc_kernels_ncu.txt), 1 GPU
-NCU_TRAFFIC = {'resnet50': {'precondition': int((631.684 + 66.406 + 326.271 + 59.948 + 629.420 + 67.422 + 325.887 + 61.678) * 1e6),
-                            # staging copies (pad_kernel) + SYRK
-                            'syrk': int(0.516594e9 + 841.322e6 + 5.494764e9 + 546.571e6)}}
+def ncu_traffic(model):
+    """DRAM bytes (read + written) per call of the two stages, from the committed `ncu --set full` capture
+    of this build (profiles/r2_tc_kernels_ncu.json, written by tools/ncu_summary.py --json from a capture of
+    `bench.py --steps 11 --warmup 0`): the precondition chain = the gradient pack + the four grouped GEMM
+    launches of one step; the factor stage = staging copies + SYRK (+ finalize) of one factor step."""
+    path = os.path.join(ROOT, 'profiles', 'r2_tc_kernels_ncu.json' if model == 'resnet50' else 'r2_tc_kernels_ncu_%s.json' % model)
+    if not os.path.exists(path):
+        return {}
+    launches = json.load(open(path))['launches']
+
+    def total(names, first_n):
+        seen, tot = {}, 0.0
+        for l in launches:
+            for n in names:
+                if l['kernel'].startswith(n) and seen.get(n, 0) < first_n.get(n, 1):
+                    seen[n] = seen.get(n, 0) + 1
+                    tot += (l['dram_read_bytes'] or 0) + (l['dram_write_bytes'] or 0)
+        return int(tot) if seen else None
+    return {'precondition': total(['gemm_tc2_kernel', 'gemm_tc_kernel'], {'gemm_tc2_kernel': 4, 'gemm_tc_kernel': 4}),
+            'syrk': total(['pad_kernel', 'syrk_tc_kernel', 'finalize_kernel'], {}),
+            'source': os.path.relpath(path, ROOT)}
 
 
 def workload_name(model):
@@ -416,7 +433,8 @@ def run_ours(args):
                            'achieved': ach, 'peak': tf32_peak, 'unit': 'TFLOP/s', 'frac': ach / tf32_peak,
                            # dram__bytes_read+write summed over the four GEMM launches of one step, ncu
                            # --set full, profiles/r1_tc_kernels_ncu.txt (algorithmic minimum 921.5 MB)
-                           'traffic': NCU_TRAFFIC.get(args.model, {}).get('precondition'),
+                           'traffic': ncu_traffic(args.model).get('precondition'),
+                           'traffic_source': ncu_traffic(args.model).get('source'),
                            'peak_source': pk['tf32_source'] + ', burst',
                            'peak_sustained': pk['tf32_sustained'], 'frac_of_sustained': ach / pk['tf32_sustained']}
     if factor_ms:
@@ -426,7 +444,7 @@ def run_ours(args):
                                   'peak': tf32_peak, 'unit': 'TFLOP/s', 'frac': ach / tf32_peak,
                                   'peak_sustained': pk['tf32_sustained'], 'frac_of_sustained': ach / pk['tf32_sustained'],
                                   'hbm_gbs': gbs, 'hbm_frac': gbs / pk['hbm_gbs'],
-                                  'traffic': NCU_TRAFFIC.get(args.model, {}).get('syrk')}
+                                  'traffic': ncu_traffic(args.model).get('syrk')}
 
     if not args.no_e2e:
         out['e2e'] = run_e2e(args, pre, caps, grads, device, dist_on)
@@ -608,52 +626,95 @@ def _native_mode():
 
 
 def run_e2e(args, pre, caps, grads, device, dist_on):
-    """Same steps, but every step's inputs start in pinned host memory."""
+    """Same steps, but every step's inputs start in pinned host memory and its result ends there.
+    Copies are pipelined the way an input pipeline would: while step i computes, a copy stream brings
+    step i+1's inputs into a second set of device buffers and another drains step i-1's result; all of
+    it is inside the timed region and every step waits for exactly its own inputs."""
     host_caps = [([t.cpu().pin_memory() for t in a], [t.cpu().pin_memory() for t in g]) for a, g in caps]
     host_grads = [(w.cpu().pin_memory(), None if b is None else b.cpu().pin_memory()) for w, b in grads]
     bytes_grads = sum(w.numel() * 4 + (0 if b is None else b.numel() * 4) for w, b in grads)
-    bytes_caps = sum(sum(t.numel() * 4 for t in a) + sum(t.numel() * 4 for t in g) for a, g in caps)
+    bytes_caps = sum(sum(t.numel() * t.element_size() for t in a) + sum(t.numel() * t.element_size() for t in g) for a, g in caps)
     result = torch.zeros(1).pin_memory()
     # the step's result is the rewritten .grad of every registered module: it is read back to pinned
     # host memory every step, together with the v.g scalar
     host_out = [(torch.empty_like(w).pin_memory(), None if b is None else torch.empty_like(b).pin_memory())
                 for w, b in host_grads]
+    # two sets of device-side input buffers (set 0 = the tensors the resident run used)
+    dev_caps = [caps, [([torch.empty_like(t) for t in a], [torch.empty_like(t) for t in g]) for a, g in caps]]
+    dev_grads = [[(torch.empty_like(w), None if b is None else torch.empty_like(b)) for w, b in grads] for _ in range(2)]
+    dev_out = [(torch.empty_like(w), None if b is None else torch.empty_like(b)) for w, b in grads]
+    h2d_stream, d2h_stream = torch.cuda.Stream(device), torch.cuda.Stream(device)
+    ready = [torch.cuda.Event(), torch.cuda.Event()]      # inputs of buffer set k have landed
+    consumed = [torch.cuda.Event(), torch.cuda.Event()]   # the step reading buffer set k has finished with it
+    drained = torch.cuda.Event()                          # dev_out has been copied to the host
     h2d = [0]
+    main = torch.cuda.current_stream(device)
+    for e in consumed:
+        e.record(main)
+    drained.record(main)
 
-    def one_step():
-        group = pre.param_groups[0]
-        if group['step'] % group['factor_update_freq'] == 0:
-            for (a, g), (ha, hg) in zip(caps, host_caps):
-                for d, h in zip(a + g, ha + hg):
-                    d.copy_(h, non_blocking=True)
-            h2d[0] += bytes_caps
-        for l, (hw, hb) in zip(pre.layers, host_grads):
-            l.module.weight.grad.copy_(hw, non_blocking=True)
-            if hb is not None:
-                l.module.bias.grad.copy_(hb, non_blocking=True)
-        h2d[0] += bytes_grads
-        feed(pre, caps)
-        pre.step()
-        for l, (ow, ob) in zip(pre.layers, host_out):
-            ow.copy_(l.module.weight.grad, non_blocking=True)
-            if ob is not None:
-                ob.copy_(l.module.bias.grad, non_blocking=True)
-        result.copy_(pre._vg_acc, non_blocking=True)
+    def upload(step_index, k):
+        """Queue the H2D copies of the inputs of K-FAC step number `step_index` into buffer set k."""
+        factor_step = step_index % pre.param_groups[0]['factor_update_freq'] == 0
+        with torch.cuda.stream(h2d_stream):
+            h2d_stream.wait_event(consumed[k])
+            if factor_step:
+                for (a, g), (ha, hg) in zip(dev_caps[k], host_caps):
+                    for d, h in zip(a + g, ha + hg):
+                        d.copy_(h, non_blocking=True)
+                h2d[0] += bytes_caps
+            for (dw, db), (hw, hb) in zip(dev_grads[k], host_grads):
+                dw.copy_(hw, non_blocking=True)
+                if db is not None:
+                    db.copy_(hb, non_blocking=True)
+            h2d[0] += bytes_grads
+            ready[k].record(h2d_stream)
 
-    for _ in range(CADENCE):
-        one_step()
+    def run(n_steps):
+        first_index = pre.param_groups[0]['step']
+        upload(first_index, first_index & 1)
+        for i in range(first_index, first_index + n_steps):
+            k = i & 1
+            if i + 1 < first_index + n_steps:
+                upload(i + 1, (i + 1) & 1)          # overlaps with this step's kernels
+            main.wait_event(ready[k])
+            for l, (dw, db) in zip(pre.layers, dev_grads[k]):
+                l.module.weight.grad.copy_(dw)      # K-FAC rewrites .grad in place: hand it this step's gradients
+                if db is not None:
+                    l.module.bias.grad.copy_(db)
+            feed(pre, dev_caps[k])
+            pre.step()
+            main.wait_event(drained)
+            for l, (ow, ob) in zip(pre.layers, dev_out):
+                ow.copy_(l.module.weight.grad)
+                if ob is not None:
+                    ob.copy_(l.module.bias.grad)
+            consumed[k].record(main)
+            done = torch.cuda.Event()
+            done.record(main)
+            with torch.cuda.stream(d2h_stream):     # overlaps with the next step's kernels
+                d2h_stream.wait_event(done)
+                for (ow, ob), (hw, hb) in zip(dev_out, host_out):
+                    hw.copy_(ow, non_blocking=True)
+                    if hb is not None:
+                        hb.copy_(ob, non_blocking=True)
+                result.copy_(pre._vg_acc, non_blocking=True)
+                drained.record(d2h_stream)
+        main.wait_event(drained)
+
+    run(CADENCE)
     h2d[0] = 0
     barrier_sync(dist_on)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(args.steps):
-        one_step()
+    run(args.steps)
     e1.record()
     barrier_sync(dist_on)
     ms = max_over_ranks(e0.elapsed_time(e1), device, dist_on)
     return {'value': ms / args.steps, 'unit': 'ms/step', 'h2d_bytes_per_step': h2d[0] // args.steps,
             'd2h_bytes_per_step': bytes_grads + 4,
-            'api': 'KFAC.step() with pinned-host activations/gradients in, rewritten gradients out'}
+            'api': 'KFAC.step() with pinned-host activations/gradients in, rewritten gradients out; copies of step '
+                   'i+1 / i-1 overlap the kernels of step i on side streams (double-buffered inputs)'}
 
 
 def run_train(args, model, pre, x, y, device, dist_on, world):

@@ -140,7 +140,24 @@ struct GreenSet {
   std::vector<int> units;       // 8-SM units per lane, non-increasing; lane 0 also owns the split's remainder
   std::vector<Lane> lanes;
 };
+// Self-tuning between candidate partitions: the cost table was measured on well-conditioned random
+// matrices with the rest of the GPU idle; real K-FAC factors (identity + low rank: heavy deflation in
+// the divide and conquer, a different number of Jacobi sweeps in the batched solver) and the batched
+// solver running beside the lanes shift the balance - on one GPU the planned 4-lane partition takes
+// 446 ms where the planned 3-lane one takes 410, on 2 and 4 GPUs four lanes win.  An inverse update
+// repeats the same job list every inv_update_freq steps, so the library times the candidates itself
+// (CUDA events on the caller's stream, read back at the next call, no synchronisation) and keeps the
+// fastest.
+struct TuneEntry {
+  std::vector<int> dims;                       // the job list this entry belongs to (sizes, descending)
+  std::vector<std::vector<int>> cand;          // candidate partitions (SM units per lane)
+  std::vector<double> ms;                      // measured time of each candidate, < 0: not yet
+  int last = -1;                               // candidate used by the call whose events are pending
+  bool pending = false;
+  cudaEvent_t begin = nullptr, end = nullptr;
+};
 struct LanePool {
+  std::vector<TuneEntry*> tune;
   Lane plain[2];                // ordinary streams of the primary context (all SMs)
   Lane grouped;                 // stream/handle for the XsyevBatched groups
   cusolverDnParams_t params = nullptr;
@@ -303,6 +320,8 @@ struct BatchPlan {
   std::vector<Lane*> lane_ptr;           // the stream / handle each lane runs on
   std::vector<size_t> lane_off;          // workspace offset per lane (+ end)
   size_t group_off = 0, total = 0;
+  TuneEntry* tune = nullptr;             // set when this call's time should be recorded
+  int tune_index = -1;
 };
 
 // ---- measured cost model (B200, CUDA 12.9 cuSOLVER; tools/try_green_ctx3.py) ----------------------
@@ -411,6 +430,18 @@ std::vector<int> choose_units(const std::vector<int>& dims, int n_units, int uni
   const double one_stream = place_jobs(dims, std::vector<int>(1, num_sms), nullptr);
   *modelled_ms = one_stream;
   if (dims.size() < 2 || max_lanes < 2 || n_units < 2) return std::vector<int>(1, n_units);
+  if (const char* e = getenv("KFB_SYEVD_UNITS")) {        // experiments: force a partition, e.g. "6,6,6" (units of 8 SMs)
+    std::vector<int> forced;
+    int left = n_units;
+    for (const char* p = e; *p && left > 0 && (int)forced.size() < kMaxLanes;) {
+      const int u = std::min(left, std::max(1, atoi(p)));
+      forced.push_back(u);
+      left -= u;
+      while (*p && *p != ',') ++p;
+      if (*p == ',') ++p;
+    }
+    if (forced.size() > 1) return forced;
+  }
   LaneSearch srch;
   srch.n_units = n_units;
   srch.max_lanes = std::min(max_lanes, (int)dims.size());
@@ -461,7 +492,7 @@ bool batched_wins(int d, size_t count, double lane_speedup) {
   return batched < lanes;
 }
 
-int make_plan(kfb::Context* ctx, LanePool* pool, const kfb_syevd_job* jobs, int n, BatchPlan* plan) {
+int make_plan(kfb::Context* ctx, LanePool* pool, const kfb_syevd_job* jobs, int n, BatchPlan* plan, bool for_run) {
   std::vector<int> order(n);
   for (int i = 0; i < n; ++i) {
     KFB_REQUIRE(jobs[i].factor && jobs[i].E && jobs[i].Q && jobs[i].w && jobs[i].dev_info && jobs[i].d > 0,
@@ -507,11 +538,55 @@ int make_plan(kfb::Context* ctx, LanePool* pool, const kfb_syevd_job* jobs, int 
   for (int i : singles) dims.push_back(jobs[i].d);
   std::vector<int> where(singles.size(), 0);
   plan->lane_ptr.clear();
+  size_t lane_ws_floor = 0;              // workspace the OTHER candidate partitions would need for their lanes
   if (!singles.empty()) {
     GreenSet* set = nullptr;
     if (green && max_lanes > 1 && singles.size() > 1) {
-      double ms = 0;
-      const std::vector<int> units = choose_units(dims, pool->n_units, pool->unit_sms, pool->rem_sms, ctx->num_sms, max_lanes, &ms);
+      // candidate partitions: the model's best for max_lanes and for one lane fewer
+      TuneEntry* te = nullptr;
+      for (TuneEntry* t : pool->tune)
+        if (t->dims == dims) { te = t; break; }
+      if (!te) {
+        te = new TuneEntry;
+        te->dims = dims;
+        for (int ml = max_lanes; ml >= std::max(2, max_lanes - 1); --ml) {
+          double ms = 0;
+          std::vector<int> units = choose_units(dims, pool->n_units, pool->unit_sms, pool->rem_sms, ctx->num_sms, ml, &ms);
+          if (std::find(te->cand.begin(), te->cand.end(), units) == te->cand.end()) te->cand.push_back(units);
+        }
+        te->ms.assign(te->cand.size(), -1.0);
+        if (pool->tune.size() >= 64) { delete pool->tune.front(); pool->tune.erase(pool->tune.begin()); }
+        pool->tune.push_back(te);
+      }
+      if (for_run && te->pending && te->last >= 0 && cudaEventQuery(te->end) == cudaSuccess) {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, te->begin, te->end) == cudaSuccess)
+          te->ms[te->last] = te->ms[te->last] < 0 ? ms : std::min<double>(te->ms[te->last], ms);
+        te->pending = false;
+      }
+      (void)cudaGetLastError();
+      int pick = 0;
+      bool exploring = false;
+      for (size_t c = 0; c < te->cand.size(); ++c)
+        if (te->ms[c] < 0) { pick = (int)c; exploring = true; break; }
+      if (!exploring)
+        for (size_t c = 1; c < te->cand.size(); ++c)
+          if (te->ms[c] < te->ms[pick]) pick = (int)c;
+      if (te->cand.size() > 1 && for_run) { plan->tune = te; plan->tune_index = pick; }
+      // the workspace must serve whichever candidate runs: every lane of every candidate gets the
+      // largest single workspace it could need
+      for (const std::vector<int>& units : te->cand)
+        if (units.size() > 1) {
+          std::vector<int> widths, w2;
+          for (size_t l = 0; l < units.size(); ++l) widths.push_back(units[l] * pool->unit_sms + (l == 0 ? pool->rem_sms : 0));
+          place_jobs(dims, widths, &w2);
+          std::vector<size_t> mx(units.size(), 0);
+          for (size_t i = 0; i < dims.size(); ++i) mx[w2[i]] = std::max(mx[w2[i]], lwork_bytes((cusolverDnHandle_t)ctx->cusolver, dims[i]));
+          size_t tot = 0;
+          for (size_t v : mx) tot += v;
+          lane_ws_floor = std::max(lane_ws_floor, tot);
+        }
+      const std::vector<int>& units = te->cand[pick];
       if (units.size() > 1) set = get_green_set(pool, units);
     }
     if (set) {
@@ -541,7 +616,7 @@ int make_plan(kfb::Context* ctx, LanePool* pool, const kfb_syevd_job* jobs, int 
     for (int i : plan->lanes[l]) mx = std::max(mx, lwork_bytes((cusolverDnHandle_t)ctx->cusolver, jobs[i].d));
     plan->lane_off[l + 1] = plan->lane_off[l] + mx;
   }
-  plan->group_off = plan->lane_off[n_lanes];
+  plan->group_off = std::max(plan->lane_off[n_lanes], lane_ws_floor);
   size_t gmax = 0;
   for (auto& g : plan->groups) gmax = std::max(gmax, g.bytes);   // groups run one after another
   plan->total = plan->group_off + gmax;
@@ -618,8 +693,9 @@ size_t kfb_syevd_batch_workspace_bytes(const kfb_syevd_job* jobs, int32_t n_jobs
   if (!ctx || !jobs || n_jobs <= 0) return 0;
   LanePool* pool;
   if (get_pool(ctx, &pool)) return 0;
+  std::lock_guard<std::mutex> call_lock(g_call_mu[ctx->device]);
   BatchPlan plan;
-  if (make_plan(ctx, pool, jobs, n_jobs, &plan)) return 0;
+  if (make_plan(ctx, pool, jobs, n_jobs, &plan, false)) return 0;
   return plan.total;
 }
 
@@ -634,12 +710,19 @@ int kfb_syevd_batch(const kfb_syevd_job* jobs, int32_t n_jobs, void* workspace, 
   LanePool* pool;
   if ((rc = get_pool(ctx, &pool))) return rc;
   BatchPlan plan;
-  if ((rc = make_plan(ctx, pool, jobs, n_jobs, &plan))) return rc;
+  std::lock_guard<std::mutex> call_lock(g_call_mu[ctx->device]);
+  if ((rc = make_plan(ctx, pool, jobs, n_jobs, &plan, true))) return rc;
   if (!workspace || workspace_bytes < plan.total)
     KFB_FAIL(KFB_ERR_WORKSPACE, "syevd batch workspace: need %zu bytes, got %zu", plan.total, workspace_bytes);
   KFB_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
-  std::lock_guard<std::mutex> call_lock(g_call_mu[ctx->device]);
   const int n_lanes = (int)plan.lanes.size();
+  if (plan.tune) {
+    if (!plan.tune->begin) {
+      KFB_CUDA(cudaEventCreate(&plan.tune->begin));
+      KFB_CUDA(cudaEventCreate(&plan.tune->end));
+    }
+    KFB_CUDA(cudaEventRecord(plan.tune->begin, stream));
+  }
   // fork: every lane starts after what is already queued on the caller's stream
   KFB_CUDA(cudaEventRecord(pool->start, stream));
   std::vector<int> status(n_lanes, KFB_OK);
@@ -677,6 +760,11 @@ int kfb_syevd_batch(const kfb_syevd_job* jobs, int32_t n_jobs, void* workspace, 
   for (int l = 0; l < n_lanes; ++l)
     if (!plan.lanes[l].empty()) KFB_CUDA(cudaStreamWaitEvent(stream, plan.lane_ptr[l]->done, 0));
   if (!plan.groups.empty() && grc == KFB_OK) KFB_CUDA(cudaStreamWaitEvent(stream, pool->grouped.done, 0));
+  if (plan.tune) {
+    KFB_CUDA(cudaEventRecord(plan.tune->end, stream));
+    plan.tune->last = plan.tune_index;
+    plan.tune->pending = true;
+  }
   if (grc) return grc;
   for (int l = 0; l < n_lanes; ++l)
     if (status[l]) KFB_FAIL(status[l], "syevd batch lane %d failed: %s", l, errors[l].c_str());

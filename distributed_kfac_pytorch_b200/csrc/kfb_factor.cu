@@ -307,9 +307,19 @@ __global__ void __launch_bounds__(256) tri_kernel(const __grid_constant__ TriBat
 
 // Staging copies for the tensor-core SYRK (PadJob): every thread writes four consecutive floats of
 // one copy.  HBM-bound: reads the capture once, writes 1.0-1.2x its size.
+// The staging copies exist only for the tensor-core SYRK, whose kind::tf32 MMAs read the top 19 bits of
+// an fp32 operand, i.e. TRUNCATE it.  Truncation is biased: every x*x term of a diagonal entry comes
+// out low by about 2^-10 of itself, which is most of the factor error budget (3.7e-4 of the 1e-3
+// tolerance, normalised, on the 4608-dim ResNet-50 factor).  Rounding to nearest here costs nothing (the
+// value passes through a register anyway) and makes the operand error unbiased, so it averages out
+// over K.  16-bit captures are exact in TF32.
 template <typename T>
 __device__ __forceinline__ float pad_load(const T* p, int dtype) {
-  if (sizeof(T) == 4) return __ldg(reinterpret_cast<const float*>(p));
+  if (sizeof(T) == 4) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(__ldg(reinterpret_cast<const float*>(p))));
+    return __uint_as_float(r);
+  }
   return widen16(__ldg(reinterpret_cast<const unsigned short*>(p)), dtype);
 }
 

@@ -260,8 +260,15 @@ __device__ __forceinline__ int snake_cluster_tile(int round, int total) {
   return t < total ? t : -1;
 }
 
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+// kEpi: what the epilogue fuses - 0 nothing, 1 the Hadamard multiplier (stage 2), 2 the <D, Dot> reduction
+// (stage 4), 3 both (generic).  kEW: epilogue warps, 4 (one per TMEM lane quarter) or 8 (two per quarter,
+// alternating 32-column chunks).  Specialising on kEpi halves the registers the operand look-ahead
+// holds, which is what lets eight epilogue warps fit without spilling: the short-K stages are bound
+// by the drain, not by the MMAs.
+template <int kEpi, int kEW>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + kEW), 1)
     gemm_tc2_kernel(const __grid_constant__ TcBatch batch, float* __restrict__ dot_acc) {
+  constexpr bool kMul = (kEpi & 1) != 0, kDot = (kEpi & 2) != 0;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint64_t* full = (uint64_t*)(smem + kStages2 * kStageBytes2);
@@ -276,8 +283,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < kStages2; ++s) { umma::mbar_init(&full[s], 1); umma::mbar_init(&empty[s], 1); }
-    // tempty lives in the leader: all 2 x 128 epilogue threads of the pair arrive there
-    for (int s = 0; s < 2; ++s) { umma::mbar_init(&tfull[s], 1); umma::mbar_init(&tempty[s], 2 * 32 * kEpilogueWarps); }
+    // tempty lives in the leader: all epilogue threads of the pair arrive there
+    for (int s = 0; s < 2; ++s) { umma::mbar_init(&tfull[s], 1); umma::mbar_init(&tempty[s], 2 * 32 * kEW); }
     umma::fence_barrier_init();
   }
   if (warp == 1) umma::tmem_alloc_pair<kTmemCols>(tmem_slot);
@@ -342,7 +349,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     }
   } else {
     // ===================== epilogue (both CTAs: each drains its own 128 accumulator rows) =====
-    const int q = warp & 3;
+    const int q = warp & 3;                      // TMEM lane quarter this warp may read
+    const int half = (warp - 2) >> 2;            // kEW = 8: which of the two warps of this quarter
+    constexpr int kStride = kEW / 4;
     int acc = 0; uint32_t acc_phase = 0;
     float dot = 0.f;
     for (int round = 0, tile; (tile = snake_cluster_tile(round, batch.total_tiles)) >= 0; ++round) {
@@ -352,50 +361,52 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
       const int m0 = (local / pr.tiles_n()) * 256 + (int)rank * 128, n0 = (local % pr.tiles_n()) * pr.bn;
       const int m = m0 + q * 32 + lane;
       const bool row_ok = m < pr.M;
-      const float* mrow = (pr.Mul && row_ok) ? pr.Mul + (int64_t)m * pr.ldmul + n0 : nullptr;
-      const float* grow = (pr.Dot && row_ok) ? pr.Dot + (int64_t)m * pr.lddot + n0 : nullptr;
+      const float* xrow = nullptr;               // the fused operand's row: Mul (stage 2) or Dot (stage 4)
+      const float* grow = nullptr;               // kEpi == 3 only: Dot beside Mul
+      if (kMul && pr.Mul && row_ok) xrow = pr.Mul + (int64_t)m * pr.ldmul + n0;
+      if (kDot && pr.Dot && row_ok) (kMul ? grow : xrow) = pr.Dot + (int64_t)m * pr.lddot + n0;
       float* drow = pr.D + (int64_t)m * pr.ldd + n0;
       const int ncols = min(pr.bn, pr.N - n0);
-      float4 mm[8], gg[8];
-      auto load_aux = [&](int c, float4 (&dm)[8], float4 (&dg)[8]) {
+      auto load_row = [&](const float* row, int c, float4 (&d)[8], float fill) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          dm[j] = make_float4(1.f, 1.f, 1.f, 1.f);
-          dg[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+          d[j] = make_float4(fill, fill, fill, fill);
           const int col = c * 32 + 4 * j;
+          if (!row) continue;
           if (col + 3 < ncols) {
-            if (mrow) dm[j] = __ldg(reinterpret_cast<const float4*>(mrow + col));
-            if (grow) dg[j] = __ldg(reinterpret_cast<const float4*>(grow + col));
+            d[j] = __ldg(reinterpret_cast<const float4*>(row + col));
           } else if (col < ncols) {
-            float tm[4] = {1.f, 1.f, 1.f, 1.f}, tg[4] = {0.f, 0.f, 0.f, 0.f};
+            float t[4] = {fill, fill, fill, fill};
             for (int e = 0; e < 4; ++e)
-              if (col + e < ncols) {
-                if (mrow) tm[e] = mrow[col + e];
-                if (grow) tg[e] = grow[col + e];
-              }
-            dm[j] = make_float4(tm[0], tm[1], tm[2], tm[3]);
-            dg[j] = make_float4(tg[0], tg[1], tg[2], tg[3]);
+              if (col + e < ncols) t[e] = row[col + e];
+            d[j] = make_float4(t[0], t[1], t[2], t[3]);
           }
         }
       };
+      const float xfill = kMul ? 1.f : 0.f;
       const int nchunks = (ncols + 31) / 32;
-      load_aux(0, mm, gg);
+      float4 xx[8], gg[8];
+      if (kEpi != 0 && half < nchunks) load_row(xrow, half, xx, xfill);
+      if (kEpi == 3 && half < nchunks) load_row(grow, half, gg, 0.f);
       umma::mbar_wait(&tfull[acc], acc_phase);
       umma::tc_fence_after();
       const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
 #pragma unroll 1
-      for (int c = 0; c < nchunks; ++c) {
+      for (int c = half; c < nchunks; c += kStride) {
         uint32_t r[32];
         umma::tmem_ld_32x32(taddr + c * 32, r);
-        float4 mm_next[8], gg_next[8];
-        if (c + 1 < nchunks) load_aux(c + 1, mm_next, gg_next);
+        float4 xn[8], gn[8];
+        const bool more = c + kStride < nchunks;
+        if (kEpi != 0 && more) load_row(xrow, c + kStride, xn, xfill);
+        if (kEpi == 3 && more) load_row(grow, c + kStride, gn, 0.f);
         umma::tmem_ld_wait();
         if (row_ok) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             const int col = c * 32 + 4 * j;
-            float4 v = make_float4(__uint_as_float(r[4 * j]) * mm[j].x, __uint_as_float(r[4 * j + 1]) * mm[j].y,
-                                   __uint_as_float(r[4 * j + 2]) * mm[j].z, __uint_as_float(r[4 * j + 3]) * mm[j].w);
+            float4 v = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
+                                   __uint_as_float(r[4 * j + 3]));
+            if (kMul) { v.x *= xx[j].x; v.y *= xx[j].y; v.z *= xx[j].z; v.w *= xx[j].w; }
             if (col + 3 < ncols) {
               *reinterpret_cast<float4*>(drow + col) = v;
             } else if (col < ncols) {
@@ -403,19 +414,23 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
               for (int e = 0; e < 4; ++e)
                 if (col + e < ncols) drow[col + e] = tv[e];
             }
-            dot = fmaf(v.x, gg[j].x, fmaf(v.y, gg[j].y, fmaf(v.z, gg[j].z, fmaf(v.w, gg[j].w, dot))));
+            if (kEpi == 2) dot = fmaf(v.x, xx[j].x, fmaf(v.y, xx[j].y, fmaf(v.z, xx[j].z, fmaf(v.w, xx[j].w, dot))));
+            if (kEpi == 3) dot = fmaf(v.x, gg[j].x, fmaf(v.y, gg[j].y, fmaf(v.z, gg[j].z, fmaf(v.w, gg[j].w, dot))));
           }
         }
-        if (c + 1 < nchunks) {
+        if (more) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) { mm[j] = mm_next[j]; gg[j] = gg_next[j]; }
+          for (int j = 0; j < 8; ++j) {
+            if (kEpi != 0) xx[j] = xn[j];
+            if (kEpi == 3) gg[j] = gn[j];
+          }
         }
       }
       umma::tc_fence_before();
       umma::mbar_arrive_leader(&tempty[acc]);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
-    if (dot_acc) {
+    if (kDot && dot_acc) {
       dot = warp_sum(dot);
       if (lane == 0 && dot != 0.f) atomicAdd(dot_acc, dot);
     }
@@ -488,18 +503,31 @@ bool gemm_tc_eligible(const GemmProb& p) {
   return p.M > 0 && p.N > 0 && p.K > 0;
 }
 
+typedef void (*Tc2Kernel)(const TcBatch, float*);
+template <int kEpi, int kEW>
+static int launch_tc2(Context* ctx, const TcBatch& batch, int clusters, float* dot_acc, cudaStream_t stream) {
+  static bool attr_set[64] = {};        // the opt-in to > 48 KB of dynamic shared memory is per device (and per instantiation)
+  if (!attr_set[ctx->device]) {
+    KFB_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel<kEpi, kEW>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes2));
+    attr_set[ctx->device] = true;
+  }
+  gemm_tc2_kernel<kEpi, kEW><<<2 * clusters, 32 * (2 + kEW), kSmemBytes2, stream>>>(batch, dot_acc);
+  KFB_CHECK_LAUNCH();
+  return KFB_OK;
+}
+
 static int gemm_grouped_tc2(Context* ctx, const GemmProb* probs, int n, float* dot_acc, cudaStream_t stream) {
+  // eight epilogue warps by default (KFB_GEMM_EPI_WARPS=4: one per TMEM lane quarter)
+  static const int epi_warps = []() { const char* e = getenv("KFB_GEMM_EPI_WARPS"); return e && atoi(e) == 4 ? 4 : 8; }();
   std::vector<GemmProb> sorted(probs, probs + n);
   std::stable_sort(sorted.begin(), sorted.end(), [](const GemmProb& a, const GemmProb& b) { return a.K > b.K; });
   probs = sorted.data();
+  // what the epilogue of this launch has to fuse (a stage's problems all ask for the same thing)
+  int epi = 0;
+  for (int i = 0; i < n; ++i) epi |= (probs[i].Mul ? 1 : 0) | ((probs[i].Dot && dot_acc) ? 2 : 0);
   static TcBatch batch;
   static std::mutex mu;
   std::lock_guard<std::mutex> lock(mu);
-  static bool attr_set[64] = {};        // the opt-in to > 48 KB of dynamic shared memory is per device
-  if (!attr_set[ctx->device]) {
-    KFB_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes2));
-    attr_set[ctx->device] = true;
-  }
   for (int base = 0; base < n; base += kTcBatch) {
     batch.n = std::min(kTcBatch, n - base);
     int tiles = 0;
@@ -511,7 +539,7 @@ static int gemm_grouped_tc2(Context* ctx, const GemmProb* probs, int n, float* d
       t.bn = g.N > 128 ? 256 : 128;
       rc = get_map(ctx, g.B, g.ldb, g.N, g.K, t.bn / 2, &t.mapB);      // each CTA loads half of the B tile
       if (rc) return rc;
-      t.D = g.D; t.Mul = g.Mul; t.Dot = g.Dot; t.ldd = g.ldd; t.ldmul = g.ldmul; t.lddot = g.lddot;
+      t.D = g.D; t.Mul = g.Mul; t.Dot = dot_acc ? g.Dot : nullptr; t.ldd = g.ldd; t.ldmul = g.ldmul; t.lddot = g.lddot;
       t.M = g.M; t.N = g.N; t.K = g.K;
       batch.start[i] = tiles;
       tiles += ceil_div(g.M, 256) * t.tiles_n();
@@ -519,8 +547,19 @@ static int gemm_grouped_tc2(Context* ctx, const GemmProb* probs, int n, float* d
     batch.start[batch.n] = tiles;
     batch.total_tiles = tiles;
     const int clusters = std::min(tiles, ctx->num_sms / 2);
-    gemm_tc2_kernel<<<2 * clusters, kThreads, kSmemBytes2, stream>>>(batch, dot_acc);
-    KFB_CHECK_LAUNCH();
+    int rc;
+    if (epi_warps == 8) {
+      rc = epi == 0 ? launch_tc2<0, 8>(ctx, batch, clusters, dot_acc, stream)
+           : epi == 1 ? launch_tc2<1, 8>(ctx, batch, clusters, dot_acc, stream)
+           : epi == 2 ? launch_tc2<2, 8>(ctx, batch, clusters, dot_acc, stream)
+                      : launch_tc2<3, 8>(ctx, batch, clusters, dot_acc, stream);
+    } else {
+      rc = epi == 0 ? launch_tc2<0, 4>(ctx, batch, clusters, dot_acc, stream)
+           : epi == 1 ? launch_tc2<1, 4>(ctx, batch, clusters, dot_acc, stream)
+           : epi == 2 ? launch_tc2<2, 4>(ctx, batch, clusters, dot_acc, stream)
+                      : launch_tc2<3, 4>(ctx, batch, clusters, dot_acc, stream);
+    }
+    if (rc) return rc;
   }
   return KFB_OK;
 }

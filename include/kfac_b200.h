@@ -141,6 +141,9 @@ KFB_API int kfb_capture_filter(const kfb_filter_job* jobs, int32_t n_jobs, const
 KFB_API int kfb_narrow(const float* src, void* dst16, int64_t n, int32_t dtype, void* stream);
 KFB_API int kfb_widen(const void* src16, float* dst, int64_t n, int32_t dtype, void* stream);
 
+/* Both factor-update entry points plan on the host and, on every call, upload their descriptor tables
+ * with cudaMemcpyAsync from ordinary (pageable) host memory owned by the library's plan cache and
+ * clear their accumulators with cudaMemsetAsync before the kernels run. */
 KFB_API size_t kfb_factor_workspace_bytes(const kfb_factor_job* jobs, int32_t n_jobs);
 KFB_API int kfb_factor_update(const kfb_factor_job* jobs, int32_t n_jobs, float alpha,
                       void* workspace, size_t workspace_bytes, void* stream);

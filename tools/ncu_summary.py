@@ -1,5 +1,7 @@
 """Summarise an .ncu-rep (ncu --set full) into a small text table for profiles/.
-Usage: python tools/ncu_summary.py report.ncu-rep > profiles/xxx.txt"""
+Usage: python tools/ncu_summary.py report.ncu-rep [--json profiles/xxx.json] > profiles/xxx.txt
+The JSON form (per launch: kernel, ms, DRAM bytes read / written, tensor-pipe %) is what bench.py reads
+its `roofline.traffic` from."""
 import csv
 import io
 import subprocess
@@ -35,6 +37,28 @@ def main():
         if m in hdr:
             i = hdr.index(m)
             print('%-100s %-10s %s' % (m, units[i], '  '.join(r[i] for r in rows[2:])))
+    if '--json' in sys.argv:
+        import json
+
+        def col(name, r, scale_units=True):
+            if name not in hdr:
+                return None
+            i = hdr.index(name)
+            v = float(r[i].replace(',', ''))
+            u = units[i].lower()
+            if scale_units:
+                v *= {'gbyte': 1e9, 'mbyte': 1e6, 'kbyte': 1e3, 'byte': 1.0, 'ms': 1.0, 'us': 1e-3, 'ns': 1e-6,
+                      'msecond': 1.0, 'usecond': 1e-3, 'nsecond': 1e-6, 'second': 1e3}.get(u, 1.0)
+            return v
+        out = []
+        for r in rows[2:]:
+            out.append({'kernel': r[name_i].split('(')[0].replace('void ', '').replace('kfb::<unnamed>::', ''),
+                        'ms': col('gpu__time_duration.sum', r),
+                        'dram_read_bytes': col('dram__bytes_read.sum', r), 'dram_write_bytes': col('dram__bytes_write.sum', r),
+                        'tensor_pipe_pct': col('sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed', r, False),
+                        'dram_pct': col('gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed', r, False)})
+        with open(sys.argv[sys.argv.index('--json') + 1], 'w') as f:
+            json.dump({'report': rep, 'launches': out}, f, indent=1)
 
 
 if __name__ == '__main__':
