@@ -531,9 +531,18 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
     uint32_t acc_phase = 0;
     int acc = 0;
     int stage = 0; uint32_t phase = 0;
+#ifdef KFB_SYRK_PROFILE
+    // clock64 breakdown of the issuing thread's time (build this file with -DKFB_SYRK_PROFILE)
+    long long pf_tempty = 0, pf_full = 0, pf_issue = 0, pf_drain = 0, pf_items = 0, pf_stages = 0;
+    long long pf_type_clk[3] = {0, 0, 0}, pf_type_units[3] = {0, 0, 0};
+    const long long pf_t0 = clock64();
+#endif
     for (int round = 0, it; (it = next_item<kPair>(round, n_items, cta_first)) >= 0; ++round) {
       const TcItem item = items[it];
       const DevJob& job = jobs[item.job];
+#ifdef KFB_SYRK_PROFILE
+      const long long pf_item0 = clock64();
+#endif
       // device-side multiplier of the segment weight (AMP unscale; 0 = capture dropped, kfb_capture_filter)
       const float* dscale = segs[item.seg].dev_scale;
       const float dmul = dscale ? __ldg(dscale) : 1.f;
@@ -544,8 +553,15 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
       const float ratio = alpha / (1.f - alpha), one_m = 1.f - alpha;
       if (!kPair && warp == 0) {
         if (lane == 0) {
+#ifdef KFB_SYRK_PROFILE
+          const long long pa = clock64();
+#endif
           umma::mbar_wait(tempty, acc_phase ^ 1);            // all four warps have drained TMEM
           umma::tc_fence_after();
+#ifdef KFB_SYRK_PROFILE
+          pf_tempty += clock64() - pa;
+          ++pf_items;
+#endif
           // Per item: everything about the (up to two) MMAs of a k step except the stage offset.  Row
           // tile m runs against column tiles n0..nj-1 in ONE instruction (N = 128 or 256); on the
           // diagonal the column tiles are the row tiles and products below the diagonal are skipped.
@@ -562,8 +578,16 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
           const bool two = item.mi > 1;
           uint32_t acc_flag = 0;
           for (uint32_t k0 = item.k_begin; k0 < item.k_end; k0 += BK) {
+#ifdef KFB_SYRK_PROFILE
+            const long long pb = clock64();
+#endif
             umma::mbar_wait_a(full_a + 8 * stage, phase);
             umma::tc_fence_after();
+#ifdef KFB_SYRK_PROFILE
+            const long long pc = clock64();
+            pf_full += pc - pb;
+            ++pf_stages;
+#endif
             const uint32_t soff = (uint32_t)stage * (kStageBytes >> 4);
 #pragma unroll
             for (int k = 0; k < BK / UMMA_K; ++k)
@@ -576,6 +600,9 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
             acc_flag = 1u;
             umma::tc_commit(&empty[stage]);
             if (++stage == kStages) { stage = 0; phase ^= 1; }
+#ifdef KFB_SYRK_PROFILE
+            pf_issue += clock64() - pc;
+#endif
           }
           umma::tc_commit(tfull);
         }
@@ -583,6 +610,9 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
       }
       umma::mbar_wait(&tfull[acc], acc_phase);
       umma::tc_fence_after();
+#ifdef KFB_SYRK_PROFILE
+      const long long pe = clock64();
+#endif
       // single CTA: both row tiles, accumulators at columns m*256; pair: this CTA's row tile only
       // (a0 + rank), accumulator buffer `acc` at columns acc*256
       const int m_begin = kPair ? (int)rank : 0;
@@ -695,6 +725,17 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
         }
       }
       umma::tc_fence_before();
+#ifdef KFB_SYRK_PROFILE
+      {
+        const long long now = clock64();
+        pf_drain += now - pe;
+        const DevSegment& ps = segs[item.seg];
+        const int ty = ps.tma >= 0 ? 0 : ps.nomask ? 1 : 2;
+        const long long units = item.a0 == item.b0 ? (item.mi * (item.mi + 1)) / 2 : item.mi * item.nj;
+        pf_type_clk[ty] += now - pf_item0;
+        pf_type_units[ty] += units * ((item.k_end - item.k_begin) / BK);
+      }
+#endif
       if (kPair) {
         umma::mbar_arrive_leader(&tempty[acc]);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
@@ -703,6 +744,15 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
         acc_phase ^= 1;
       }
     }
+#ifdef KFB_SYRK_PROFILE
+    if (!kPair && threadIdx.x == 0 && (blockIdx.x % 21) == 0)
+      printf("syrk cta %3d: total %lld clk, items %lld stages %lld | issuer: wait tempty %lld, wait full %lld, issue %lld | drain %lld | "
+             "clk per stage-unit: tma %.0f (%lld), staged %.0f (%lld), gather %.0f (%lld)\n",
+             blockIdx.x, clock64() - pf_t0, pf_items, pf_stages, pf_tempty, pf_full, pf_issue, pf_drain,
+             pf_type_units[0] ? (double)pf_type_clk[0] / pf_type_units[0] : 0.0, pf_type_units[0],
+             pf_type_units[1] ? (double)pf_type_clk[1] / pf_type_units[1] : 0.0, pf_type_units[1],
+             pf_type_units[2] ? (double)pf_type_clk[2] / pf_type_units[2] : 0.0, pf_type_units[2]);
+#endif
   }
 
   umma::tc_fence_before();
