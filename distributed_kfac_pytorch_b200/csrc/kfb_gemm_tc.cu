@@ -323,16 +323,35 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + kEW), 1)
     if (leader && lane == 0) {
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0;
+#ifdef KFB_GEMM_PROFILE
+      long long pf_tempty = 0, pf_full = 0, pf_issue = 0, pf_tiles = 0, pf_kb = 0;
+      const long long pf_t0 = clock64();
+#endif
       for (int round = 0, tile; (tile = snake_cluster_tile(round, batch.total_tiles)) >= 0; ++round) {
         const int p = find_prob(batch, tile);
         const int kblocks = (batch.probs[p].K + BK - 1) / BK;
         const uint32_t idesc = umma::make_idesc_tf32(256, batch.probs[p].bn);
+#ifdef KFB_GEMM_PROFILE
+        const long long pa = clock64();
+#endif
         umma::mbar_wait(&tempty[acc], acc_phase ^ 1);
         umma::tc_fence_after();
+#ifdef KFB_GEMM_PROFILE
+        pf_tempty += clock64() - pa;
+        ++pf_tiles;
+#endif
         const uint32_t d_tmem = tmem_base + acc * BN;
         for (int kb = 0; kb < kblocks; ++kb) {
+#ifdef KFB_GEMM_PROFILE
+          const long long pb = clock64();
+#endif
           umma::mbar_wait(&full[stage], phase);
           umma::tc_fence_after();
+#ifdef KFB_GEMM_PROFILE
+          const long long pc = clock64();
+          pf_full += pc - pb;
+          ++pf_kb;
+#endif
           const uint32_t sa = umma::smem_u32(smem + stage * kStageBytes2);
           const uint32_t sb = sa + 128 * BK * 4;
           const uint64_t da = umma::make_kmajor_sw128_desc(sa);
@@ -342,10 +361,18 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + kEW), 1)
             umma::mma_tf32_ss_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
           umma::tc_commit_pair(&empty[stage]);
           if (++stage == kStages2) { stage = 0; phase ^= 1; }
+#ifdef KFB_GEMM_PROFILE
+          pf_issue += clock64() - pc;
+#endif
         }
         umma::tc_commit_pair(&tfull[acc]);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
+#ifdef KFB_GEMM_PROFILE
+      if ((blockIdx.x % 36) == 0)
+        printf("gemm<%d,%d> cta %3d: total %lld clk, tiles %lld k-blocks %lld | issuer: wait tempty %lld, wait full %lld, issue %lld\n", kEpi, kEW,
+               blockIdx.x, clock64() - pf_t0, pf_tiles, pf_kb, pf_tempty, pf_full, pf_issue);
+#endif
     }
   } else {
     // ===================== epilogue (both CTAs: each drains its own 128 accumulator rows) =====
@@ -354,6 +381,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + kEW), 1)
     constexpr int kStride = kEW / 4;
     int acc = 0; uint32_t acc_phase = 0;
     float dot = 0.f;
+#ifdef KFB_GEMM_PROFILE
+    long long pe_wait = 0, pe_drain = 0;
+#endif
     for (int round = 0, tile; (tile = snake_cluster_tile(round, batch.total_tiles)) >= 0; ++round) {
       const int p = find_prob(batch, tile);
       const TcProb& pr = batch.probs[p];
@@ -388,8 +418,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + kEW), 1)
       float4 xx[8], gg[8];
       if (kEpi != 0 && half < nchunks) load_row(xrow, half, xx, xfill);
       if (kEpi == 3 && half < nchunks) load_row(grow, half, gg, 0.f);
+#ifdef KFB_GEMM_PROFILE
+      const long long pe0 = clock64();
+#endif
       umma::mbar_wait(&tfull[acc], acc_phase);
       umma::tc_fence_after();
+#ifdef KFB_GEMM_PROFILE
+      const long long pe1 = clock64();
+      pe_wait += pe1 - pe0;
+#endif
       const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
 #pragma unroll 1
       for (int c = half; c < nchunks; c += kStride) {
@@ -427,9 +464,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + kEW), 1)
         }
       }
       umma::tc_fence_before();
+#ifdef KFB_GEMM_PROFILE
+      pe_drain += clock64() - pe1;
+#endif
       umma::mbar_arrive_leader(&tempty[acc]);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+#ifdef KFB_GEMM_PROFILE
+    if (warp == 2 && lane == 0 && (blockIdx.x % 36) == 0)
+      printf("gemm<%d,%d> cta %3d epilogue warp: wait tfull %lld, drain %lld\n", kEpi, kEW, blockIdx.x, pe_wait, pe_drain);
+#endif
     if (kDot && dot_acc) {
       dot = warp_sum(dot);
       if (lane == 0 && dot != 0.f) atomicAdd(dot_acc, dot);
