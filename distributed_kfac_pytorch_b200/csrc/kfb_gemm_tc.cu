@@ -265,7 +265,10 @@ __device__ __forceinline__ int snake_cluster_tile(int round, int total) {
 // alternating 32-column chunks).  Specialising on kEpi halves the registers the operand look-ahead
 // holds, which is what lets eight epilogue warps fit without spilling: the short-K stages are bound
 // by the drain, not by the MMAs.
-template <int kEpi, int kEW>
+// kCoal: the epilogue passes every 32 x 32 chunk through a 4 KB shared-memory buffer of its warp so that its
+// global accesses are whole 128-byte row segments (a thread owns an accumulator ROW, so straight from the
+// registers one store instruction touches 32 different lines, 16 of every sector's 32 bytes).
+template <int kEpi, int kEW, bool kCoal>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + kEW), 1)
     gemm_tc2_kernel(const __grid_constant__ TcBatch batch, float* __restrict__ dot_acc) {
   constexpr bool kMul = (kEpi & 1) != 0, kDot = (kEpi & 2) != 0;
@@ -415,6 +418,87 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + kEW), 1)
       };
       const float xfill = kMul ? 1.f : 0.f;
       const int nchunks = (ncols + 31) / 32;
+      if (kCoal) {
+        // ---- coalesced drain: lane (rsub = lane >> 3, slot = lane & 7) handles columns 4*slot..4*slot+3 of
+        // rows 4*i + rsub, i = 0..7, of the chunk: 8 lanes = one 128-byte row segment
+        const uint32_t stg = umma::smem_u32(smem + kStages2 * kStageBytes2 + 256) + (uint32_t)(warp - 2) * 4096u;
+        const int rsub = lane >> 3, slot = lane & 7;
+        const int mrow0 = m0 + q * 32 + rsub;                    // global row of i = 0
+        const float* mul_base = (kMul && pr.Mul) ? pr.Mul + n0 + 4 * slot : nullptr;
+        const float* dot_base = (kDot && pr.Dot) ? pr.Dot + n0 + 4 * slot : nullptr;
+        float* d_base = pr.D + n0 + 4 * slot;
+        auto load_aux = [&](const float* base, int64_t ld, int c, float4 (&d)[8], float fill) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            d[i] = make_float4(fill, fill, fill, fill);
+            const int mm = mrow0 + 4 * i, col = c * 32 + 4 * slot;
+            if (!base || mm >= pr.M) continue;
+            const float* ptr = base + (int64_t)mm * ld + c * 32;
+            if (col + 3 < ncols) d[i] = __ldg(reinterpret_cast<const float4*>(ptr));
+            else if (col < ncols) {
+              float t[4] = {fill, fill, fill, fill};
+              for (int e = 0; e < 4; ++e)
+                if (col + e < ncols) t[e] = ptr[e];
+              d[i] = make_float4(t[0], t[1], t[2], t[3]);
+            }
+          }
+        };
+        float4 ax[8], ag[8];
+        if (kMul && half < nchunks) load_aux(mul_base, pr.ldmul, half, ax, 1.f);
+        if (kDot && half < nchunks) load_aux(dot_base, pr.lddot, half, ag, 0.f);
+        umma::mbar_wait(&tfull[acc], acc_phase);
+        umma::tc_fence_after();
+        const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
+#pragma unroll 1
+        for (int c = half; c < nchunks; c += kStride) {
+          uint32_t r[32];
+          umma::tmem_ld_32x32(taddr + c * 32, r);
+          float4 axn[8], agn[8];
+          const bool more = c + kStride < nchunks;
+          if (kMul && more) load_aux(mul_base, pr.ldmul, c + kStride, axn, 1.f);
+          if (kDot && more) load_aux(dot_base, pr.lddot, c + kStride, agn, 0.f);
+          umma::tmem_ld_wait();
+          // registers (row = lane) -> shared, 16-byte slots XOR-swizzled by the row: conflict-free both ways
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(stg + (uint32_t)lane * 128u + (uint32_t)((j ^ (lane & 7)) << 4)),
+                         "r"(r[4 * j]), "r"(r[4 * j + 1]), "r"(r[4 * j + 2]), "r"(r[4 * j + 3])
+                         : "memory");
+          __syncwarp();
+          const int col = c * 32 + 4 * slot;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int rr = 4 * i + rsub, mm = mrow0 + 4 * i;
+            float4 v;
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                         : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                         : "r"(stg + (uint32_t)rr * 128u + (uint32_t)((slot ^ (rr & 7)) << 4)));
+            if (kMul) { v.x *= ax[i].x; v.y *= ax[i].y; v.z *= ax[i].z; v.w *= ax[i].w; }
+            if (mm < pr.M) {
+              float* dp = d_base + (int64_t)mm * pr.ldd + c * 32;
+              if (col + 3 < ncols) *reinterpret_cast<float4*>(dp) = v;
+              else if (col < ncols) {
+                const float tv[4] = {v.x, v.y, v.z, v.w};
+                for (int e = 0; e < 4; ++e)
+                  if (col + e < ncols) dp[e] = tv[e];
+              }
+              if (kDot) dot = fmaf(v.x, ag[i].x, fmaf(v.y, ag[i].y, fmaf(v.z, ag[i].z, fmaf(v.w, ag[i].w, dot))));
+            }
+          }
+          __syncwarp();
+          if (more) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              if (kMul) ax[i] = axn[i];
+              if (kDot) ag[i] = agn[i];
+            }
+          }
+        }
+        umma::tc_fence_before();
+        umma::mbar_arrive_leader(&tempty[acc]);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        continue;
+      }
       float4 xx[8], gg[8];
       if (kEpi != 0 && half < nchunks) load_row(xrow, half, xx, xfill);
       if (kEpi == 3 && half < nchunks) load_row(grow, half, gg, 0.f);
@@ -548,14 +632,15 @@ bool gemm_tc_eligible(const GemmProb& p) {
 }
 
 typedef void (*Tc2Kernel)(const TcBatch, float*);
-template <int kEpi, int kEW>
+template <int kEpi, int kEW, bool kCoal>
 static int launch_tc2(Context* ctx, const TcBatch& batch, int clusters, float* dot_acc, cudaStream_t stream) {
   static bool attr_set[64] = {};        // the opt-in to > 48 KB of dynamic shared memory is per device (and per instantiation)
+  constexpr int smem = kSmemBytes2 + (kCoal ? kEW * 4096 : 0);      // + one 32 x 32 fp32 staging buffer per epilogue warp
   if (!attr_set[ctx->device]) {
-    KFB_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel<kEpi, kEW>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes2));
+    KFB_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel<kEpi, kEW, kCoal>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr_set[ctx->device] = true;
   }
-  gemm_tc2_kernel<kEpi, kEW><<<2 * clusters, 32 * (2 + kEW), kSmemBytes2, stream>>>(batch, dot_acc);
+  gemm_tc2_kernel<kEpi, kEW, kCoal><<<2 * clusters, 32 * (2 + kEW), smem, stream>>>(batch, dot_acc);
   KFB_CHECK_LAUNCH();
   return KFB_OK;
 }
@@ -591,17 +676,23 @@ static int gemm_grouped_tc2(Context* ctx, const GemmProb* probs, int n, float* d
     batch.start[batch.n] = tiles;
     batch.total_tiles = tiles;
     const int clusters = std::min(tiles, ctx->num_sms / 2);
+    static const bool coal = []() { const char* e = getenv("KFB_GEMM_COALESCE"); return !e || atoi(e) != 0; }();
     int rc;
-    if (epi_warps == 8) {
-      rc = epi == 0 ? launch_tc2<0, 8>(ctx, batch, clusters, dot_acc, stream)
-           : epi == 1 ? launch_tc2<1, 8>(ctx, batch, clusters, dot_acc, stream)
-           : epi == 2 ? launch_tc2<2, 8>(ctx, batch, clusters, dot_acc, stream)
-                      : launch_tc2<3, 8>(ctx, batch, clusters, dot_acc, stream);
+    if (coal) {          // coalesced drain through shared memory, eight warps
+      rc = epi == 0 ? launch_tc2<0, 8, true>(ctx, batch, clusters, dot_acc, stream)
+           : epi == 1 ? launch_tc2<1, 8, true>(ctx, batch, clusters, dot_acc, stream)
+           : epi == 2 ? launch_tc2<2, 8, true>(ctx, batch, clusters, dot_acc, stream)
+                      : launch_tc2<3, 8, true>(ctx, batch, clusters, dot_acc, stream);
+    } else if (epi_warps == 8) {
+      rc = epi == 0 ? launch_tc2<0, 8, false>(ctx, batch, clusters, dot_acc, stream)
+           : epi == 1 ? launch_tc2<1, 8, false>(ctx, batch, clusters, dot_acc, stream)
+           : epi == 2 ? launch_tc2<2, 8, false>(ctx, batch, clusters, dot_acc, stream)
+                      : launch_tc2<3, 8, false>(ctx, batch, clusters, dot_acc, stream);
     } else {
-      rc = epi == 0 ? launch_tc2<0, 4>(ctx, batch, clusters, dot_acc, stream)
-           : epi == 1 ? launch_tc2<1, 4>(ctx, batch, clusters, dot_acc, stream)
-           : epi == 2 ? launch_tc2<2, 4>(ctx, batch, clusters, dot_acc, stream)
-                      : launch_tc2<3, 4>(ctx, batch, clusters, dot_acc, stream);
+      rc = epi == 0 ? launch_tc2<0, 4, false>(ctx, batch, clusters, dot_acc, stream)
+           : epi == 1 ? launch_tc2<1, 4, false>(ctx, batch, clusters, dot_acc, stream)
+           : epi == 2 ? launch_tc2<2, 4, false>(ctx, batch, clusters, dot_acc, stream)
+                      : launch_tc2<3, 4, false>(ctx, batch, clusters, dot_acc, stream);
     }
     if (rc) return rc;
   }
