@@ -53,11 +53,11 @@ def ncu_traffic(model):
         seen, tot = {}, 0.0
         for l in launches:
             for n in names:
-                if l['kernel'].startswith(n) and seen.get(n, 0) < first_n.get(n, 1):
+                if n in l['kernel'] and seen.get(n, 0) < first_n.get(n, 1):
                     seen[n] = seen.get(n, 0) + 1
                     tot += (l['dram_read_bytes'] or 0) + (l['dram_write_bytes'] or 0)
         return int(tot) if seen else None
-    return {'precondition': total(['gemm_tc2_kernel', 'gemm_tc_kernel'], {'gemm_tc2_kernel': 4, 'gemm_tc_kernel': 4}),
+    return {'precondition': total(['gemm_tc2_kernel'], {'gemm_tc2_kernel': 4}),
             'syrk': total(['pad_kernel', 'syrk_tc_kernel', 'finalize_kernel'], {}),
             'source': os.path.relpath(path, ROOT)}
 

@@ -95,7 +95,7 @@ struct GradJob {
 };
 constexpr int kGradBatch = 512;
 typedef Batch<GradJob, kGradBatch> GradBatch;
-constexpr int kElemsPerBlock = 2048;
+constexpr int kElemsPerBlock = 8192;     // 32 KB read + 32 KB written per block: eight 16-byte accesses per thread in flight
 
 enum { kPack = 0, kDot = 1, kWrite = 2 };
 
@@ -116,13 +116,17 @@ __global__ void __launch_bounds__(256) grad_kernel(const __grid_constant__ GradB
   // weight-only layers whose matrix rows are unpadded 16-byte multiples (every ResNet conv but the
   // first): matrix and gradient are the same flat array, moved 16 bytes per thread
   if (kMode == kWrite && j.nw == j.da && j.ld == j.da && (j.da & 3) == 0 && (((uintptr_t)j.wg | (uintptr_t)j.v) & 15) == 0) {
+    float4 v[kElemsPerBlock / 1024];
+#pragma unroll
+    for (int u = 0; u < kElemsPerBlock / 1024; ++u) {          // all loads first: eight lines in flight per thread
+      const int64_t e = e0 + (int64_t)(u * 256 + threadIdx.x) * 4;
+      v[u] = e < total ? __ldcs(reinterpret_cast<const float4*>(j.v + e)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
 #pragma unroll
     for (int u = 0; u < kElemsPerBlock / 1024; ++u) {
       const int64_t e = e0 + (int64_t)(u * 256 + threadIdx.x) * 4;
       if (e >= total) break;
-      float4 v = *reinterpret_cast<const float4*>(j.v + e);
-      v.x *= nu; v.y *= nu; v.z *= nu; v.w *= nu;
-      *reinterpret_cast<float4*>(j.wg + e) = v;
+      *reinterpret_cast<float4*>(j.wg + e) = make_float4(v[u].x * nu, v[u].y * nu, v[u].z * nu, v[u].w * nu);
     }
     return;
   }
