@@ -86,6 +86,8 @@ _SIGNATURES = {
     'kfb_get_mma_mode': (C.c_int, []),
     'kfb_launch_count': (C.c_ulonglong, []),
     'kfb_factor_workspace_bytes': (C.c_size_t, [C.POINTER(CFactorJob), C.c_int32]),
+    'kfb_factor_workspace_dedicate': (C.c_int, [C.c_void_p, C.c_size_t]),
+    'kfb_factor_workspace_release': (C.c_int, [C.c_void_p]),
     'kfb_factor_update': (C.c_int, [C.POINTER(CFactorJob), C.c_int32, C.c_float, C.c_void_p,
                                     C.c_size_t, C.c_void_p]),
     'kfb_capture_filter': (C.c_int, [C.POINTER(CFilterJob), C.c_int32, C.POINTER(CFilterGroup), C.c_int32, C.c_void_p]),
@@ -229,6 +231,7 @@ class CudaOps(object):
         self.lib = load_library()
         self._inited = set()
         self._workspaces = {}
+        self._factor_ws = {}
         self._keepalive = None
 
     # -- helpers
@@ -252,6 +255,26 @@ class CudaOps(object):
             buf = torch.empty(max(int(nbytes), 1 << 20), dtype=torch.uint8, device=device)
             self._workspaces[key] = buf
         return buf
+
+    def factor_workspace(self, nbytes, device):
+        """The factor update's own workspace: nothing else writes into it, and the library is told so
+        (kfb_factor_workspace_dedicate), which lets it keep its split-K accumulators zeroed in place."""
+        key = (device.type, device.index)
+        buf = self._factor_ws.get(key)
+        if buf is None or buf.numel() < nbytes:
+            if buf is not None:
+                self._call('kfb_factor_workspace_release', buf.data_ptr())
+            buf = torch.empty(max(int(nbytes), 1 << 20), dtype=torch.uint8, device=device)
+            self._call('kfb_factor_workspace_dedicate', buf.data_ptr(), buf.numel())
+            self._factor_ws[key] = buf
+        return buf
+
+    def __del__(self):
+        try:
+            for buf in self._factor_ws.values():
+                self.lib.kfb_factor_workspace_release(buf.data_ptr())
+        except Exception:
+            pass
 
     def set_mma_mode(self, mode):
         self._call('kfb_set_mma_mode', int(mode))
@@ -348,7 +371,7 @@ class CudaOps(object):
         cjobs, keep = self._factor_cjobs(jobs)
         n = len(jobs)
         nbytes = self.lib.kfb_factor_workspace_bytes(cjobs, n)
-        ws = self.workspace(nbytes, jobs[0].state.device)
+        ws = self.factor_workspace(nbytes, jobs[0].state.device)
         self._call('kfb_factor_update', cjobs, n, float(alpha), ws.data_ptr(), ws.numel(), stream)
 
     def factor_update_static(self, jobs, alpha):

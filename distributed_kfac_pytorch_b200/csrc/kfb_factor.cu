@@ -459,6 +459,15 @@ int run_tri(const kfb_tri_job* jobs, int n_jobs, float scale, bool unpack, cudaS
 // planning (host)
 // ============================================================================================
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+// KFB_SYRK_LAST_ARRIVER=0: split-K jobs go back to scratch + finalize_kernel
+static int last_arriver_mode() {
+  const char* e = getenv("KFB_SYRK_LAST_ARRIVER");
+  return e ? atoi(e) : 1;
+}
+static int stream_k_mode() {
+  const char* e = getenv("KFB_SYRK_STREAMK");
+  return e ? atoi(e) : 0;
+}
 static int64_t fused_max_rows() {
   const char* e = getenv("KFB_SYRK_FUSE_MAX_ROWS");
   return e ? atoll(e) : kFusedMaxRows;
@@ -483,6 +492,8 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
   plan->pads.clear(); plan->seg_pad.clear(); plan->pad_off.clear(); plan->pad_start.clear();
   plan->stage_floats = 0;
   plan->scratch_floats = 0;
+  plan->la_blocks = 0;
+  size_t la_floats = 0;
   int items = 0, fins = 0;
   const int target = std::max(1, num_sms) * 4;
   for (int ji = 0; ji < n_jobs; ++ji) {
@@ -660,17 +671,41 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
     // a fused job's packed triangle is exported from its finished state by the (coalesced) pack kernel
     // after the SYRK rather than row by row from the epilogue's registers
     if (dj.fused && j.write_state) dj.tri_out = nullptr;
-    dj.scratch_off = plan->scratch_floats;
     dj.T128 = ceil_div(j.d, 128);
     dj.native = (tc && !dj.fused) ? 1 : 0;
-    if (dj.native) plan->scratch_floats += (size_t)dj.T128 * dj.T128 * 128 * 128;
-    else if (!dj.fused) plan->scratch_floats += align_up((size_t)dj.ld_scratch * j.d, 64);
+    // split-K jobs of the single-CTA tensor-core kernel can finish themselves (DevJob::la); their accumulators
+    // and counters form the second part of the scratch region
+    const int pair_min = syrk_pair_mode();
+    dj.la = (dj.native && last_arriver_mode() && !stream_k_mode() && !(pair_min > 0 && dj.T128 >= pair_min)) ? 1 : 0;
+    dj.la_items = 0; dj.arrive = nullptr; dj.arrive_off = 0;
+    if (dj.la) {
+      const int TB = (dj.T128 + 1) / 2;
+      dj.scratch_off = la_floats;
+      la_floats += (size_t)dj.T128 * dj.T128 * 128 * 128;
+      dj.arrive_off = la_floats;
+      la_floats += align_up((size_t)TB * TB, 64);
+      plan->la_blocks += TB * (TB + 1) / 2;
+      if (j.write_state) dj.tri_out = nullptr;    // exported from the finished state by the pack kernel, like a fused job's
+    } else {
+      dj.scratch_off = plan->scratch_floats;
+      if (dj.native) plan->scratch_floats += (size_t)dj.T128 * dj.T128 * 128 * 128;
+      else if (!dj.fused) plan->scratch_floats += align_up((size_t)dj.ld_scratch * j.d, 64);
+    }
     plan->item_start.push_back(items);
     plan->fin_start.push_back(fins);
     if (!tc) items += dj.n_pairs * chunks;
-    if (!dj.fused) fins += dj.T32 * (dj.T32 + 1) / 2;
+    if (!dj.fused && !dj.la) fins += dj.T32 * (dj.T32 + 1) / 2;
     plan->jobs.push_back(dj);
   }
+  plan->la_begin = plan->scratch_floats;
+  for (DevJob& dj : plan->jobs)
+    if (dj.la) { dj.scratch_off += plan->la_begin; dj.arrive_off += plan->la_begin; }
+  // the queue of completed blocks: [pushed, popped, CTAs gone, ...][la_blocks slots]
+  plan->la_ctl_off = plan->la_begin + la_floats;
+  if (plan->la_blocks > 0) la_floats += align_up((size_t)kLaCtlInts + plan->la_blocks, 64);
+  plan->scratch_floats += la_floats;
+  static uint64_t generation = 0;
+  plan->generation = ++generation;
   plan->item_start.push_back(items);
   plan->fin_start.push_back(fins);
   plan->n_items = items;
@@ -712,7 +747,7 @@ std::vector<int64_t> g_plan_sig;
 
 void signature(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool tc, std::vector<int64_t>* sig) {
   sig->clear();
-  sig->push_back(n_jobs); sig->push_back(num_sms); sig->push_back(tc); sig->push_back(tma_mode()); sig->push_back(stage_mode()); sig->push_back(syrk_pair_mode()); sig->push_back(fused_max_rows()); sig->push_back(getenv("KFB_SYRK_STREAMK") ? atoi(getenv("KFB_SYRK_STREAMK")) : 0);
+  sig->push_back(n_jobs); sig->push_back(num_sms); sig->push_back(tc); sig->push_back(tma_mode()); sig->push_back(stage_mode()); sig->push_back(syrk_pair_mode()); sig->push_back(fused_max_rows()); sig->push_back(stream_k_mode()); sig->push_back(last_arriver_mode());
   for (int i = 0; i < n_jobs; ++i) {
     const kfb_factor_job& j = jobs[i];
     sig->push_back(j.d); sig->push_back(j.n_segments); sig->push_back(j.ld_state);
@@ -745,7 +780,7 @@ static int cached_plan(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool
       DevJob& dj = g_plan.jobs[i];
       dj.state = j.state; dj.seed_identity = j.seed_identity; dj.write_state = j.write_state;
       dj.dev_rescale = j.dev_rescale;
-      dj.tri_out = (dj.fused && j.write_state) ? nullptr : j.tri_out;
+      dj.tri_out = ((dj.fused || dj.la) && j.write_state) ? nullptr : j.tri_out;
       for (int k = 0; k < j.n_segments; ++k) {
         KFB_REQUIRE(j.segments[k].data, "factor job %d segment %d: null data", i, k);
         DevSegment& ds = g_plan.segs[dj.seg_start + k];
@@ -758,6 +793,30 @@ static int cached_plan(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool
     }
   }
   *out = &g_plan;
+  return KFB_OK;
+}
+
+// Workspaces the caller has promised to use for kfb_factor_update only (kfb_factor_workspace_dedicate): what the
+// library leaves in them survives until its next call.  Guarded by g_plan_mu.
+namespace {
+struct Dedicated {
+  void* ptr;
+  size_t bytes;
+  uint64_t clean_for;     // generation of the plan whose last-arriver region is known to be zero; 0 = unknown
+};
+std::vector<Dedicated> g_dedicated;
+Dedicated* find_dedicated(void* p) {
+  for (Dedicated& d : g_dedicated)
+    if (d.ptr == p) return &d;
+  return nullptr;
+}
+}  // namespace
+
+int dedicate_workspace(void* workspace, size_t bytes, bool on) {
+  std::lock_guard<std::mutex> lock(g_plan_mu);
+  for (size_t i = 0; i < g_dedicated.size(); ++i)
+    if (g_dedicated[i].ptr == workspace) { g_dedicated.erase(g_dedicated.begin() + i); break; }
+  if (on) g_dedicated.push_back(Dedicated{workspace, bytes, 0});
   return KFB_OK;
 }
 
@@ -774,17 +833,22 @@ int factor_update_with(const kfb_factor_job* jobs, int n_jobs, float alpha, Cont
   bind_workspace(plan, workspace);
   rc = refresh_tmaps(plan, ctx);
   if (rc) return rc;
-  rc = upload_plan(plan, workspace, stream);
+  // a dedicated workspace that last served this very plan holds zeroed last-arriver accumulators and counters
+  Dedicated* own = find_dedicated(workspace);
+  const bool la_clean = own && own->clean_for == plan->generation && own->bytes >= plan->total_bytes;
+  if (own) own->clean_for = 0;
+  rc = upload_plan(plan, workspace, stream, la_clean);
   if (rc) return rc;
   rc = launch_pad(*plan, workspace, stream);
   if (rc) return rc;
   rc = launch_syrk(*plan, workspace, ctx, alpha, stream);
   if (rc) return rc;
+  if (own) own->clean_for = plan->generation;
   rc = launch_finalize(*plan, workspace, alpha, stream);
   if (rc) return rc;
   std::vector<kfb_tri_job> deferred;
   for (int i = 0; i < n_jobs; ++i)
-    if (plan->jobs[i].fused && jobs[i].write_state && jobs[i].tri_out) {
+    if ((plan->jobs[i].fused || plan->jobs[i].la) && jobs[i].write_state && jobs[i].tri_out) {
       kfb_tri_job t;
       t.tri = jobs[i].tri_out; t.state = jobs[i].state; t.ld_state = jobs[i].ld_state; t.d = jobs[i].d;
       deferred.push_back(t);
@@ -805,7 +869,10 @@ size_t factor_workspace_bytes(const kfb_factor_job* jobs, int n_jobs, Context* c
 void bind_workspace(FactorPlan* plan, void* workspace) {
   char* ws = (char*)workspace;
   float* scratch = (float*)(ws + plan->off_scratch);
-  for (auto& j : plan->jobs) j.scratch = scratch + j.scratch_off;
+  for (auto& j : plan->jobs) {
+    j.scratch = scratch + j.scratch_off;
+    j.arrive = j.la ? (int*)(scratch + j.arrive_off) : nullptr;
+  }
   float* stage = (float*)(ws + plan->off_stage);
   for (size_t i = 0; i < plan->segs.size(); ++i) {
     const int pad = plan->seg_pad[i];
@@ -815,7 +882,7 @@ void bind_workspace(FactorPlan* plan, void* workspace) {
   }
 }
 
-int upload_plan(FactorPlan* plan, void* workspace, cudaStream_t stream) {
+int upload_plan(FactorPlan* plan, void* workspace, cudaStream_t stream, bool la_clean) {
   char* ws = (char*)workspace;
   float* scratch = (float*)(ws + plan->off_scratch);
   if (!plan->pads.empty()) {
@@ -832,7 +899,10 @@ int upload_plan(FactorPlan* plan, void* workspace, cudaStream_t stream) {
     KFB_CUDA(cudaMemcpyAsync(ws + plan->off_cta_first, plan->cta_first.data(), plan->cta_first.size() * sizeof(int), cudaMemcpyHostToDevice, stream));
   if (!plan->tmaps.empty())
     KFB_CUDA(cudaMemcpyAsync(ws + plan->off_tmaps, plan->tmaps.data(), plan->tmaps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice, stream));
-  KFB_CUDA(cudaMemsetAsync(scratch, 0, plan->scratch_floats * sizeof(float), stream));
+  // the last-arriver part is re-zeroed by the kernel that used it: cleared here only when this workspace is not
+  // known to hold what the previous update of the same plan left (kfb_factor_workspace_dedicate)
+  const size_t clear = la_clean ? plan->la_begin : plan->scratch_floats;
+  if (clear) KFB_CUDA(cudaMemsetAsync(scratch, 0, clear * sizeof(float), stream));
   return KFB_OK;
 }
 
@@ -888,6 +958,13 @@ int kfb_factor_update(const kfb_factor_job* jobs, int32_t n_jobs, float alpha, v
   return kfb::factor_update_with(jobs, n_jobs, alpha, ctx, workspace, workspace_bytes, "kfb_factor_update",
                                  (cudaStream_t)stream_);
 }
+
+int kfb_factor_workspace_dedicate(void* workspace, size_t workspace_bytes) {
+  KFB_REQUIRE(workspace && ((uintptr_t)workspace & 255) == 0, "workspace must be a 256-byte aligned device pointer");
+  return kfb::dedicate_workspace(workspace, workspace_bytes, true);
+}
+
+int kfb_factor_workspace_release(void* workspace) { return kfb::dedicate_workspace(workspace, 0, false); }
 
 int kfb_tri_unpack(const kfb_tri_job* jobs, int32_t n_jobs, float scale, void* stream) {
   kfb::Context* ctx;

@@ -55,6 +55,12 @@ struct DevJob {
   int T128;              // 128-wide tiles per side
   int fused;             // 1: one K chunk, one segment: the SYRK epilogue applies the running average
                          //    itself and writes the state - no scratch, no reds, no finalize pass
+  int la;                // 1: split-K job finished by the LAST item of every 256 x 256 block to arrive (per-block
+                         //    counter): that item reads the block's sum back from the scratch, re-zeroes scratch and
+                         //    counter, and applies the running average as a fused job does - no finalize pass
+  int la_items;          // items (K chunks over all segments) per block
+  int* arrive;           // [ceil(T128/2)^2] arrival counters, zero between updates
+  size_t arrive_off;     // host only: float offset of the counters inside the scratch region
 };
 
 // One captured element, widened to fp32 (16-bit captures come from AMP autocast).
@@ -129,21 +135,27 @@ struct FactorPlan {
   std::vector<const void*> tmap_ptr;     // the address each descriptor was encoded for
   size_t off_tmaps = 0;
   int n_items = 0, n_fin = 0;
-  size_t scratch_floats = 0;
+  size_t scratch_floats = 0;             // [accumulators cleared by every call][last-arriver accumulators + counters]
+  size_t la_begin = 0;                   // float offset of the second part: left zero by the kernel itself
+  size_t la_ctl_off = 0;                 // float offset of the completed-block queue inside the scratch region
+  int la_blocks = 0;                     // 256 x 256 blocks of all last-arriver jobs
+  uint64_t generation = 0;               // bumped whenever the plan is rebuilt (the layout may have moved)
   size_t off_jobs = 0, off_segs = 0, off_items = 0, off_fin = 0, off_scratch = 0, total_bytes = 0;
 };
 
 KFB_HIDDEN int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_tc, FactorPlan* plan);
 KFB_HIDDEN void plan_syrk_tc(FactorPlan* plan, int num_sms);
-KFB_HIDDEN int upload_plan(FactorPlan* plan, void* workspace, cudaStream_t stream);
+KFB_HIDDEN int upload_plan(FactorPlan* plan, void* workspace, cudaStream_t stream, bool la_clean = false);
 KFB_HIDDEN int refresh_tmaps(FactorPlan* plan, Context* ctx);
 KFB_HIDDEN void bind_workspace(FactorPlan* plan, void* workspace);
 KFB_HIDDEN int launch_pad(const FactorPlan& plan, void* workspace, cudaStream_t stream);
 KFB_HIDDEN int launch_syrk_simt(const FactorPlan& plan, void* workspace, cudaStream_t stream);
 KFB_HIDDEN int launch_syrk(const FactorPlan& plan, void* workspace, Context* ctx, float alpha, cudaStream_t stream);
+constexpr int kLaCtlInts = 64;            // control words in front of the completed-block queue
 constexpr int64_t kFusedMaxRows = 4096;   // jobs with at most this many rows of X are never split along K
 KFB_HIDDEN int factor_update_with(const kfb_factor_job* jobs, int n_jobs, float alpha, Context* ctx, void* workspace,
                                   size_t workspace_bytes, const char* what, cudaStream_t stream);
+KFB_HIDDEN int dedicate_workspace(void* workspace, size_t bytes, bool on);
 KFB_HIDDEN size_t factor_workspace_bytes(const kfb_factor_job* jobs, int n_jobs, Context* ctx);
 KFB_HIDDEN int launch_finalize(const FactorPlan& plan, void* workspace, float alpha, cudaStream_t stream);
 

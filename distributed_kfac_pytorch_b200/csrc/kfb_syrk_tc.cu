@@ -163,12 +163,114 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
+// ---- last-arriver finish of one 32 x 32 chunk of a split-K job (DevJob::la) --------------------------------
+// The chunk's complete sum is read back from the scratch in the accumulator's own layout (lane = row i, 32
+// columns per lane; coalesced), the scratch is re-zeroed for the next update, and
+//   new = (old * alpha/(1-alpha) + rescale*sum) * (1-alpha)           (kfac/layers/utils.py:175-178)
+// goes to state[i][j] and state[j][i].  `old` is read from the MIRROR position state[j][i] (the state is kept
+// exactly symmetric), which the 32 lanes of a warp touch as one 128-byte segment, as do the mirror stores; the
+// row stores are one full line per lane.  Diagonal tiles hold j >= i only.
+__device__ __forceinline__ void la_finish_chunk(const DevJob& job, int tile_m, int tile_n, int q, int c, int lane, float ratio,
+                                                float one_m, float resc, uint8_t* stage) {
+  const int d = job.d;
+  const int jb = tile_n * TM + c * 32;
+  const bool diag_tile = tile_m == tile_n;
+  if (jb >= d || tile_m * TM + q * 32 >= d || (diag_tile && c < q)) return;       // warp-uniform: nothing was accumulated here
+  const int i = tile_m * TM + q * 32 + lane;
+  float* cb = job.scratch + (((int64_t)(tile_m * job.T128 + tile_n) * 16 + q * 4 + c) << 10) + (lane << 2);
+  uint32_t r[32];
+#pragma unroll
+  for (int g = 0; g < 8; ++g)
+    asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[4 * g]), "=r"(r[4 * g + 1]), "=r"(r[4 * g + 2]), "=r"(r[4 * g + 3]) : "l"(cb + g * 128) : "memory");
+#pragma unroll
+  for (int g = 0; g < 8; ++g) __stcg(reinterpret_cast<float4*>(cb + g * 128), make_float4(0.f, 0.f, 0.f, 0.f));
+  const bool row_ok = i < d;
+  const bool keep_old = resc < 0.f;                       // every capture was dropped: the average stays
+  const bool on_diag = diag_tile && c == q;               // the chunk the diagonal runs through: j >= i only
+  float* mcol = job.state + (int64_t)jb * job.ld_state + i;                      // state[jb + e][i]
+  const bool full = !on_diag && jb + 31 < d && row_ok;
+  // two halves of 16 columns: all of a half's old values are requested before the first is used (the stores
+  // below go through the same pointer, so the compiler would otherwise wait for each load in turn)
+#pragma unroll
+  for (int h = 0; h < 32; h += 16) {
+    float o[16];
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+      const int j = jb + h + e;
+      const bool ok = full || (row_ok && j < d && (!on_diag || j >= i));
+      o[e] = 0.f;
+      if (job.seed_identity) o[e] = i == j ? 1.f : 0.f;
+      else if (ok) o[e] = __ldcg(mcol + (int64_t)(h + e) * job.ld_state);
+    }
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+      const int j = jb + h + e;
+      const bool ok = full || (row_ok && j < d && (!on_diag || j >= i));
+      const float v = keep_old ? o[e] : (o[e] * ratio + __uint_as_float(r[h + e]) * resc) * one_m;
+      r[h + e] = __float_as_uint(v);
+      if (ok && job.write_state && (!diag_tile || j > i)) __stcg(mcol + (int64_t)(h + e) * job.ld_state, v);
+    }
+  }
+  // Row stores.  A lane owns a row, so a store instruction of the warp touches 32 different lines with 16 bytes
+  // each - measured at ~13 bytes per clock and SM.  With a 4 KB staging buffer (XOR-swizzled 16-byte groups,
+  // conflict-free both ways) the chunk is turned so that eight lanes write one whole 128-byte row segment.
+  const bool whole = !on_diag && jb + 31 < d;                 // warp-uniform
+  if (stage && whole && job.write_state && (job.ld_state & 3) == 0 && (((uintptr_t)job.state) & 15) == 0) {
+#pragma unroll
+    for (int g = 0; g < 8; ++g)
+      *reinterpret_cast<uint4*>(stage + lane * 128 + ((g ^ (lane & 7)) << 4)) = make_uint4(r[4 * g], r[4 * g + 1], r[4 * g + 2], r[4 * g + 3]);
+    __syncwarp();
+    const int i0 = tile_m * TM + q * 32, g = lane & 7;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int row = 4 * k + (lane >> 3);
+      const uint4 v = *reinterpret_cast<const uint4*>(stage + row * 128 + ((g ^ (row & 7)) << 4));
+      if (i0 + row < d) __stcg(reinterpret_cast<uint4*>(job.state + (int64_t)(i0 + row) * job.ld_state + jb + 4 * g), v);
+    }
+    __syncwarp();
+    if (!row_ok) return;
+  } else if (!row_ok) {
+    return;
+  } else if (job.write_state) {
+    float* srow = job.state + (int64_t)i * job.ld_state + jb;
+    if (full && (((uintptr_t)srow) & 15) == 0) {
+#pragma unroll
+      for (int g = 0; g < 8; ++g)
+        *reinterpret_cast<uint4*>(srow + 4 * g) = make_uint4(r[4 * g], r[4 * g + 1], r[4 * g + 2], r[4 * g + 3]);
+    } else {
+#pragma unroll
+      for (int e = 0; e < 32; ++e)
+        if (jb + e < d && (!on_diag || jb + e >= i)) srow[e] = __uint_as_float(r[e]);
+    }
+  }
+  if (job.tri_out) {
+    float* trow = job.tri_out + ((int64_t)i * d - ((int64_t)i * (i - 1)) / 2 - i);
+#pragma unroll
+    for (int e = 0; e < 32; ++e)
+      if (jb + e < d && jb + e >= i) trow[jb + e] = __uint_as_float(r[e]);
+  }
+}
+
+// All chunks of one completed 256 x 256 block, shared among `n_warps` warps (this one is number `w`).
+__device__ __forceinline__ void la_finish_block(const DevJob& job, const TcItem& item, int w, int n_warps, int lane, float alpha,
+                                                uint8_t* stage) {
+  const float ratio = alpha / (1.f - alpha), one_m = 1.f - alpha;
+  const float resc = job.dev_rescale ? __ldg(job.dev_rescale) : 1.f;
+  const int units = item.mi * item.nj * 16;
+  for (int u = w; u < units; u += n_warps) {
+    const int t = u >> 4, m = t / item.nj, nn = t - m * item.nj;
+    if (item.a0 == item.b0 && nn < m) continue;
+    la_finish_chunk(job, item.a0 + m, item.b0 + nn, (u >> 2) & 3, u & 3, lane, ratio, one_m, resc, stage);
+  }
+}
+
 template <bool kPair>
 __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const DevJob* __restrict__ jobs,
                                                                         const DevSegment* __restrict__ segs,
                                                                         const TcItem* __restrict__ items, int n_items, float alpha,
                                                                         const CUtensorMap* __restrict__ tmaps,
-                                                                        const int* __restrict__ cta_first) {
+                                                                        const int* __restrict__ cta_first, int* la_ctl, int la_blocks) {
   using C = Cfg<kPair>;
   constexpr int kStages = C::kStages, kStageBytes = C::kStageBytes, kSlots = C::kSlots;
   extern __shared__ uint8_t smem_raw[];
@@ -178,6 +280,7 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
   uint64_t* tfull = empty + kStages;       // [2]; the single-CTA build uses [0] only
   uint64_t* tempty = tfull + 2;            // [2]; in a pair the LEADER's copy collects both CTAs' arrivals
   uint32_t* tmem_slot = (uint32_t*)(tempty + 2);
+  int* la_bcast = (int*)(tmem_slot + 2);              // end of kernel: the completed block all warps finish next
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = kPair ? umma::cluster_ctarank() : 0u;
@@ -533,7 +636,7 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
     int stage = 0; uint32_t phase = 0;
 #ifdef KFB_SYRK_PROFILE
     // clock64 breakdown of the issuing thread's time (build this file with -DKFB_SYRK_PROFILE)
-    long long pf_tempty = 0, pf_full = 0, pf_issue = 0, pf_drain = 0, pf_items = 0, pf_stages = 0;
+    long long pf_tempty = 0, pf_full = 0, pf_issue = 0, pf_drain = 0, pf_items = 0, pf_stages = 0, pf_arrive = 0;
     long long pf_type_clk[3] = {0, 0, 0}, pf_type_units[3] = {0, 0, 0};
     const long long pf_t0 = clock64();
 #endif
@@ -551,6 +654,86 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
       const int d = job.d;
       const bool diag = item.a0 == item.b0;
       const float ratio = alpha / (1.f - alpha), one_m = 1.f - alpha;
+      // ---- finish of one 32-row x 32-column chunk whose COMPLETE sum is in r[] (thread = row i):
+      //   new = (old * alpha/(1-alpha) + w*acc) * (1-alpha)     (kfac/layers/utils.py:175-178)
+      // written to the state row, mirrored into column i (one coalesced 128-byte store per column: the 32
+      // lanes are 32 consecutive rows), and exported to the packed triangle.  Used by the fused jobs (one
+      // item holds the whole sum; a diagonal TILE then holds both of its triangles) and by the last-arriver
+      // finish of split-K jobs (upper_only on diagonal tiles: the scratch holds j >= i).
+      auto finish_chunk = [&](int i, int jb, uint32_t (&r)[32], bool diag_tile, bool upper_only, float weight, bool keep_old) {
+        const bool row_ok = i < d;
+        if (row_ok) {
+          const float* orow = job.state + (int64_t)i * job.ld_state + jb;
+          if (!job.seed_identity && jb + 31 < d && (((uintptr_t)orow) & 15) == 0) {
+            // this thread's 32 old values are one 128-byte line: eight 16-byte loads (a scalar
+            // load per value costs 32 cache wavefronts per instruction, one per lane's row)
+            float4 o[8];
+            if ((((uintptr_t)orow) & 31) == 0) {
+#pragma unroll
+              for (int g = 0; g < 8; g += 2) ldg_v8(orow + 4 * g, o[g], o[g + 1]);
+            } else {
+#pragma unroll
+              for (int g = 0; g < 8; ++g) o[g] = *reinterpret_cast<const float4*>(orow + 4 * g);
+            }
+#pragma unroll
+            for (int g = 0; g < 8; ++g) {
+              r[4 * g] = __float_as_uint(keep_old ? o[g].x : (o[g].x * ratio + __uint_as_float(r[4 * g]) * weight) * one_m);
+              r[4 * g + 1] = __float_as_uint(keep_old ? o[g].y : (o[g].y * ratio + __uint_as_float(r[4 * g + 1]) * weight) * one_m);
+              r[4 * g + 2] = __float_as_uint(keep_old ? o[g].z : (o[g].z * ratio + __uint_as_float(r[4 * g + 2]) * weight) * one_m);
+              r[4 * g + 3] = __float_as_uint(keep_old ? o[g].w : (o[g].w * ratio + __uint_as_float(r[4 * g + 3]) * weight) * one_m);
+            }
+          } else {
+#pragma unroll
+            for (int e = 0; e < 32; ++e) {
+              const int j = jb + e;
+              float old = 0.f;
+              if (j < d) old = job.seed_identity ? (i == j ? 1.f : 0.f) : orow[e];
+              r[e] = __float_as_uint(keep_old ? old : (old * ratio + __uint_as_float(r[e]) * weight) * one_m);
+            }
+          }
+          if (job.write_state && upper_only) {
+            // the block's sum was accumulated for j >= i only (split-K scratch): write that part of the row;
+            // the rest of it arrives through the mirror stores of the rows above
+            float* srow = job.state + (int64_t)i * job.ld_state + jb;
+#pragma unroll
+            for (int e = 0; e < 32; ++e)
+              if (jb + e < d && jb + e >= i) srow[e] = __uint_as_float(r[e]);
+          } else if (job.write_state) {
+            float* srow = job.state + (int64_t)i * job.ld_state + jb;
+            if (jb + 31 < d && (((uintptr_t)srow) & 31) == 0) {
+#pragma unroll
+              for (int g = 0; g < 8; g += 2)
+                stg_v8(srow + 4 * g, r[4 * g], r[4 * g + 1], r[4 * g + 2], r[4 * g + 3], r[4 * g + 4], r[4 * g + 5],
+                       r[4 * g + 6], r[4 * g + 7]);
+            } else
+#pragma unroll
+            for (int g = 0; g < 8; ++g) {
+              const int j = jb + 4 * g;
+              if (j + 3 < d) {
+                *reinterpret_cast<uint4*>(srow + 4 * g) = make_uint4(r[4 * g], r[4 * g + 1], r[4 * g + 2], r[4 * g + 3]);
+              } else {
+                for (int e = 0; e < 4; ++e)
+                  if (j + e < d) srow[4 * g + e] = __uint_as_float(r[4 * g + e]);
+              }
+            }
+          }
+          if (job.tri_out) {
+            float* trow = job.tri_out + ((int64_t)i * d - ((int64_t)i * (i - 1)) / 2 - i);
+#pragma unroll
+            for (int e = 0; e < 32; ++e) {
+              const int j = jb + e;
+              if (j < d && j >= i) trow[j] = __uint_as_float(r[e]);
+            }
+          }
+        }
+        if ((!diag_tile || upper_only) && job.write_state) {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+            const int j = jb + e;
+            if (row_ok && j < d && (!upper_only || j > i)) job.state[(int64_t)j * job.ld_state + i] = __uint_as_float(r[e]);
+          }
+        }
+      };
       if (!kPair && warp == 0) {
         if (lane == 0) {
 #ifdef KFB_SYRK_PROFILE
@@ -631,77 +814,7 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
             umma::tmem_ld_32x32(taddr + c * 32, r);
             umma::tmem_ld_wait();
             if (job.fused) {
-              // ---- fused finish: this item holds the COMPLETE sum for its block.
-              //   new = (old * alpha/(1-alpha) + w*acc) * (1-alpha)     (kfac/layers/utils.py:175-178)
-              // written to the state row (this thread owns row i), mirrored into column i (one
-              // coalesced 128-byte store per column: the 32 lanes are 32 consecutive rows), and
-              // exported to the packed triangle.  A diagonal TILE holds both of its triangles.
-              const bool diag_tile = (item.a0 + m) == (item.b0 + nn);
-              const bool row_ok = i < d;
-              if (row_ok) {
-                const float* orow = job.state + (int64_t)i * job.ld_state + jb;
-                if (!job.seed_identity && jb + 31 < d && (((uintptr_t)orow) & 15) == 0) {
-                  // this thread's 32 old values are one 128-byte line: eight 16-byte loads (a scalar
-                  // load per value costs 32 cache wavefronts per instruction, one per lane's row)
-                  float4 o[8];
-                  if ((((uintptr_t)orow) & 31) == 0) {
-#pragma unroll
-                    for (int g = 0; g < 8; g += 2) ldg_v8(orow + 4 * g, o[g], o[g + 1]);
-                  } else {
-#pragma unroll
-                    for (int g = 0; g < 8; ++g) o[g] = *reinterpret_cast<const float4*>(orow + 4 * g);
-                  }
-#pragma unroll
-                  for (int g = 0; g < 8; ++g) {
-                    r[4 * g] = __float_as_uint((o[g].x * ratio + __uint_as_float(r[4 * g]) * weight) * one_m);
-                    r[4 * g + 1] = __float_as_uint((o[g].y * ratio + __uint_as_float(r[4 * g + 1]) * weight) * one_m);
-                    r[4 * g + 2] = __float_as_uint((o[g].z * ratio + __uint_as_float(r[4 * g + 2]) * weight) * one_m);
-                    r[4 * g + 3] = __float_as_uint((o[g].w * ratio + __uint_as_float(r[4 * g + 3]) * weight) * one_m);
-                  }
-                } else {
-#pragma unroll
-                  for (int e = 0; e < 32; ++e) {
-                    const int j = jb + e;
-                    float old = 0.f;
-                    if (j < d) old = job.seed_identity ? (i == j ? 1.f : 0.f) : orow[e];
-                    r[e] = __float_as_uint((old * ratio + __uint_as_float(r[e]) * weight) * one_m);
-                  }
-                }
-                if (job.write_state) {
-                  float* srow = job.state + (int64_t)i * job.ld_state + jb;
-                  if (jb + 31 < d && (((uintptr_t)srow) & 31) == 0) {
-#pragma unroll
-                    for (int g = 0; g < 8; g += 2)
-                      stg_v8(srow + 4 * g, r[4 * g], r[4 * g + 1], r[4 * g + 2], r[4 * g + 3], r[4 * g + 4], r[4 * g + 5],
-                             r[4 * g + 6], r[4 * g + 7]);
-                  } else
-#pragma unroll
-                  for (int g = 0; g < 8; ++g) {
-                    const int j = jb + 4 * g;
-                    if (j + 3 < d) {
-                      *reinterpret_cast<uint4*>(srow + 4 * g) = make_uint4(r[4 * g], r[4 * g + 1], r[4 * g + 2], r[4 * g + 3]);
-                    } else {
-                      for (int e = 0; e < 4; ++e)
-                        if (j + e < d) srow[4 * g + e] = __uint_as_float(r[4 * g + e]);
-                    }
-                  }
-                }
-                if (job.tri_out) {
-                  float* trow = job.tri_out + ((int64_t)i * d - ((int64_t)i * (i - 1)) / 2 - i);
-#pragma unroll
-                  for (int e = 0; e < 32; ++e) {
-                    const int j = jb + e;
-                    if (j < d && j >= i) trow[j] = __uint_as_float(r[e]);
-                  }
-                }
-              }
-              if (!diag_tile && job.write_state) {
-#pragma unroll
-                for (int e = 0; e < 32; ++e) {
-                  const int j = jb + e;
-                  if (row_ok && j < d) job.state[(int64_t)j * job.ld_state + i] = __uint_as_float(r[e]);
-                }
-              }
+              finish_chunk(i, jb, r, (item.a0 + m) == (item.b0 + nn), false, weight, false);
               continue;
             }
             if (i < d && jb + 31 >= i) {
@@ -724,6 +837,29 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
           }
         }
       }
+#ifdef KFB_SYRK_PROFILE
+      const long long pla = clock64();
+#endif
+      if (!kPair && job.la) {
+        // ---- last-arriver finish (split-K jobs): every item of a 256 x 256 block counts itself in after its
+        // reds; the one that completes the block publishes it in the queue of completed blocks.  CTAs that have
+        // run out of items take blocks from that queue and finish them with all their warps (end of the kernel)
+        // - off every MMA issuer's path, and in the time the early CTAs would otherwise idle.
+        __threadfence();                                     // this thread's reds before the count
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (threadIdx.x == 0) {
+          int* cnt = job.arrive + (item.a0 >> 1) * ((job.T128 + 1) >> 1) + (item.b0 >> 1);
+          if (atomicAdd(cnt, 1) == job.la_items - 1) {
+            *cnt = 0;                                        // ready for the next update
+            __threadfence();
+            const int slot = atomicAdd(&la_ctl[0], 1);
+            atomicExch(&la_ctl[kLaCtlInts + slot], it + 1);
+          }
+        }
+      }
+#ifdef KFB_SYRK_PROFILE
+      pf_arrive += clock64() - pla;
+#endif
       umma::tc_fence_before();
 #ifdef KFB_SYRK_PROFILE
       {
@@ -746,9 +882,9 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
     }
 #ifdef KFB_SYRK_PROFILE
     if (!kPair && threadIdx.x == 0 && (blockIdx.x % 21) == 0)
-      printf("syrk cta %3d: total %lld clk, items %lld stages %lld | issuer: wait tempty %lld, wait full %lld, issue %lld | drain %lld | "
+      printf("syrk cta %3d: total %lld clk, items %lld stages %lld | issuer: wait tempty %lld, wait full %lld, issue %lld | drain %lld (arrival %lld) | "
              "clk per stage-unit: tma %.0f (%lld), staged %.0f (%lld), gather %.0f (%lld)\n",
-             blockIdx.x, clock64() - pf_t0, pf_items, pf_stages, pf_tempty, pf_full, pf_issue, pf_drain,
+             blockIdx.x, clock64() - pf_t0, pf_items, pf_stages, pf_tempty, pf_full, pf_issue, pf_drain, pf_arrive,
              pf_type_units[0] ? (double)pf_type_clk[0] / pf_type_units[0] : 0.0, pf_type_units[0],
              pf_type_units[1] ? (double)pf_type_clk[1] / pf_type_units[1] : 0.0, pf_type_units[1],
              pf_type_units[2] ? (double)pf_type_clk[2] / pf_type_units[2] : 0.0, pf_type_units[2]);
@@ -757,6 +893,49 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
 
   umma::tc_fence_before();
   __syncthreads();
+  if (!kPair && la_ctl != nullptr) {
+    // Finish completed blocks (running average + mirror) for as long as the queue holds any: never waits for a
+    // block that is not complete yet - whoever completes it later drains the queue after its own items, so the
+    // last CTA to get here leaves it empty.  The stage ring is free by now: 4 KB of it per warp turn the chunks.
+#ifdef KFB_SYRK_PROFILE
+    const long long pf0 = clock64();
+    int pf_n = 0;
+#endif
+    for (;;) {
+      if (threadIdx.x == 0) {
+        int got = -1;
+        for (;;) {
+          const int popped = *(volatile int*)&la_ctl[1], pushed = *(volatile int*)&la_ctl[0];
+          if (popped >= pushed) break;
+          if (atomicCAS(&la_ctl[1], popped, popped + 1) != popped) continue;
+          volatile int* slot = la_ctl + kLaCtlInts + popped;
+          while ((got = *slot) == 0) __nanosleep(64);        // its publisher is between two instructions
+          *slot = 0;                                         // empty for the next update
+          got -= 1;
+          __threadfence();
+          break;
+        }
+        *la_bcast = got;
+      }
+      __syncthreads();
+      const int got = *la_bcast;
+      __syncthreads();
+      if (got < 0) break;
+      const TcItem item = items[got];
+      la_finish_block(jobs[item.job], item, warp, C::kThreads / 32, lane, alpha, smem + warp * 4096);
+#ifdef KFB_SYRK_PROFILE
+      ++pf_n;
+#endif
+    }
+    // the last CTA out resets the queue's counters (every push and pop of this launch has happened by then)
+    if (threadIdx.x == 0) {
+      __threadfence();
+      if (atomicAdd(&la_ctl[2], 1) == (int)gridDim.x - 1) { la_ctl[0] = 0; la_ctl[1] = 0; la_ctl[2] = 0; }
+    }
+#ifdef KFB_SYRK_PROFILE
+    if (threadIdx.x == 0 && (blockIdx.x % 21) == 0) printf("syrk cta %3d: finished %d blocks in %lld clk\n", blockIdx.x, pf_n, clock64() - pf0);
+#endif
+  }
   if (kPair) {
     umma::cluster_sync_all();                 // the peer may still be signalling this CTA's barriers
     if (warp == 4) {
@@ -801,6 +980,7 @@ void plan_syrk_tc(FactorPlan* plan, int num_sms) {
       const bool whole = j.fused || (stream_k && !pair);      // one unit per block; cut later
       const int64_t nch = whole ? 1 : std::max<int64_t>(1, ceil_div64(K, kChunk));
       const int64_t len = ceil_div64(ceil_div64(K, nch), BK) * BK;
+      if (j.la) plan->jobs[ji].la_items += (int)ceil_div64(K, len);     // arrivals every block waits for
       for (int bi = 0; bi < TB; ++bi)
         for (int bj = bi; bj < TB; ++bj)
           for (int64_t k = 0; k < K; k += len) {
@@ -901,7 +1081,7 @@ int launch_syrk_tc(const FactorPlan& plan, void* workspace, Context* ctx, float 
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    KFB_CUDA(cudaLaunchKernelEx(&cfg, syrk_tc_kernel<true>, jobs, segs, items, n_pair, alpha, tmaps, (const int*)nullptr));
+    KFB_CUDA(cudaLaunchKernelEx(&cfg, syrk_tc_kernel<true>, jobs, segs, items, n_pair, alpha, tmaps, (const int*)nullptr, (int*)nullptr, 0));
     count_launch();
   }
   if (n_single > 0) {
@@ -909,11 +1089,12 @@ int launch_syrk_tc(const FactorPlan& plan, void* workspace, Context* ctx, float 
       // stream-K shares: one CTA per share (cta_first indexes the whole item array)
       const int grid = (int)plan.cta_first.size() - 1;
       syrk_tc_kernel<false><<<grid, Cfg<false>::kThreads, Cfg<false>::kSmemBytes, stream>>>(jobs, segs, items, n_pair + n_single, alpha,
-                                                                                           tmaps, cta_first);
+                                                                                           tmaps, cta_first, (int*)nullptr, 0);
     } else {
       const int grid = std::min(n_single, ctx->num_sms);
+      int* la_ctl = plan.la_blocks > 0 ? (int*)((float*)(ws + plan.off_scratch) + plan.la_ctl_off) : nullptr;
       syrk_tc_kernel<false><<<grid, Cfg<false>::kThreads, Cfg<false>::kSmemBytes, stream>>>(jobs, segs, items + n_pair, n_single, alpha,
-                                                                                           tmaps, (const int*)nullptr);
+                                                                                           tmaps, (const int*)nullptr, la_ctl, plan.la_blocks);
     }
     KFB_CHECK_LAUNCH();
   }

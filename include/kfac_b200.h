@@ -148,6 +148,17 @@ KFB_API size_t kfb_factor_workspace_bytes(const kfb_factor_job* jobs, int32_t n_
 KFB_API int kfb_factor_update(const kfb_factor_job* jobs, int32_t n_jobs, float alpha,
                       void* workspace, size_t workspace_bytes, void* stream);
 
+/* Split-K jobs accumulate into the workspace and are finished (scale, running average, mirror:
+ * kfac/layers/utils.py:164-178) inside the SYRK by whichever work item of a 256 x 256 block arrives last;
+ * that item also re-zeroes the block's accumulator and its arrival counter.  A caller that uses a
+ * workspace for kfb_factor_update ONLY can say so: the library then relies on what it left there and
+ * skips the per-call clear of those accumulators when the same set of jobs (same shapes) comes again on
+ * a stream ordered after the previous call.  Anything else writing into a dedicated workspace between
+ * two updates corrupts the second.  `release` withdraws the promise (call it before freeing the
+ * memory).  Neither call touches the device. */
+KFB_API int kfb_factor_workspace_dedicate(void* workspace, size_t workspace_bytes);
+KFB_API int kfb_factor_workspace_release(void* workspace);
+
 /* kfb_factor_update for callers that cannot allocate device memory.  No counterpart in the
  * reference (which allocates freely through torch); it exists for hosts that own all GPU memory
  * themselves or that may not call cudaMalloc once running.  Same jobs, same results, but the

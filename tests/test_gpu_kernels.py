@@ -216,6 +216,79 @@ def test_stream_k_schedule_matches_default(monkeypatch):
             assert_factor_close(st, ref)
 
 
+def test_last_arriver_finish_repeats_and_matches_finalize(monkeypatch):
+    """Split-K jobs are finished inside the SYRK by the last K chunk of each 256 x 256 block to arrive, which
+    also re-zeroes the block's accumulator and counter.  The factor workspace of CudaOps is dedicated, so from
+    the second update on the library clears nothing itself: four updates in a row (running averages chained,
+    packed triangles exported) must each give the oracle's factor, a caller-supplied undedicated workspace
+    full of garbage must too, and KFB_SYRK_LAST_ARRIVER=0 (scratch + finalize_kernel) must agree."""
+    N.set_ops(None)
+    o = N.get_ops()
+    o._enter(torch.zeros(1, device=DEV))
+    o.set_mma_mode(1)
+    gen = torch.Generator().manual_seed(77)
+    # long-K single segment (several chunks), two segments, 300 = ragged 128-tiles, 64x64 map = TMA-fed
+    xs = [torch.randn(10, 64, 28, 28, generator=gen)]                       # im2col 3x3: d = 576, K = 7840
+    gs = [torch.randn(24, 300, 14, 14, generator=gen), torch.randn(3, 130, 64, 64, generator=gen)]
+    g_two = [torch.randn(9, 96, 28, 28, generator=gen), torch.randn(5, 96, 28, 28, generator=gen)]
+
+    def build(states, tris):
+        jobs = []
+        for x in xs:
+            d, segs = conv_segments(x, (3, 3), (1, 1), (1, 1), True)
+            jobs.append((d, segs))
+        for g in gs:
+            n, c, h, w = g.shape
+            S = h * w
+            jobs.append((c, [N.Segment(N.KFB_SEG_NCHW, g.to(DEV), n, c, 1.0 / (S * S * n * S), h=h, w=w)]))
+        S = 28 * 28
+        wgt = 1.0 / (S * S * 14 * S)
+        jobs.append((96, [N.Segment(N.KFB_SEG_NCHW, g.to(DEV), g.shape[0], 96, wgt, h=28, w=28) for g in g_two]))
+        return [N.FactorJob(d, segs, st, False, True, tri) for (d, segs), st, tri in zip(jobs, states, tris)]
+
+    raw = [O.conv2d_A([x], (3, 3), (1, 1), (1, 1), True) for x in xs] + [O.conv2d_G([g]) for g in gs]
+    raw.append(O.conv2d_G(g_two))
+    dims = [r.shape[0] for r in raw]
+    results = {}
+    for env in ('1', '0'):
+        monkeypatch.setenv('KFB_SYRK_LAST_ARRIVER', env)
+        states = [alloc2d(d, d, DEV)[1] for d in dims]
+        tris = [torch.full((d * (d + 1) // 2,), float('nan'), device=DEV) for d in dims]
+        for st in states:
+            st.copy_(torch.eye(st.shape[0]))
+        refs = [torch.eye(d, dtype=torch.float64) for d in dims]
+        jobs = build(states, tris)
+        for step in range(4):
+            o.factor_update(jobs, 0.9)
+            torch.cuda.synchronize()
+            refs = [O.factor_ema(r, ref.float(), 0.9).double() for r, ref in zip(raw, refs)]
+            for st, tri, ref in zip(states, tris, refs):
+                assert_factor_close(st, ref.float())
+                assert torch.equal(tri.cpu(), triu_pack(st.cpu()))
+        results[env] = [st.clone() for st in states]
+    for a, b in zip(results['1'], results['0']):
+        assert_factor_close(a, b, tol=1e-5)
+    # an ordinary (undedicated) workspace holding garbage: cleared by the call itself
+    monkeypatch.setenv('KFB_SYRK_LAST_ARRIVER', '1')
+    states = [alloc2d(d, d, DEV)[1] for d in dims]
+    for st in states:
+        st.copy_(torch.eye(st.shape[0]))
+    jobs = build(states, [None] * len(dims))
+    cjobs, keep = o._factor_cjobs(jobs)
+    nbytes = o.lib.kfb_factor_workspace_bytes(cjobs, len(jobs))
+    ws = torch.full((nbytes,), 0x7f, dtype=torch.uint8, device=DEV)
+    for step in range(2):
+        o._call('kfb_factor_update', cjobs, len(jobs), 0.9, ws.data_ptr(), ws.numel(),
+                torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        ws[nbytes // 2:].fill_(0x55)            # someone else scribbles on it between the calls
+    refs = [torch.eye(d) for d in dims]
+    for step in range(2):
+        refs = [O.factor_ema(r, ref, 0.9) for r, ref in zip(raw, refs)]
+    for st, ref in zip(states, refs):
+        assert_factor_close(st, ref)
+
+
 def test_nchw_tma_and_gather_paths_agree(monkeypatch):
     """fp32 NCHW operands with 16-byte image rows are fetched by TMA (per-image 32-row blocks, tail
     zero-filled); KFB_SYRK_TMA=0 and a capture that is not 16-byte aligned use the gathering
