@@ -702,7 +702,8 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
     if (dj.la) { dj.scratch_off += plan->la_begin; dj.arrive_off += plan->la_begin; }
   // the queue of completed blocks: [pushed, popped, CTAs gone, ...][la_blocks slots]
   plan->la_ctl_off = plan->la_begin + la_floats;
-  if (plan->la_blocks > 0) la_floats += align_up((size_t)kLaCtlInts + plan->la_blocks, 64);
+  plan->la_ctl = allow_tc && last_arriver_mode() && !stream_k_mode();
+  if (plan->la_ctl) la_floats += align_up((size_t)kLaCtlInts + plan->la_blocks, 64);
   plan->scratch_floats += la_floats;
   static uint64_t generation = 0;
   plan->generation = ++generation;

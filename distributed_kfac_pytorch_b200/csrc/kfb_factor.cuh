@@ -139,6 +139,7 @@ struct FactorPlan {
   size_t la_begin = 0;                   // float offset of the second part: left zero by the kernel itself
   size_t la_ctl_off = 0;                 // float offset of the completed-block queue inside the scratch region
   int la_blocks = 0;                     // 256 x 256 blocks of all last-arriver jobs
+  bool la_ctl = false;                   // the control block exists: dynamic item hand-out + completed-block queue
   uint64_t generation = 0;               // bumped whenever the plan is rebuilt (the layout may have moved)
   size_t off_jobs = 0, off_segs = 0, off_items = 0, off_fin = 0, off_scratch = 0, total_bytes = 0;
 };
@@ -151,7 +152,7 @@ KFB_HIDDEN void bind_workspace(FactorPlan* plan, void* workspace);
 KFB_HIDDEN int launch_pad(const FactorPlan& plan, void* workspace, cudaStream_t stream);
 KFB_HIDDEN int launch_syrk_simt(const FactorPlan& plan, void* workspace, cudaStream_t stream);
 KFB_HIDDEN int launch_syrk(const FactorPlan& plan, void* workspace, Context* ctx, float alpha, cudaStream_t stream);
-constexpr int kLaCtlInts = 64;            // control words in front of the completed-block queue
+constexpr int kLaCtlInts = 64;            // control words [pushed, popped, CTAs gone, items handed out] in front of the completed-block queue
 constexpr int64_t kFusedMaxRows = 4096;   // jobs with at most this many rows of X are never split along K
 KFB_HIDDEN int factor_update_with(const kfb_factor_job* jobs, int n_jobs, float alpha, Context* ctx, void* workspace,
                                   size_t workspace_bytes, const char* what, cudaStream_t stream);

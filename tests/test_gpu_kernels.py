@@ -197,8 +197,8 @@ def test_stream_k_schedule_matches_default(monkeypatch):
     gs = [torch.randn(24, 260, 14, 14, generator=gen), torch.randn(2, 16, 56, 56, generator=gen)]
     refs = [O.factor_ema(O.conv2d_A([x], (3, 3), (1, 1), (1, 1), False), None, 0.95) for x in xs]
     refs += [O.factor_ema(O.conv2d_G([g]), None, 0.95) for g in gs]
-    for env in ('1', '0'):
-        monkeypatch.setenv('KFB_SYRK_STREAMK', env)
+    for name, env in (('KFB_SYRK_STREAMK', '1'), ('KFB_SYRK_STREAMK', '0'), ('KFB_SYRK_DYNAMIC', '1')):
+        monkeypatch.setenv(name, env)     # the last round: CTAs claim items from a shared counter
         jobs, states = [], []
         for x in xs:
             d, segs = conv_segments(x, (3, 3), (1, 1), (1, 1), False)
