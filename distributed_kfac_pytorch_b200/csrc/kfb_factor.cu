@@ -404,6 +404,34 @@ __device__ __forceinline__ void pad_transpose(const PadJob& p, uint32_t e0) {
   *reinterpret_cast<float4*>(p.dst + e0) = make_float4(v[0], v[1], v[2], v[3]);     // wp % 4 == 0
 }
 
+// Variant 5: dst[c][k] = src[k][c] for a row-major capture (Linear layers: h = features, w = pitch, hp = rows,
+// wp = rows rounded up to 32), plus a row of ones (bias) when channels = h + 1; k >= rows is zero.  One 32 x 32
+// tile per block through shared memory: reads run along the features, writes along k.
+template <typename T>
+__device__ __forceinline__ void pad_rows(const PadJob& p, int b) {
+  __shared__ float tile[32][33];
+  const int tiles_k = (int)p.quads;
+  const int c0 = (b / tiles_k) * 32, k0 = (b % tiles_k) * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const T* src = reinterpret_cast<const T*>(p.src);
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int k = k0 + ty + 8 * r, c = c0 + tx;
+    float v = 0.f;
+    if (k < p.hp) {
+      if (c < p.h) v = pad_load(src + (size_t)k * p.w + c, p.dtype);
+      else if (c < p.channels) v = 1.f;
+    }
+    tile[ty + 8 * r][tx] = v;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int c = c0 + ty + 8 * r;
+    if (c < p.channels) p.dst[(size_t)c * p.wp + k0 + tx] = tile[tx][ty + 8 * r];
+  }
+}
+
 // Staging copies for the tensor-core SYRK (PadJob).  HBM-bound: reads the capture once, writes kw x
 // (about) its size.
 __global__ void __launch_bounds__(256) pad_kernel(const PadJob* __restrict__ pads, const int* __restrict__ start, int n_pads) {
@@ -415,6 +443,10 @@ __global__ void __launch_bounds__(256) pad_kernel(const PadJob* __restrict__ pad
   const PadJob& p = pads[lo];
   const uint32_t t = (uint32_t)(blockIdx.x - start[lo]) * 256 + threadIdx.x;
   const bool f32 = p.dtype == KFB_F32;
+  if (p.variant == 5) {                         // block-uniform
+    if (f32) pad_rows<float>(p, blockIdx.x - start[lo]); else pad_rows<unsigned short>(p, blockIdx.x - start[lo]);
+    return;
+  }
   if (p.variant == 0 || p.variant == 4) {
     const uint32_t e0 = t * 4;
     if (e0 >= (uint32_t)p.total) return;
@@ -462,6 +494,11 @@ static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 // KFB_SYRK_LAST_ARRIVER=0: split-K jobs go back to scratch + finalize_kernel
 static int last_arriver_mode() {
   const char* e = getenv("KFB_SYRK_LAST_ARRIVER");
+  return e ? atoi(e) : 1;
+}
+// KFB_SYRK_ROWS_TC=0: Linear-layer captures go back to the SIMT SYRK
+static int rows_tc_mode() {
+  const char* e = getenv("KFB_SYRK_ROWS_TC");
   return e ? atoi(e) : 1;
 }
 static int stream_k_mode() {
@@ -548,7 +585,12 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
       KFB_REQUIRE(feat == j.d, "factor job %d segment %d: feature count %d != d %d", ji, si, feat, j.d);
       k_total += ds.K;
       KFB_REQUIRE(ds.K < ((int64_t)1 << 31), "segment has %lld rows; at most 2^31-1 are supported", (long long)ds.K);
-      if (s.kind == KFB_SEG_ROWS) tc = false;
+      // row-major captures (Linear layers) reach the tensor-core SYRK through a transposed fp32 copy (PadJob
+      // variant 5) that TMA reads like a one-image NCHW capture
+      if (s.kind == KFB_SEG_ROWS &&
+          !(stage_mode() && tma_mode() && rows_tc_mode() && s.ld < ((int64_t)1 << 31) &&
+            (int64_t)feat * ((s.n + 31) / 32 * 32) < ((int64_t)1 << 31)))
+        tc = false;
       if (s.c * s.h * s.w >= ((int64_t)1 << 26)) tc = false;   // packed row offsets hold 26 bits
       ds.tma = -1;
       ds.nb = 0;
@@ -626,6 +668,27 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
           magic_div(ds.ow, &ds.mul_w, &ds.sh_w);
           aligned = true;       // staging copies start on 256-byte boundaries
         }
+      }
+      if (ds.kind == KFB_SEG_ROWS) {
+        // X (rows x features, any pitch, any type) -> fp32 [features (+ a row of ones for the bias)][Kp], Kp = rows
+        // rounded up to 32 and zero-filled: from here on a plain NCHW segment of one "image" of Kp "pixels"
+        const int64_t Kp = (ds.K + 31) / 32 * 32;
+        const int C = ds.c + (ds.has_bias ? 1 : 0);
+        PadJob pj;
+        memset(&pj, 0, sizeof(pj));
+        pj.src = ds.data; pj.dtype = ds.dtype; pj.variant = 5;
+        pj.channels = C; pj.h = ds.c; pj.w = (int)ds.ld; pj.hp = (int)ds.K; pj.wp = (int)Kp; pj.kw = 1;
+        pj.quads = Kp / 32;                                   // 32 x 32 tiles along K
+        pj.total = (int64_t)C * Kp;
+        plan->seg_pad.back() = (int)plan->pads.size();
+        plan->pad_off.push_back(plan->stage_floats);
+        plan->stage_floats += align_up((size_t)pj.total, 64);
+        plan->pads.push_back(pj);
+        ds.kind = KFB_SEG_NCHW; ds.dtype = KFB_F32; ds.has_bias = 0;
+        ds.c = C; ds.h = 1; ds.w = (int)Kp; ds.oh = 1; ds.ow = (int)Kp; ds.K = Kp; ds.ld = 0;
+        magic_div(ds.K, &ds.mul_s, &ds.sh_s);
+        magic_div(ds.ow, &ds.mul_w, &ds.sh_w);
+        aligned = true;
       }
       {
         // NCHW operands TMA cannot take as they are: stage an fp32 [channels][images * padded pixels]
@@ -725,7 +788,8 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
   int pad_blocks = 0;
   for (const PadJob& pj : plan->pads) {
     plan->pad_start.push_back(pad_blocks);
-    pad_blocks += (int)((pj.variant >= 1 && pj.variant <= 3) ? ceil_div64(pj.quads, 256) : ceil_div64(pj.total, 1024));
+    pad_blocks += (int)(pj.variant == 5 ? pj.quads * ceil_div(pj.channels, 32)
+                        : (pj.variant >= 1 && pj.variant <= 3) ? ceil_div64(pj.quads, 256) : ceil_div64(pj.total, 1024));
   }
   plan->pad_start.push_back(pad_blocks);
   plan->off_pads = off;      off = align_up(off + plan->pads.size() * sizeof(PadJob), 256);
@@ -748,7 +812,7 @@ std::vector<int64_t> g_plan_sig;
 
 void signature(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool tc, std::vector<int64_t>* sig) {
   sig->clear();
-  sig->push_back(n_jobs); sig->push_back(num_sms); sig->push_back(tc); sig->push_back(tma_mode()); sig->push_back(stage_mode()); sig->push_back(syrk_pair_mode()); sig->push_back(fused_max_rows()); sig->push_back(stream_k_mode()); sig->push_back(last_arriver_mode());
+  sig->push_back(n_jobs); sig->push_back(num_sms); sig->push_back(tc); sig->push_back(tma_mode()); sig->push_back(stage_mode()); sig->push_back(syrk_pair_mode()); sig->push_back(fused_max_rows()); sig->push_back(stream_k_mode()); sig->push_back(last_arriver_mode()); sig->push_back(rows_tc_mode());
   for (int i = 0; i < n_jobs; ++i) {
     const kfb_factor_job& j = jobs[i];
     sig->push_back(j.d); sig->push_back(j.n_segments); sig->push_back(j.ld_state);

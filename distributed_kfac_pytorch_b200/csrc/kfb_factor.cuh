@@ -99,8 +99,9 @@ struct PadJob {
   int variant;           // 0: one thread per 4 output floats; 1: (sx,kw) = (1,3), 2: (2,3), 3: (2,7): one thread
                          // reads a source row segment once and writes the 4-pixel group of all kw planes;
                          // 4: NCHW capture -> [channels][images * wp] (see below)
+                         // 5: row-major capture -> [features (+ ones)][rows rounded up to 32] (pad_rows)
   int channels;          // variant 4
-  int64_t quads;         // variants 1-3: planes * hp * wp/4 threads
+  int64_t quads;         // variants 1-3: planes * hp * wp/4 threads; variant 5: 32-row tiles along K
   int64_t total;         // planes * kw * hp * wp (< 2^31)
 };
 

@@ -677,8 +677,10 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
       // device-side multiplier of the segment weight (AMP unscale; 0 = capture dropped, kfb_capture_filter)
       const float* dscale = segs[item.seg].dev_scale;
       const float dmul = dscale ? __ldg(dscale) : 1.f;
-      const bool dropped = dmul == 0.f;                   // warp-uniform: skip every write of this item
-      const float weight = segs[item.seg].weight * dmul;
+      // a fused job has no finish pass to apply its rescale (< 0: no capture survived, keep the state)
+      const float fresc = (job.fused && job.dev_rescale) ? __ldg(job.dev_rescale) : 1.f;
+      const bool dropped = dmul == 0.f || fresc < 0.f;    // warp-uniform: skip every write of this item
+      const float weight = segs[item.seg].weight * dmul * fresc;
       const int d = job.d;
       const bool diag = item.a0 == item.b0;
       const float ratio = alpha / (1.f - alpha), one_m = 1.f - alpha;

@@ -335,6 +335,36 @@ def test_linear_factor_rows(ops, rows, feat, bias):
     assert_factor_close(state, O.factor_ema(O.linear_A([a], bias), None, 0.95))
 
 
+def test_linear_rows_tensor_core_and_simt_paths_agree(monkeypatch):
+    """Row-major (Linear) captures reach the tcgen05 SYRK through a transposed fp32 staging copy
+    (pad_kernel variant 5, bias = a row of ones); KFB_SYRK_ROWS_TC=0 keeps them on the SIMT kernel.
+    Long K (split into chunks, finished by the last arriver), ragged sizes, a pitch, 16-bit rows."""
+    N.set_ops(None)
+    o = N.get_ops()
+    o._enter(torch.zeros(1, device=DEV))
+    o.set_mma_mode(1)
+    gen = torch.Generator().manual_seed(8)
+    cases = [(20000, 300, True, torch.float32), (700, 651, True, torch.float32), (33, 130, False, torch.float16),
+             (5, 7, True, torch.float32), (9000, 64, False, torch.bfloat16)]
+    for rows, feat, bias, dtype in cases:
+        wide = torch.randn(rows, feat + 3, generator=gen).to(dtype)
+        x = wide.to(DEV)[:, :feat]                                       # pitch feat + 3
+        d = feat + int(bias)
+        ref = O.factor_ema(O.linear_A([wide[:, :feat].float()], bias), None, 0.95)
+        got = {}
+        for env in ('1', '0'):
+            monkeypatch.setenv('KFB_SYRK_ROWS_TC', env)
+            seg = N.Segment(N.KFB_SEG_ROWS, x, rows, feat, 1.0 / rows, has_bias=bias, ld=feat + 3)
+            buf, state = alloc2d(d, d, DEV)
+            tri = torch.full((d * (d + 1) // 2,), float('nan'), device=DEV)
+            o.factor_update([N.FactorJob(d, [seg], state, True, True, tri)], 0.95)
+            torch.cuda.synchronize()
+            assert_factor_close(state, ref)
+            assert torch.equal(tri.cpu(), triu_pack(state.cpu()))
+            got[env] = state.clone()
+        assert_factor_close(got['1'], got['0'])
+
+
 @pytest.mark.parametrize('dtype', [torch.float16, torch.bfloat16], ids=['fp16', 'bf16'])
 def test_half_precision_captures(ops, dtype):
     """AMP captures (fp16 / bf16) are read natively: same factor as for the widened fp32 copy."""
@@ -637,7 +667,7 @@ def test_capture_filter_and_16bit_round_trip(ops):
     _, st = alloc2d(6, 6, DEV, zero=True)
     ops.factor_update([N.FactorJob(6, [seg_ok, seg_bad], st, False, True, None)], 0.5)
     ref = 0.5 * (0.25 / 16.0) * (x.t() @ x)
-    torch.testing.assert_close(st, ref, rtol=1e-5, atol=1e-7)
+    assert_factor_close(st, ref)      # row-major captures run in TF32 on the tensor-core path
     st2 = torch.full((6, 8), 3.0, device=DEV)[:, :6]
     job = N.FactorJob(6, [seg_ok], st2, False, True, None)
     job.dev_rescale = skip

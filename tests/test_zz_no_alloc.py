@@ -80,10 +80,11 @@ def test_static_scratch_rejects_oversized_jobs():
     ops._enter(torch.zeros(1, device=DEV))
     limit = ops.static_scratch_bytes()
     assert limit == 16 << 20
-    d = 2304                                  # 2304^2 fp32 accumulators = 21 MB > 16 MiB
-    x = torch.randn(64, d, device=DEV)
+    d = 2304                                  # 2304^2 fp32 split-K accumulators = 21 MB > 16 MiB
+    rows = 5000                               # more rows than one work item takes: the job is split along K
+    x = torch.randn(rows, d, device=DEV)
     _, st = alloc2d(d, d, DEV, zero=True)
-    job = N.FactorJob(d, [N.Segment(N.KFB_SEG_ROWS, x, 64, d, 1.0 / 64, ld=d)], st, True, True, None)
+    job = N.FactorJob(d, [N.Segment(N.KFB_SEG_ROWS, x, rows, d, 1.0 / rows, ld=d)], st, True, True, None)
     with pytest.raises(N.NativeError, match=r'need \d+ bytes of scratch but the built-in array holds %d' % limit):
         ops.factor_update_static([job], 0.9)
     torch.cuda.synchronize()
