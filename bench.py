@@ -643,26 +643,23 @@ def run_e2e(args, pre, caps, grads, device, dist_on):
     dev_caps = [caps, [([torch.empty_like(t) for t in a], [torch.empty_like(t) for t in g]) for a, g in caps]]
     dev_grads = [[(torch.empty_like(w), None if b is None else torch.empty_like(b)) for w, b in grads] for _ in range(2)]
     dev_out = [(torch.empty_like(w), None if b is None else torch.empty_like(b)) for w, b in grads]
-    h2d_stream, d2h_stream = torch.cuda.Stream(device), torch.cuda.Stream(device)
-    ready = [torch.cuda.Event(), torch.cuda.Event()]      # inputs of buffer set k have landed
+    h2d_stream, d2h_stream, caps_stream = torch.cuda.Stream(device), torch.cuda.Stream(device), torch.cuda.Stream(device)
+    ready = [torch.cuda.Event(), torch.cuda.Event()]      # gradients of buffer set k have landed
     consumed = [torch.cuda.Event(), torch.cuda.Event()]   # the step reading buffer set k has finished with it
+    caps_ready = [torch.cuda.Event(), torch.cuda.Event()]     # the same for the captures, which only factor
+    caps_consumed = [torch.cuda.Event(), torch.cuda.Event()]  # steps read: set (step // factor_update_freq) & 1
     drained = torch.cuda.Event()                          # dev_out has been copied to the host
     h2d = [0]
     main = torch.cuda.current_stream(device)
-    for e in consumed:
+    freq = pre.param_groups[0]['factor_update_freq']
+    for e in consumed + caps_consumed:
         e.record(main)
     drained.record(main)
 
     def upload(step_index, k):
-        """Queue the H2D copies of the inputs of K-FAC step number `step_index` into buffer set k."""
-        factor_step = step_index % pre.param_groups[0]['factor_update_freq'] == 0
+        """Queue the H2D copies of the gradients of K-FAC step number `step_index` into buffer set k."""
         with torch.cuda.stream(h2d_stream):
             h2d_stream.wait_event(consumed[k])
-            if factor_step:
-                for (a, g), (ha, hg) in zip(dev_caps[k], host_caps):
-                    for d, h in zip(a + g, ha + hg):
-                        d.copy_(h, non_blocking=True)
-                h2d[0] += bytes_caps
             for (dw, db), (hw, hb) in zip(dev_grads[k], host_grads):
                 dw.copy_(hw, non_blocking=True)
                 if db is not None:
@@ -670,20 +667,48 @@ def run_e2e(args, pre, caps, grads, device, dist_on):
             h2d[0] += bytes_grads
             ready[k].record(h2d_stream)
 
-    def run(n_steps):
+    def upload_caps(step_index):
+        """Queue the H2D copies of the captures of factor step `step_index` (2.8 GB for ResNet-50: ~50 ms of
+        PCIe time).  Issued as soon as the previous factor step has been queued, i.e. one factor period ahead,
+        so that it overlaps the steps in between instead of the single ordinary step before it."""
+        kc = (step_index // freq) & 1
+        with torch.cuda.stream(caps_stream):
+            caps_stream.wait_event(caps_consumed[kc])
+            for (a, g), (ha, hg) in zip(dev_caps[kc], host_caps):
+                for d, h in zip(a + g, ha + hg):
+                    d.copy_(h, non_blocking=True)
+            h2d[0] += bytes_caps
+            caps_ready[kc].record(caps_stream)
+
+    def run(n_steps, trace=None):
         first_index = pre.param_groups[0]['step']
+        last = first_index + n_steps
         upload(first_index, first_index & 1)
-        for i in range(first_index, first_index + n_steps):
+        first_factor = (first_index + freq - 1) // freq * freq
+        if first_factor < last:
+            upload_caps(first_factor)
+        for i in range(first_index, last):
             k = i & 1
-            if i + 1 < first_index + n_steps:
+            if i + 1 < last:
                 upload(i + 1, (i + 1) & 1)          # overlaps with this step's kernels
             main.wait_event(ready[k])
             for l, (dw, db) in zip(pre.layers, dev_grads[k]):
                 l.module.weight.grad.copy_(dw)      # K-FAC rewrites .grad in place: hand it this step's gradients
                 if db is not None:
                     l.module.bias.grad.copy_(db)
-            feed(pre, dev_caps[k])
+            if i % freq == 0:
+                kc = (i // freq) & 1
+                main.wait_event(caps_ready[kc])
+                feed(pre, dev_caps[kc])
+                if i + freq < last:
+                    upload_caps(i + freq)           # the next factor step's captures: a whole period to land
             pre.step()
+            if i % freq == 0:
+                caps_consumed[(i // freq) & 1].record(main)
+            if trace is not None:
+                ev = torch.cuda.Event(enable_timing=True)
+                ev.record(main)
+                trace.append(ev)
             main.wait_event(drained)
             for l, (ow, ob) in zip(pre.layers, dev_out):
                 ow.copy_(l.module.weight.grad)
@@ -707,14 +732,19 @@ def run_e2e(args, pre, caps, grads, device, dist_on):
     barrier_sync(dist_on)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    run(args.steps)
+    trace = []
+    run(args.steps, trace)
     e1.record()
     barrier_sync(dist_on)
     ms = max_over_ranks(e0.elapsed_time(e1), device, dist_on)
+    marks = [e0] + trace
+    per_step = [round(marks[i].elapsed_time(marks[i + 1]), 2) for i in range(len(trace))]
     return {'value': ms / args.steps, 'unit': 'ms/step', 'h2d_bytes_per_step': h2d[0] // args.steps,
+            'per_step_ms_rank0': per_step,
             'd2h_bytes_per_step': bytes_grads + 4,
             'api': 'KFAC.step() with pinned-host activations/gradients in, rewritten gradients out; copies of step '
-                   'i+1 / i-1 overlap the kernels of step i on side streams (double-buffered inputs)'}
+                   'i+1 / i-1 overlap the kernels of step i on side streams (double-buffered inputs; the captures, which '
+                   'only factor steps read, are uploaded one factor period ahead)'}
 
 
 def run_train(args, model, pre, x, y, device, dist_on, world):
