@@ -268,6 +268,24 @@ def test_last_arriver_finish_repeats_and_matches_finalize(monkeypatch):
         results[env] = [st.clone() for st in states]
     for a, b in zip(results['1'], results['0']):
         assert_factor_close(a, b, tol=1e-5)
+    # write_state = False: only the packed triangle receives the new average, the state stays as it was
+    monkeypatch.setenv('KFB_SYRK_LAST_ARRIVER', '1')
+    g = gs[0]
+    n, c, h, w = g.shape
+    S = h * w
+    seg = N.Segment(N.KFB_SEG_NCHW, g.to(DEV), n, c, 1.0 / (S * S * n * S), h=h, w=w)
+    st = alloc2d(c, c, DEV)[1]
+    st.copy_(torch.eye(c))
+    tri = torch.full((c * (c + 1) // 2,), float('nan'), device=DEV)
+    o.factor_update([N.FactorJob(c, [seg], st, False, False, tri)], 0.9)
+    torch.cuda.synchronize()
+    assert torch.equal(st.cpu(), torch.eye(c))
+    want = O.factor_ema(raw[1], torch.eye(c), 0.9)
+    full = torch.zeros(c, c)
+    iu = torch.triu_indices(c, c)
+    full[iu[0], iu[1]] = tri.cpu()
+    full = full + full.triu(1).t()
+    assert_factor_close(full, want)
     # an ordinary (undedicated) workspace holding garbage: cleared by the call itself
     monkeypatch.setenv('KFB_SYRK_LAST_ARRIVER', '1')
     states = [alloc2d(d, d, DEV)[1] for d in dims]
