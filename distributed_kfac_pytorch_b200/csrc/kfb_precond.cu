@@ -95,7 +95,10 @@ struct GradJob {
 };
 constexpr int kGradBatch = 512;
 typedef Batch<GradJob, kGradBatch> GradBatch;
-constexpr int kElemsPerBlock = 8192;     // 32 KB read + 32 KB written per block: eight 16-byte accesses per thread in flight
+constexpr int kElemsPerBlock = 8192;     // write-back: 32 KB read + 32 KB written per block, eight 16-byte accesses per thread in flight
+// pack / dot touch a few small layers (conv1 and fc in a ResNet: 2 M elements): small blocks so that the
+// handful of layers still spreads over every SM
+template <int kMode> struct GradBlock { static constexpr int kElems = kMode == 2 ? kElemsPerBlock : 2048; };
 
 enum { kPack = 0, kDot = 1, kWrite = 2 };
 
@@ -106,7 +109,8 @@ __global__ void __launch_bounds__(256) grad_kernel(const __grid_constant__ GradB
   const int jidx = find_job(batch, blockIdx.x);
   const GradJob j = batch.jobs[jidx];
   const int64_t total = (int64_t)j.dg * j.da;
-  const int64_t e0 = (int64_t)(blockIdx.x - batch.start[jidx]) * kElemsPerBlock;
+  constexpr int kEPB = GradBlock<kMode>::kElems;
+  const int64_t e0 = (int64_t)(blockIdx.x - batch.start[jidx]) * kEPB;
   float nu = fixed_scale;
   if (kMode == kWrite && vg_acc) {
     float vg = *vg_acc * lr * lr;
@@ -130,11 +134,12 @@ __global__ void __launch_bounds__(256) grad_kernel(const __grid_constant__ GradB
     }
     return;
   }
+  const bool small = total < ((int64_t)1 << 31);          // 32-bit division: a 64-bit one costs ~100 instructions
 #pragma unroll
-  for (int u = 0; u < kElemsPerBlock / 256; ++u) {
+  for (int u = 0; u < kEPB / 256; ++u) {
     int64_t e = e0 + u * 256 + threadIdx.x;
     if (e >= total) break;
-    int r = (int)(e / j.da), c = (int)(e - (int64_t)r * j.da);
+    int r = small ? (int)((uint32_t)e / (uint32_t)j.da) : (int)(e / j.da), c = (int)(e - (int64_t)r * j.da);
     float* gp = c < j.nw ? j.wg + (int64_t)r * j.nw + c : j.bg + r;
     float* vp = j.v + (int64_t)r * j.ld + c;
     if (kMode == kPack) *vp = *gp;
@@ -163,7 +168,7 @@ int run_grad(const GradJob* jobs, int n, float* acc_out, const float* vg_acc, fl
     for (int i = 0; i < batch.n; ++i) {
       batch.jobs[i] = jobs[base + i];
       batch.start[i] = blocks;
-      blocks += (int)ceil_div64((int64_t)jobs[base + i].dg * jobs[base + i].da, kElemsPerBlock);
+      blocks += (int)ceil_div64((int64_t)jobs[base + i].dg * jobs[base + i].da, GradBlock<kMode>::kElems);
     }
     batch.start[batch.n] = blocks;
     grad_kernel<kMode><<<blocks, 256, 0, stream>>>(batch, acc_out, vg_acc, lr, kl_clip, fixed_scale);
