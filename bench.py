@@ -401,7 +401,7 @@ def run_ours(args):
         'metric': 'kfac_step_ms', 'value': ms_total / args.steps, 'unit': 'ms/step',
         'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
         'ms_per_step': ms_total / args.steps, 'higher_is_better': False, 'scaling': 'weak',
-        'vs_baseline': None, 'dtype': 'tf32' if ops.get_mma_mode() == 1 else 'f32',
+        'vs_baseline': None, 'dtype': {0: 'f32', 1: 'tf32', 2: 'tf32 (3xTF32 precondition chain)'}[ops.get_mma_mode()],
         'data': 'synthetic', 'impl': 'ours',
         'config': {'workload': workload_name(args.model),
                    'comm_method': args.comm_method, 'batch_per_gpu': LSTM_LM['batch'] if args.model == 'lstm_lm' else BATCH,

@@ -58,7 +58,7 @@ struct Context {
 
 KFB_HIDDEN Context* current_context();          // context selected by the last kfb_init on this thread
 KFB_HIDDEN int require_context(Context** out);  // KFB_OK or error if kfb_init was never called
-KFB_HIDDEN int mma_mode();                      // 0 SIMT, 1 tcgen05
+KFB_HIDDEN int mma_mode();                      // 0 SIMT, 1 tcgen05 (TF32), 2 tcgen05 with a 3xTF32 precondition chain
 KFB_HIDDEN int syrk_pair_mode();                // factor SYRK: factors of at least this many 128-wide tiles per side go to the CTA-pair (cta_group::2) kernel; 0 (default): none.  env KFB_SYRK_2CTA=<tiles>
 KFB_HIDDEN int stage_mode();                    // factor SYRK: 1 (default) im2col operands are read from zero-padded fp32 staging copies; env KFB_SYRK_STAGE=0: in place
 KFB_HIDDEN void set_stage_override(int v);       // this thread: -1 follow the environment, 0 / 1 force staging off / on

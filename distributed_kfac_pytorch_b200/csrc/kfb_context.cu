@@ -15,7 +15,13 @@ static thread_local char g_err[1024] = "";
 static thread_local Context* g_ctx = nullptr;
 static Context g_contexts[64];
 static std::mutex g_mu;
-static int g_mma_mode = 1;
+// KFB_MMA_MODE=0/1/2 chooses the initial mode (kfb_set_mma_mode changes it later)
+static int initial_mma_mode() {
+  const char* e = getenv("KFB_MMA_MODE");
+  const int m = e ? atoi(e) : 1;
+  return m >= 0 && m <= 2 ? m : 1;
+}
+static int g_mma_mode = initial_mma_mode();
 static std::atomic<unsigned long long> g_launches{0};
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
@@ -103,7 +109,7 @@ const char* kfb_last_error(void) { return kfb::get_error(); }
 int kfb_init(int device) { return kfb::init_device(device); }
 
 int kfb_set_mma_mode(int mode) {
-  KFB_REQUIRE(mode == 0 || mode == 1, "mma mode must be 0 (SIMT) or 1 (tcgen05), got %d", mode);
+  KFB_REQUIRE(mode >= 0 && mode <= 2, "mma mode must be 0 (SIMT), 1 (tcgen05 TF32) or 2 (tcgen05, 3xTF32 precondition chain), got %d", mode);
   kfb::g_mma_mode = mode;
   return KFB_OK;
 }

@@ -889,7 +889,7 @@ int factor_update_with(const kfb_factor_job* jobs, int n_jobs, float alpha, Cont
                        size_t workspace_bytes, const char* what, cudaStream_t stream) {
   std::lock_guard<std::mutex> lock(g_plan_mu);
   FactorPlan* plan;
-  int rc = cached_plan(jobs, n_jobs, ctx->num_sms, ctx->umma_ok && mma_mode() == 1, &plan);
+  int rc = cached_plan(jobs, n_jobs, ctx->num_sms, ctx->umma_ok && mma_mode() != 0, &plan);
   if (rc) return rc;
   if (!workspace || workspace_bytes < plan->total_bytes)
     KFB_FAIL(KFB_ERR_WORKSPACE, "%s: these %d job(s) need %zu bytes of scratch but %zu are available", what, n_jobs,
@@ -925,7 +925,7 @@ int factor_update_with(const kfb_factor_job* jobs, int n_jobs, float alpha, Cont
 size_t factor_workspace_bytes(const kfb_factor_job* jobs, int n_jobs, Context* ctx) {
   std::lock_guard<std::mutex> lock(g_plan_mu);
   FactorPlan* plan;
-  bool tc = ctx && ctx->umma_ok && mma_mode() == 1;
+  bool tc = ctx && ctx->umma_ok && mma_mode() != 0;
   if (cached_plan(jobs, n_jobs, ctx ? ctx->num_sms : 148, tc, &plan) != KFB_OK) return 0;
   return plan->total_bytes;
 }

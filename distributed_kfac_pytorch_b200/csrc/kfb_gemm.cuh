@@ -24,7 +24,7 @@ typedef Batch<GemmProb, kGemmBatch> GemmBatch;
 // Run `n` problems (one launch per kGemmBatch problems). SIMT fp32.
 KFB_HIDDEN int gemm_grouped_simt(const GemmProb* probs, int n, float* dot_acc, cudaStream_t stream);
 // tcgen05 TF32; problems must satisfy gemm_tc_eligible().
-KFB_HIDDEN int gemm_grouped_tc(Context* ctx, const GemmProb* probs, int n, float* dot_acc, cudaStream_t stream);
+KFB_HIDDEN int gemm_grouped_tc(Context* ctx, const GemmProb* probs, int n, float* dot_acc, cudaStream_t stream, bool x3 = false);
 KFB_HIDDEN bool gemm_tc_eligible(const GemmProb& p);
 
 }  // namespace kfb

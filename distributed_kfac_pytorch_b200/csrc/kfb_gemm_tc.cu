@@ -253,6 +253,11 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
 constexpr int kStages2 = 6;
 constexpr int kStageBytes2 = (128 + 128) * BK * 4;                 // A 16 KB + half of B 16 KB
 constexpr int kSmemBytes2 = kStages2 * kStageBytes2 + 1024 + 256;
+// 3xTF32 build of the pair kernel (k3x): a stage also holds the LOW parts of its two tiles, written by four
+// extra warps from the fp32 tiles TMA delivered: [A 16 KB][B half 16 KB][A_lo][B_lo], three stages
+constexpr int kStages3 = 3;
+constexpr int kStageBytes3 = 2 * kStageBytes2;
+constexpr int kSplitWarps = 4;
 
 __device__ __forceinline__ int snake_cluster_tile(int round, int total) {
   const int g = gridDim.x >> 1, c = blockIdx.x >> 1;
@@ -268,10 +273,19 @@ __device__ __forceinline__ int snake_cluster_tile(int round, int total) {
 // kCoal: the epilogue passes every 32 x 32 chunk through a 4 KB shared-memory buffer of its warp so that its
 // global accesses are whole 128-byte row segments (a thread owns an accumulator ROW, so straight from the
 // registers one store instruction touches 32 different lines, 16 of every sector's 32 bytes).
-template <int kEpi, int kEW, bool kCoal>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + kEW), 1)
+// k3x: error-compensated "3xTF32" products.  kind::tf32 reads the top 19 bits of an fp32 operand, i.e. x_hi =
+// trunc(x); with x_lo = x - x_hi (exact in fp32) the sum A_lo B_hi + A_hi B_lo + A_hi B_hi, accumulated in fp32,
+// carries a relative error of ~2^-20 instead of 2^-10.  The low parts never touch global memory: four extra warps
+// compute them from the fp32 tiles in shared memory, stage by stage, between the TMA's arrival and the MMAs
+// (fence.proxy.async in between), so the operand traffic out of L2 - the bound of the single-pass kernel - is
+// unchanged and only the MMA count triples.  In this build every CTA's TMA reports to its OWN full barrier (its
+// split warps wait on it) and the split warps of both CTAs report to the leader's xfull, which the issuer waits on.
+template <int kEpi, int kEW, bool kCoal, bool k3x>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + kEW + (k3x ? kSplitWarps : 0)), 1)
     gemm_tc2_kernel(const __grid_constant__ TcBatch batch, float* __restrict__ dot_acc) {
   constexpr bool kMul = (kEpi & 1) != 0, kDot = (kEpi & 2) != 0;
+  constexpr int kStages2 = k3x ? kStages3 : kfb::kStages2;
+  constexpr int kStageBytes2 = k3x ? kStageBytes3 : kfb::kStageBytes2;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint64_t* full = (uint64_t*)(smem + kStages2 * kStageBytes2);
@@ -279,6 +293,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + kEW), 1)
   uint64_t* tfull = empty + kStages2;
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = (uint32_t*)(tempty + 2);
+  uint64_t* xfull = (uint64_t*)(tmem_slot + 2);       // [kStages2], k3x only: low parts of both CTAs are in place
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = umma::cluster_ctarank();
@@ -288,6 +303,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + kEW), 1)
     for (int s = 0; s < kStages2; ++s) { umma::mbar_init(&full[s], 1); umma::mbar_init(&empty[s], 1); }
     // tempty lives in the leader: all epilogue threads of the pair arrive there
     for (int s = 0; s < 2; ++s) { umma::mbar_init(&tfull[s], 1); umma::mbar_init(&tempty[s], 2 * 32 * kEW); }
+    if (k3x)
+      for (int s = 0; s < kStages2; ++s) umma::mbar_init(&xfull[s], 2 * kSplitWarps);
     umma::fence_barrier_init();
   }
   if (warp == 1) umma::tmem_alloc_pair<kTmemCols>(tmem_slot);
@@ -314,9 +331,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + kEW), 1)
           umma::mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sa = smem + stage * kStageBytes2;
           uint8_t* sb = sa + 128 * BK * 4;
-          if (leader) umma::mbar_arrive_expect_tx(&full[stage], tx);
-          umma::tma_load_2d_pair(sa, &pr.mapA, &full[stage], kb * BK, m0);
-          umma::tma_load_2d_pair(sb, &pr.mapB, &full[stage], kb * BK, n0);
+          if (k3x) {
+            umma::mbar_arrive_expect_tx(&full[stage], tx >> 1);        // this CTA's own bytes, on its own barrier
+            umma::tma_load_2d(sa, &pr.mapA, &full[stage], kb * BK, m0);
+            umma::tma_load_2d(sb, &pr.mapB, &full[stage], kb * BK, n0);
+          } else {
+            if (leader) umma::mbar_arrive_expect_tx(&full[stage], tx);
+            umma::tma_load_2d_pair(sa, &pr.mapA, &full[stage], kb * BK, m0);
+            umma::tma_load_2d_pair(sb, &pr.mapB, &full[stage], kb * BK, n0);
+          }
           if (++stage == kStages2) { stage = 0; phase ^= 1; }
         }
       }
@@ -348,7 +371,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + kEW), 1)
 #ifdef KFB_GEMM_PROFILE
           const long long pb = clock64();
 #endif
-          umma::mbar_wait(&full[stage], phase);
+          if (k3x) umma::mbar_wait_acquire_cluster_a(umma::smem_u32(&xfull[stage]), phase);
+          else umma::mbar_wait(&full[stage], phase);
           umma::tc_fence_after();
 #ifdef KFB_GEMM_PROFILE
           const long long pc = clock64();
@@ -359,9 +383,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + kEW), 1)
           const uint32_t sb = sa + 128 * BK * 4;
           const uint64_t da = umma::make_kmajor_sw128_desc(sa);
           const uint64_t db = umma::make_kmajor_sw128_desc(sb);
+          if (k3x) {
+            // small terms first: A_lo B_hi, A_hi B_lo, then A_hi B_hi (the hardware's truncation IS the hi part)
+            const uint64_t dal = umma::make_kmajor_sw128_desc(sa + kfb::kStageBytes2);
+            const uint64_t dbl = umma::make_kmajor_sw128_desc(sb + kfb::kStageBytes2);
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k)
+              umma::mma_tf32_ss_pair(d_tmem, dal + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k)
+              umma::mma_tf32_ss_pair(d_tmem, da + 2 * k, dbl + 2 * k, idesc, 1u);
+          }
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k)
-            umma::mma_tf32_ss_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+            umma::mma_tf32_ss_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, k3x ? 1u : (uint32_t)((kb | k) != 0));
           umma::tc_commit_pair(&empty[stage]);
           if (++stage == kStages2) { stage = 0; phase ^= 1; }
 #ifdef KFB_GEMM_PROFILE
@@ -376,6 +411,45 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(32 * (2 + kEW), 1)
         printf("gemm<%d,%d> cta %3d: total %lld clk, tiles %lld k-blocks %lld | issuer: wait tempty %lld, wait full %lld, issue %lld\n", kEpi, kEW,
                blockIdx.x, clock64() - pf_t0, pf_tiles, pf_kb, pf_tempty, pf_full, pf_issue);
 #endif
+    }
+  } else if (k3x && warp >= 2 + kEW) {
+    // ===================== split warps (k3x, both CTAs): x_lo = x - trunc19(x) for this CTA's two tiles =====
+    // Elementwise on the swizzled image as it lies (the layout does not matter); warp w takes a quarter of each
+    // 16 KB tile.  Rows past the half of a 128-wide B tile hold stale bytes: written, never read by the MMAs.
+    const int w = warp - (2 + kEW);
+    int stage = 0; uint32_t phase = 0;
+    for (int round = 0, tile; (tile = snake_cluster_tile(round, batch.total_tiles)) >= 0; ++round) {
+      const int p = find_prob(batch, tile);
+      const int kblocks = (batch.probs[p].K + BK - 1) / BK;
+      for (int kb = 0; kb < kblocks; ++kb) {
+        umma::mbar_wait(&full[stage], phase);                 // this CTA's TMA bytes have landed
+        const uint32_t base = umma::smem_u32(smem + stage * kStageBytes2) + (uint32_t)w * 4096u + (uint32_t)lane * 16u;
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+          uint4 v[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(v[i].x), "=r"(v[i].y), "=r"(v[i].z), "=r"(v[i].w)
+                         : "r"(base + (uint32_t)t * 16384u + (uint32_t)i * 512u));
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            // the low part is itself rounded to nearest TF32 here, so the hardware's truncation of it is exact
+            auto lo = [](uint32_t x) {
+              uint32_t r;
+              asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(__uint_as_float(x) - __uint_as_float(x & 0xFFFFE000u)));
+              return r;
+            };
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(base + (uint32_t)kfb::kStageBytes2 + (uint32_t)t * 16384u + (uint32_t)i * 512u),
+                         "r"(lo(v[i].x)), "r"(lo(v[i].y)), "r"(lo(v[i].z)), "r"(lo(v[i].w))
+                         : "memory");
+          }
+        }
+        umma::fence_proxy_async_smem();                       // generic-proxy writes -> the MMAs' async-proxy reads
+        __syncwarp();
+        if (lane == 0) umma::mbar_arrive_leader_release_a(umma::smem_u32(&xfull[stage]));
+        if (++stage == kStages2) { stage = 0; phase ^= 1; }
+      }
     }
   } else {
     // ===================== epilogue (both CTAs: each drains its own 128 accumulator rows) =====
@@ -632,20 +706,22 @@ bool gemm_tc_eligible(const GemmProb& p) {
 }
 
 typedef void (*Tc2Kernel)(const TcBatch, float*);
-template <int kEpi, int kEW, bool kCoal>
+template <int kEpi, int kEW, bool kCoal, bool k3x = false>
 static int launch_tc2(Context* ctx, const TcBatch& batch, int clusters, float* dot_acc, cudaStream_t stream) {
   static bool attr_set[64] = {};        // the opt-in to > 48 KB of dynamic shared memory is per device (and per instantiation)
-  constexpr int smem = kSmemBytes2 + (kCoal ? kEW * 4096 : 0);      // + one 32 x 32 fp32 staging buffer per epilogue warp
+  // + one 32 x 32 fp32 staging buffer per epilogue warp
+  constexpr int smem = (k3x ? kStages3 * kStageBytes3 + 1024 + 256 : kSmemBytes2) + (kCoal ? kEW * 4096 : 0);
+  static_assert(smem <= 232448, "shared memory of the GEMM kernel exceeds 227 KB");
   if (!attr_set[ctx->device]) {
-    KFB_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel<kEpi, kEW, kCoal>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    KFB_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel<kEpi, kEW, kCoal, k3x>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr_set[ctx->device] = true;
   }
-  gemm_tc2_kernel<kEpi, kEW, kCoal><<<2 * clusters, 32 * (2 + kEW), smem, stream>>>(batch, dot_acc);
+  gemm_tc2_kernel<kEpi, kEW, kCoal, k3x><<<2 * clusters, 32 * (2 + kEW + (k3x ? kSplitWarps : 0)), smem, stream>>>(batch, dot_acc);
   KFB_CHECK_LAUNCH();
   return KFB_OK;
 }
 
-static int gemm_grouped_tc2(Context* ctx, const GemmProb* probs, int n, float* dot_acc, cudaStream_t stream) {
+static int gemm_grouped_tc2(Context* ctx, const GemmProb* probs, int n, float* dot_acc, cudaStream_t stream, bool x3) {
   // eight epilogue warps by default (KFB_GEMM_EPI_WARPS=4: one per TMEM lane quarter)
   static const int epi_warps = []() { const char* e = getenv("KFB_GEMM_EPI_WARPS"); return e && atoi(e) == 4 ? 4 : 8; }();
   std::vector<GemmProb> sorted(probs, probs + n);
@@ -678,7 +754,12 @@ static int gemm_grouped_tc2(Context* ctx, const GemmProb* probs, int n, float* d
     const int clusters = std::min(tiles, ctx->num_sms / 2);
     static const bool coal = []() { const char* e = getenv("KFB_GEMM_COALESCE"); return !e || atoi(e) != 0; }();
     int rc;
-    if (coal) {          // coalesced drain through shared memory, eight warps
+    if (x3) {            // error-compensated products: always the coalesced eight-warp build
+      rc = epi == 0 ? launch_tc2<0, 8, true, true>(ctx, batch, clusters, dot_acc, stream)
+           : epi == 1 ? launch_tc2<1, 8, true, true>(ctx, batch, clusters, dot_acc, stream)
+           : epi == 2 ? launch_tc2<2, 8, true, true>(ctx, batch, clusters, dot_acc, stream)
+                      : launch_tc2<3, 8, true, true>(ctx, batch, clusters, dot_acc, stream);
+    } else if (coal) {   // coalesced drain through shared memory, eight warps
       rc = epi == 0 ? launch_tc2<0, 8, true>(ctx, batch, clusters, dot_acc, stream)
            : epi == 1 ? launch_tc2<1, 8, true>(ctx, batch, clusters, dot_acc, stream)
            : epi == 2 ? launch_tc2<2, 8, true>(ctx, batch, clusters, dot_acc, stream)
@@ -699,12 +780,12 @@ static int gemm_grouped_tc2(Context* ctx, const GemmProb* probs, int n, float* d
   return KFB_OK;
 }
 
-int gemm_grouped_tc(Context* ctx, const GemmProb* probs, int n, float* dot_acc, cudaStream_t stream) {
+int gemm_grouped_tc(Context* ctx, const GemmProb* probs, int n, float* dot_acc, cudaStream_t stream, bool x3) {
   // CTA-pair kernel by default (measured 0.72 -> 0.67 ms for the ResNet-50 chain; routing the
   // problems with M <= 128 to the single-CTA kernel instead was slower); KFB_GEMM_2CTA=0 selects
   // the single-CTA kernel
   static const bool use_pair = []() { const char* e = getenv("KFB_GEMM_2CTA"); return !e || atoi(e) != 0; }();
-  if (use_pair) return gemm_grouped_tc2(ctx, probs, n, dot_acc, stream);
+  if (use_pair || x3) return gemm_grouped_tc2(ctx, probs, n, dot_acc, stream, x3);
   // longest tiles first: with the static round-robin tile schedule this is close to LPT
   std::vector<GemmProb> sorted(probs, probs + n);
   std::stable_sort(sorted.begin(), sorted.end(), [](const GemmProb& a, const GemmProb& b) { return a.K > b.K; });

@@ -211,11 +211,14 @@ int gemm_grouped_simt(const GemmProb* probs, int n, float* dot_acc, cudaStream_t
 }
 
 static int run_stage(Context* ctx, std::vector<GemmProb>& probs, float* dot_acc, cudaStream_t stream) {
-  if (mma_mode() == 1 && ctx->umma_ok) {
+  // KFB_CHAIN_MMA=0/1/2 overrides the MMA mode for the precondition chain alone (error attribution experiments)
+  const char* chain_env = getenv("KFB_CHAIN_MMA");
+  const int chain_mode = chain_env ? atoi(chain_env) : mma_mode();
+  if (chain_mode != 0 && ctx->umma_ok) {
     std::vector<GemmProb> tc, simt;
     for (auto& p : probs) (gemm_tc_eligible(p) ? tc : simt).push_back(p);
     int rc = KFB_OK;
-    if (!tc.empty()) rc = gemm_grouped_tc(ctx, tc.data(), (int)tc.size(), dot_acc, stream);
+    if (!tc.empty()) rc = gemm_grouped_tc(ctx, tc.data(), (int)tc.size(), dot_acc, stream, chain_mode == 2);
     if (rc == KFB_OK && !simt.empty()) rc = gemm_grouped_simt(simt.data(), (int)simt.size(), dot_acc, stream);
     return rc;
   }

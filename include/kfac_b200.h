@@ -51,7 +51,10 @@ KFB_API const char* kfb_last_error(void);
  * `device` and make it the context used by later calls from this thread. Idempotent. */
 KFB_API int kfb_init(int device);
 /* Which code path the GEMM-shaped kernels use: 0 = SIMT fp32 (exact fp32 FMA, the
- * first-correct path), 1 = tcgen05 TF32 tensor cores (default when available). */
+ * first-correct path), 1 = tcgen05 TF32 tensor cores (default when available), 2 = as 1, but the
+ * precondition chain (kfac/layers/base.py:459-470) forms every product as the error-compensated
+ * "3xTF32" sum A_lo B_hi + A_hi B_lo + A_hi B_hi with fp32 accumulation: fp32-grade gradients at a
+ * third of the tensor-core rate. */
 KFB_API int kfb_set_mma_mode(int mode);
 KFB_API int kfb_get_mma_mode(void);
 /* Number of kernels of this library launched so far in this process (all devices); cuSOLVER's

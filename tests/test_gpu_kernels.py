@@ -585,6 +585,40 @@ def test_gemm_tn(ops, shape):
         assert torch.isnan(buf[:, Nn:]).all()
 
 
+@pytest.mark.parametrize('shape', GEMM_SHAPES, ids=lambda s: 'x'.join(map(str, s)))
+def test_gemm_tn_3xtf32(shape):
+    """mma mode 2: every product is A_lo B_hi + A_hi B_lo + A_hi B_hi (the low parts are made in shared
+    memory by the kernel's split warps).  Same tiles, same TMA traffic, three times the MMAs; the error
+    bound against float64 is 400 times tighter than single-pass TF32's."""
+    M, Nn, K = shape
+    g = torch.Generator().manual_seed(M * 7 + Nn * 3 + K)
+    A = torch.randn(M, K, generator=g)
+    B = torch.randn(Nn, K, generator=g)
+    mul = torch.rand(M, Nn, generator=g) + 0.5
+    N.set_ops(None)
+    o = N.get_ops()
+    o._enter(torch.zeros(1, device=DEV))
+    _, a = alloc2d(M, K, DEV, zero=True); a.copy_(A)
+    _, b = alloc2d(Nn, K, DEV, zero=True); b.copy_(B)
+    _, m = alloc2d(M, Nn, DEV, zero=True); m.copy_(mul)
+    buf, d = alloc2d(M, Nn, DEV)
+    buf.fill_(float('nan'))
+    o.set_mma_mode(2)
+    try:
+        o.gemm_tn(a, b, d, m)
+        torch.cuda.synchronize()
+    finally:
+        o.set_mma_mode(1)
+    ref = (A.double() @ B.double().t()) * mul.double()
+    bound = 5e-6 * torch.outer(A.double().norm(dim=1), B.double().norm(dim=1)) * mul.double() + 1e-7
+    err = (d.cpu().double() - ref).abs()
+    assert torch.isfinite(d).all()
+    worst = (err / bound).max().item()
+    assert worst <= 1.0, 'gemm error %.3g x bound' % worst
+    if buf.shape[1] > Nn:
+        assert torch.isnan(buf[:, Nn:]).all()
+
+
 def make_precond_job(da, dg, bias, wshape, seed):
     g = torch.Generator().manual_seed(seed)
     A = torch.randn(2 * da, da, generator=g)
@@ -656,6 +690,38 @@ def test_precondition_chain_and_kl_clip(ops):
     before = jobs[0].out.clone()
     ops.scale_writeback(items[:1], vg, lr, kl)
     torch.testing.assert_close(jobs[0].weight_grad.reshape(before.shape), before, rtol=0, atol=0)
+
+
+def test_precondition_chain_3xtf32_matches_fp32():
+    """mma mode 2 on the whole chain (larger layers added so that every stage runs on the tensor cores): the
+    result must meet the bound the exact fp32 SIMT path is held to (1e-4 * scale), twenty times tighter than
+    single-pass TF32's, and agree with the SIMT path itself."""
+    cases = PRECOND_CASES + [(1152, 256, False, (256, 128, 3, 3)), (513, 1024, True, (1024, 512))]
+    N.set_ops(None)
+    o = N.get_ops()
+    o._enter(torch.zeros(1, device=DEV))
+    outs = {}
+    for mode in (2, 0):
+        jobs, refs = [], []
+        for i, (da, dg, bias, wshape) in enumerate(cases):
+            job, ref, wg, bg = make_precond_job(da, dg, bias, wshape, 100 + i)
+            jobs.append(job); refs.append(ref)
+        vg = torch.zeros(1, device=DEV)
+        o.set_mma_mode(mode)
+        try:
+            o.precondition(jobs, vg)
+            torch.cuda.synchronize()
+        finally:
+            o.set_mma_mode(1)
+        for job, ref in zip(jobs, refs):
+            scale = max(1.0, ref.abs().max().item())
+            torch.testing.assert_close(job.out.cpu(), ref, rtol=1e-2, atol=1e-4 * scale)
+        outs[mode] = [j.out.cpu().clone() for j in jobs], vg.item()
+    for a, b, ref in zip(outs[2][0], outs[0][0], refs):
+        diff, scale = (a - b).abs().max().item(), max(1.0, ref.abs().max().item())
+        assert diff <= 1e-4 * scale, 'modes 2 and 0 differ by %.3g on a scale of %.3g' % (diff, scale)
+        print('3xTF32 vs fp32: %.3g of scale %.3g; fp32 vs float64 oracle: %.3g' % (diff, scale, (b - ref).abs().max().item()))
+    assert abs(outs[2][1] - outs[0][1]) <= 1e-4 * abs(outs[0][1])
 
 
 def test_capture_filter_and_16bit_round_trip(ops):
