@@ -41,6 +41,14 @@ def test_errors_without_context(lib):
     assert b'kfb_init' in lib.kfb_last_error()
     assert lib.kfb_set_mma_mode(7) != 0
     assert b'mma mode' in lib.kfb_last_error()
+    prev = lib.kfb_get_mma_mode()
+    for mode in (0, 2, 1):               # SIMT fp32, TF32 + 3xTF32 chain, TF32
+        assert lib.kfb_set_mma_mode(mode) == 0 and lib.kfb_get_mma_mode() == mode
+    assert lib.kfb_set_mma_mode(prev) == 0
+    # the workspace promise is bookkeeping only: no device needed, bad pointers refused
+    assert lib.kfb_factor_workspace_dedicate(None, 0) != 0
+    assert lib.kfb_factor_workspace_dedicate(4096, 1 << 20) == 0 and lib.kfb_factor_workspace_release(4096) == 0
+    assert lib.kfb_factor_workspace_release(4096) == 0      # releasing twice is harmless
     assert lib.kfb_init(0) != 0          # no device here
     assert lib.kfb_last_error() != b''
 
