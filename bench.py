@@ -116,6 +116,8 @@ class ClockSampler(object):
 
     def __init__(self, index):
         self.proc, self.lines = None, []
+        if os.environ.get('KFB_BENCH_NO_SAMPLER'):      # experiments only: how much the polling itself costs
+            return
         try:
             self.proc = subprocess.Popen(
                 ['nvidia-smi', '-i', str(index), '--query-gpu=' + self.Q,
@@ -394,6 +396,7 @@ def run_ours(args):
     factor_ms, precond_ms = t_factor.mean_ms(), t_precond.mean_ms()
     syevd_ms_total = sum(a.elapsed_time(b) for a, b in t_syevd.pairs)
     n_inv_steps = max(1, len(t_factor.pairs))
+    syevd_calls = [round(a.elapsed_time(b), 1) for a, b in t_syevd.pairs]
     for t in (t_factor, t_precond, t_syevd):
         t.reset(False)
 
@@ -411,7 +414,8 @@ def run_ours(args):
                    'mma_mode': ops.get_mma_mode()},
         'clocks': clocks, 'gpu_launches': launches,
         'stages_ms': {'factor_update_call': factor_ms, 'precondition_call': precond_ms,
-                      'syevd_per_inverse_step': syevd_ms_total / n_inv_steps},
+                      'syevd_per_inverse_step': syevd_ms_total / n_inv_steps,
+                      'syevd_calls_ms': syevd_calls},
     }
     if dist_on:
         # every rank's own stage times (the step is as slow as the slowest rank: the allocator's n^3
