@@ -210,15 +210,18 @@ int gemm_grouped_simt(const GemmProb* probs, int n, float* dot_acc, cudaStream_t
   return KFB_OK;
 }
 
-static int run_stage(Context* ctx, std::vector<GemmProb>& probs, float* dot_acc, cudaStream_t stream) {
+static int run_stage(Context* ctx, std::vector<GemmProb>& probs, float* dot_acc, cudaStream_t stream, int stage = 0) {
   // KFB_CHAIN_MMA=0/1/2 overrides the MMA mode for the precondition chain alone (error attribution experiments)
   const char* chain_env = getenv("KFB_CHAIN_MMA");
   const int chain_mode = chain_env ? atoi(chain_env) : mma_mode();
+  // KFB_CHAIN_3X_STAGES="12": in mode 2, only the listed stages (1-4) use 3xTF32 products (experiments)
+  const char* only = getenv("KFB_CHAIN_3X_STAGES");
+  const bool x3 = chain_mode == 2 && (!only || stage == 0 || strchr(only, '0' + stage) != nullptr);
   if (chain_mode != 0 && ctx->umma_ok) {
     std::vector<GemmProb> tc, simt;
     for (auto& p : probs) (gemm_tc_eligible(p) ? tc : simt).push_back(p);
     int rc = KFB_OK;
-    if (!tc.empty()) rc = gemm_grouped_tc(ctx, tc.data(), (int)tc.size(), dot_acc, stream, chain_mode == 2);
+    if (!tc.empty()) rc = gemm_grouped_tc(ctx, tc.data(), (int)tc.size(), dot_acc, stream, x3);
     if (rc == KFB_OK && !simt.empty()) rc = gemm_grouped_simt(simt.data(), (int)simt.size(), dot_acc, stream);
     return rc;
   }
@@ -289,10 +292,10 @@ int kfb_precondition(const kfb_precond_job* jobs, int32_t n_jobs, float* vg_acc,
   }
   rc = run_grad<kPack>(pack.data(), (int)pack.size(), nullptr, nullptr, 0.f, 0.f, 1.f, stream);
   if (rc) return rc;
-  if ((rc = run_stage(ctx, s1, nullptr, stream))) return rc;
-  if (!s2.empty() && (rc = run_stage(ctx, s2, nullptr, stream))) return rc;
-  if (!s3.empty() && (rc = run_stage(ctx, s3, nullptr, stream))) return rc;
-  return run_stage(ctx, s4, vg_acc, stream);
+  if ((rc = run_stage(ctx, s1, nullptr, stream, 1))) return rc;
+  if (!s2.empty() && (rc = run_stage(ctx, s2, nullptr, stream, 2))) return rc;
+  if (!s3.empty() && (rc = run_stage(ctx, s3, nullptr, stream, 3))) return rc;
+  return run_stage(ctx, s4, vg_acc, stream, 4);
 }
 
 int kfb_gemm_tn(const float* A, int64_t lda, const float* B, int64_t ldb, float* D, int64_t ldd, int32_t M,
