@@ -398,6 +398,14 @@ __device__ __forceinline__ void pad_transpose(const PadJob& p, uint32_t e0) {
   const uint32_t c = p.mul_hp ? (__umulhi(row, p.mul_hp) >> p.sh_hp) : row;
   const uint32_t n = row - c * (uint32_t)p.hp;
   const T* srow = reinterpret_cast<const T*>(p.src) + ((size_t)n * p.channels + c) * p.ow_valid;
+  if (sizeof(T) == 2 && p.out16) {        // the copy keeps the 16-bit type: raw bits, zero padding
+    unsigned short u[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) u[i] = x0 + i < p.ow_valid ? __ldg(reinterpret_cast<const unsigned short*>(srow) + x0 + i) : (unsigned short)0;
+    *reinterpret_cast<uint2*>(reinterpret_cast<unsigned short*>(p.dst) + e0) =
+        make_uint2((uint32_t)u[0] | ((uint32_t)u[1] << 16), (uint32_t)u[2] | ((uint32_t)u[3] << 16));
+    return;
+  }
   float v[4];
 #pragma unroll
   for (int i = 0; i < 4; ++i) v[i] = x0 + i < p.ow_valid ? pad_load(srow + x0 + i, p.dtype) : 0.f;
@@ -418,9 +426,11 @@ __device__ __forceinline__ void pad_rows(const PadJob& p, int b) {
   for (int r = 0; r < 4; ++r) {
     const int k = k0 + ty + 8 * r, c = c0 + tx;
     float v = 0.f;
+    const bool raw = sizeof(T) == 2 && p.out16;       // 16-bit copy: the tile carries the raw bits
     if (k < p.hp) {
-      if (c < p.h) v = pad_load(src + (size_t)k * p.w + c, p.dtype);
-      else if (c < p.channels) v = 1.f;
+      if (c < p.h) v = raw ? __uint_as_float((uint32_t)__ldg(reinterpret_cast<const unsigned short*>(src) + (size_t)k * p.w + c))
+                           : pad_load(src + (size_t)k * p.w + c, p.dtype);
+      else if (c < p.channels) v = raw ? __uint_as_float(p.dtype == KFB_F16 ? 0x3C00u : 0x3F80u) : 1.f;    // 1.0
     }
     tile[ty + 8 * r][tx] = v;
   }
@@ -428,7 +438,11 @@ __device__ __forceinline__ void pad_rows(const PadJob& p, int b) {
 #pragma unroll
   for (int r = 0; r < 4; ++r) {
     const int c = c0 + ty + 8 * r;
-    if (c < p.channels) p.dst[(size_t)c * p.wp + k0 + tx] = tile[tx][ty + 8 * r];
+    if (c >= p.channels) continue;
+    if (sizeof(T) == 2 && p.out16)
+      reinterpret_cast<unsigned short*>(p.dst)[(size_t)c * p.wp + k0 + tx] = (unsigned short)__float_as_uint(tile[tx][ty + 8 * r]);
+    else
+      p.dst[(size_t)c * p.wp + k0 + tx] = tile[tx][ty + 8 * r];
   }
 }
 
@@ -499,6 +513,11 @@ static int last_arriver_mode() {
 // KFB_SYRK_ROWS_TC=0: Linear-layer captures go back to the SIMT SYRK
 static int rows_tc_mode() {
   const char* e = getenv("KFB_SYRK_ROWS_TC");
+  return e ? atoi(e) : 1;
+}
+// KFB_SYRK_HALF=0: 16-bit captures are widened to fp32 staging copies (kind::tf32) instead of feeding kind::f16
+static int half_mode() {
+  const char* e = getenv("KFB_SYRK_HALF");
   return e ? atoi(e) : 1;
 }
 static int stream_k_mode() {
@@ -612,6 +631,9 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
     }
     dj.n_chunks = chunks;
     dj.use_tc = tc ? 1 : 0;
+    // 16-bit operands for kind::f16 need the TMA-fed single-CTA kernel
+    const bool half16 = tc && half_mode() && tma_mode() && stage_mode() &&
+                        !(syrk_pair_mode() > 0 && ceil_div(j.d, 128) >= syrk_pair_mode());
     for (int si = 0; si < j.n_segments; ++si) {
       DevSegment& ds = plan->segs[dj.seg_start + si];
       plan->seg_pad.push_back(-1);
@@ -672,23 +694,59 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
       if (ds.kind == KFB_SEG_ROWS) {
         // X (rows x features, any pitch, any type) -> fp32 [features (+ a row of ones for the bias)][Kp], Kp = rows
         // rounded up to 32 and zero-filled: from here on a plain NCHW segment of one "image" of Kp "pixels"
-        const int64_t Kp = (ds.K + 31) / 32 * 32;
+        // A 16-bit capture keeps its type (DevSegment::fmt): Kp is then a multiple of 64 rows = 32 words.
+        const bool keep16 = half16 && ds.dtype != KFB_F32;
+        const int64_t Kp = keep16 ? (ds.K + 63) / 64 * 64 : (ds.K + 31) / 32 * 32;
         const int C = ds.c + (ds.has_bias ? 1 : 0);
         PadJob pj;
         memset(&pj, 0, sizeof(pj));
-        pj.src = ds.data; pj.dtype = ds.dtype; pj.variant = 5;
+        pj.src = ds.data; pj.dtype = ds.dtype; pj.variant = 5; pj.out16 = keep16 ? 1 : 0;
         pj.channels = C; pj.h = ds.c; pj.w = (int)ds.ld; pj.hp = (int)ds.K; pj.wp = (int)Kp; pj.kw = 1;
         pj.quads = Kp / 32;                                   // 32 x 32 tiles along K
         pj.total = (int64_t)C * Kp;
         plan->seg_pad.back() = (int)plan->pads.size();
         plan->pad_off.push_back(plan->stage_floats);
-        plan->stage_floats += align_up((size_t)pj.total, 64);
+        plan->stage_floats += align_up((size_t)(keep16 ? (pj.total + 1) / 2 : pj.total), 64);
         plan->pads.push_back(pj);
+        const int64_t Kw = keep16 ? Kp / 2 : Kp;              // row length in 4-byte words
+        ds.fmt = keep16 ? ds.dtype : 0;
         ds.kind = KFB_SEG_NCHW; ds.dtype = KFB_F32; ds.has_bias = 0;
-        ds.c = C; ds.h = 1; ds.w = (int)Kp; ds.oh = 1; ds.ow = (int)Kp; ds.K = Kp; ds.ld = 0;
+        ds.c = C; ds.h = 1; ds.w = (int)Kw; ds.oh = 1; ds.ow = (int)Kw; ds.K = Kw; ds.ld = 0;
         magic_div(ds.K, &ds.mul_s, &ds.sh_s);
         magic_div(ds.ow, &ds.mul_w, &ds.sh_w);
         aligned = true;
+      }
+      if (half16 && ds.kind == KFB_SEG_NCHW && ds.dtype != KFB_F32 && plan->seg_pad.back() < 0) {
+        // 16-bit NCHW captures (AMP) feed kind::f16 MMAs.  The operand is described to TMA and to the kernel as an
+        // fp32 matrix of HALF as many pixels (DevSegment::fmt): image rows that are 16-byte multiples (S % 8 == 0)
+        // are read in place; the others (14 x 14, 7 x 7 maps) through a 16-bit [channels][images * wp] copy.
+        const int64_t S0 = (int64_t)ds.oh * ds.ow, images = ds.K / S0, wp = (S0 + 7) / 8 * 8;
+        if ((S0 & 7) == 0 && S0 >= 2 * BK && aligned) {
+          ds.fmt = ds.dtype; ds.dtype = KFB_F32;
+          ds.h = 1; ds.w = (int)(S0 / 2); ds.oh = 1; ds.ow = ds.w;
+          ds.K = images * (S0 / 2);
+          magic_div((int64_t)ds.oh * ds.ow, &ds.mul_s, &ds.sh_s);
+          magic_div(ds.ow, &ds.mul_w, &ds.sh_w);
+        } else if (images * wp >= 2 * BK && (int64_t)ds.c * images * wp < ((int64_t)1 << 31)) {
+          PadJob pj;
+          memset(&pj, 0, sizeof(pj));
+          pj.src = ds.data; pj.dtype = ds.dtype; pj.variant = 4; pj.out16 = 1;
+          pj.channels = ds.c; pj.hp = (int)images; pj.wp = (int)wp; pj.ow_valid = (int)S0; pj.kw = 1;
+          pj.total = (int64_t)ds.c * images * wp;
+          magic_div(pj.wp, &pj.mul_wp, &pj.sh_wp);
+          magic_div(pj.hp, &pj.mul_hp, &pj.sh_hp);
+          plan->seg_pad.back() = (int)plan->pads.size();
+          plan->pad_off.push_back(plan->stage_floats);
+          plan->stage_floats += align_up((size_t)((pj.total + 1) / 2), 64);
+          plan->pads.push_back(pj);
+          ds.fmt = ds.dtype; ds.dtype = KFB_F32;
+          ds.h = 1; ds.w = (int)(images * wp / 2);
+          ds.oh = 1; ds.ow = ds.w;
+          ds.K = ds.w;
+          magic_div(ds.K, &ds.mul_s, &ds.sh_s);
+          magic_div(ds.ow, &ds.mul_w, &ds.sh_w);
+          aligned = true;
+        }
       }
       {
         // NCHW operands TMA cannot take as they are: stage an fp32 [channels][images * padded pixels]
@@ -812,7 +870,7 @@ std::vector<int64_t> g_plan_sig;
 
 void signature(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool tc, std::vector<int64_t>* sig) {
   sig->clear();
-  sig->push_back(n_jobs); sig->push_back(num_sms); sig->push_back(tc); sig->push_back(tma_mode()); sig->push_back(stage_mode()); sig->push_back(syrk_pair_mode()); sig->push_back(fused_max_rows()); sig->push_back(stream_k_mode()); sig->push_back(last_arriver_mode()); sig->push_back(rows_tc_mode());
+  sig->push_back(n_jobs); sig->push_back(num_sms); sig->push_back(tc); sig->push_back(tma_mode()); sig->push_back(stage_mode()); sig->push_back(syrk_pair_mode()); sig->push_back(fused_max_rows()); sig->push_back(stream_k_mode()); sig->push_back(last_arriver_mode()); sig->push_back(rows_tc_mode()); sig->push_back(half_mode());
   for (int i = 0; i < n_jobs; ++i) {
     const kfb_factor_job& j = jobs[i];
     sig->push_back(j.d); sig->push_back(j.n_segments); sig->push_back(j.ld_state);

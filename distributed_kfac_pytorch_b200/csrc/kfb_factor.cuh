@@ -31,6 +31,10 @@ struct DevSegment {
   int ow_valid;          // nomask: output pixels per row that exist (bias feature = 1 only there)
   int tma;               // index of this segment's TMA descriptor, -1: gathered by the producer warps
   int nb;                // TMA segments: 32-row blocks per image (the last one zero-filled past oh*ow)
+  int fmt;               // 0: fp32 operands, kind::tf32.  KFB_F16 / KFB_BF16: the operand is 16-bit and TMA-fed; it is
+                         // DESCRIBED as an fp32 matrix of half as many columns (two X rows per 4-byte word: same bytes,
+                         // same 128-byte tile rows, K counted in words) and only the MMA differs: kind::f16 reads every
+                         // 128-byte row as 64 K-elements - exact products, half the bytes, twice the MMA rate
 };
 
 struct DevJob {
@@ -101,6 +105,7 @@ struct PadJob {
                          // 4: NCHW capture -> [channels][images * wp] (see below)
                          // 5: row-major capture -> [features (+ ones)][rows rounded up to 32] (pad_rows)
   int channels;          // variant 4
+  int out16;             // variants 4, 5: the copy keeps the capture's 16-bit type (DevSegment::fmt) instead of widening
   int64_t quads;         // variants 1-3: planes * hp * wp/4 threads; variant 5: 32-row tiles along K
   int64_t total;         // planes * kw * hp * wp (< 2^31)
 };

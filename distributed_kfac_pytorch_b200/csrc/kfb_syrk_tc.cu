@@ -779,11 +779,13 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
           // tile m runs against column tiles n0..nj-1 in ONE instruction (N = 128 or 256); on the
           // diagonal the column tiles are the row tiles and products below the diagonal are skipped.
           uint32_t idesc_m[2], a_lo[2], b_lo[2], d_tm[2];
+          const int fmt16 = segs[item.seg].fmt;      // 16-bit TMA-fed operand: kind::f16 over the same tile bytes
           const uint32_t lo0 = umma::kmajor_sw128_desc_lo(umma::smem_u32(smem));
 #pragma unroll
           for (int m = 0; m < 2; ++m) {
             const int n0 = diag ? m : 0;
-            idesc_m[m] = umma::make_idesc_tf32(TM, (item.nj - n0) * TM);
+            idesc_m[m] = fmt16 ? umma::make_idesc_f16(fmt16 == KFB_BF16 ? 1 : 0, TM, (item.nj - n0) * TM)
+                               : umma::make_idesc_tf32(TM, (item.nj - n0) * TM);
             a_lo[m] = lo0 + ((m * kTileBytes) >> 4);
             b_lo[m] = lo0 + ((((diag ? 0 : 2) + n0) * kTileBytes) >> 4);
             d_tm[m] = tmem_base + m * 256 + n0 * TM;
@@ -802,13 +804,24 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
             ++pf_stages;
 #endif
             const uint32_t soff = (uint32_t)stage * (kStageBytes >> 4);
-#pragma unroll
-            for (int k = 0; k < BK / UMMA_K; ++k)
-              umma::mma_tf32_ss_lohi(d_tm[0], a_lo[0] + soff + 2 * k, b_lo[0] + soff + 2 * k, idesc_m[0], k == 0 ? acc_flag : 1u);
-            if (two) {
+            if (fmt16) {
 #pragma unroll
               for (int k = 0; k < BK / UMMA_K; ++k)
-                umma::mma_tf32_ss_lohi(d_tm[1], a_lo[1] + soff + 2 * k, b_lo[1] + soff + 2 * k, idesc_m[1], k == 0 ? acc_flag : 1u);
+                umma::mma_f16_ss_lohi(d_tm[0], a_lo[0] + soff + 2 * k, b_lo[0] + soff + 2 * k, idesc_m[0], k == 0 ? acc_flag : 1u);
+              if (two) {
+#pragma unroll
+                for (int k = 0; k < BK / UMMA_K; ++k)
+                  umma::mma_f16_ss_lohi(d_tm[1], a_lo[1] + soff + 2 * k, b_lo[1] + soff + 2 * k, idesc_m[1], k == 0 ? acc_flag : 1u);
+              }
+            } else {
+#pragma unroll
+              for (int k = 0; k < BK / UMMA_K; ++k)
+                umma::mma_tf32_ss_lohi(d_tm[0], a_lo[0] + soff + 2 * k, b_lo[0] + soff + 2 * k, idesc_m[0], k == 0 ? acc_flag : 1u);
+              if (two) {
+#pragma unroll
+                for (int k = 0; k < BK / UMMA_K; ++k)
+                  umma::mma_tf32_ss_lohi(d_tm[1], a_lo[1] + soff + 2 * k, b_lo[1] + soff + 2 * k, idesc_m[1], k == 0 ? acc_flag : 1u);
+              }
             }
             acc_flag = 1u;
             umma::tc_commit(&empty[stage]);

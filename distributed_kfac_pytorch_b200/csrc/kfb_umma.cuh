@@ -155,6 +155,10 @@ __host__ __device__ constexpr uint32_t make_idesc_tf32(int m, int n) {
          | (2u << 10)              // B format: TF32
          | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
+// The same for kind::f16: fmt 0 = fp16, 1 = bf16 operands (cute::UMMA::F16F32Format), fp32 accumulate.
+__host__ __device__ constexpr uint32_t make_idesc_f16(int fmt, int m, int n) {
+  return (1u << 4) | ((uint32_t)fmt << 7) | ((uint32_t)fmt << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
 // D[tmem] (+)= A[smem] * B[smem]^T ; one thread issues on behalf of the CTA
 __device__ __forceinline__ void mma_tf32_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
                                             uint32_t accumulate) {
@@ -185,6 +189,21 @@ __device__ __forceinline__ void mma_tf32_ss_lohi(uint32_t d_tmem, uint32_t a_lo,
       "mov.b64 da, {%1, %5};\n\t"
       "mov.b64 db, {%2, %5};\n\t"
       "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %3, p;\n\t"
+      "}" ::"r"(d_tmem),
+      "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(accumulate), "r"(kmajor_sw128_desc_hi())
+      : "memory");
+}
+// kind::f16 (fp16 / bf16 operands, K = 16 per instruction = the same 32 bytes of a tile row)
+__device__ __forceinline__ void mma_f16_ss_lohi(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t idesc,
+                                                uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      ".reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "mov.b64 da, {%1, %5};\n\t"
+      "mov.b64 db, {%2, %5};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, p;\n\t"
       "}" ::"r"(d_tmem),
       "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(accumulate), "r"(kmajor_sw128_desc_hi())
       : "memory");

@@ -405,6 +405,47 @@ def test_half_precision_captures(ops, dtype):
     assert_factor_close(state, O.factor_ema(O.linear_A([a.float()], True), None, 0.95))
 
 
+@pytest.mark.parametrize('dtype', [torch.float16, torch.bfloat16], ids=['fp16', 'bf16'])
+def test_16bit_captures_feed_f16_mmas(monkeypatch, dtype):
+    """AMP captures that TMA can fetch (NCHW / Linear rows) stay 16-bit all the way into shared memory and are
+    multiplied by kind::f16 MMAs: the products are exact, so against the float64 factor of the SAME 16-bit
+    values the error is fp32 accumulation only - fifty times inside the TF32 tolerance.  In place (S % 8 == 0),
+    through the 16-bit copy (14 x 14, 7 x 7 maps), split along K (last-arriver finish), two segments, and rows
+    with a bias; KFB_SYRK_HALF=0 (fp32 staging copies + kind::tf32) must agree within the TF32 tolerance."""
+    N.set_ops(None)
+    o = N.get_ops()
+    o._enter(torch.zeros(1, device=DEV))
+    o.set_mma_mode(1)
+    gen = torch.Generator().manual_seed(5)
+    jobs = []
+    for shape in [(10, 200, 28, 28), (6, 130, 14, 14), (5, 300, 7, 7), (2, 64, 56, 56)]:
+        g = torch.randn(*shape, generator=gen).to(dtype)
+        n, c, h, w = shape
+        S = h * w
+        jobs.append((c, [(N.KFB_SEG_NCHW, g, dict(n=n, c=c, weight=1.0 / (S * S * n * S), h=h, w=w))], O.conv2d_G([g.float()])))
+    g2 = [torch.randn(9, 96, 28, 28, generator=gen).to(dtype), torch.randn(5, 96, 28, 28, generator=gen).to(dtype)]
+    S = 28 * 28
+    jobs.append((96, [(N.KFB_SEG_NCHW, g, dict(n=g.shape[0], c=96, weight=1.0 / (S * S * 14 * S), h=28, w=28)) for g in g2],
+                 O.conv2d_G([g.float() for g in g2])))
+    a = torch.randn(700, 650, generator=gen).to(dtype)
+    jobs.append((651, [(N.KFB_SEG_ROWS, a, dict(n=700, c=650, weight=1.0 / 700, has_bias=True, ld=650))], O.linear_A([a.float()], True)))
+    results = {}
+    for env in ('1', '0'):
+        monkeypatch.setenv('KFB_SYRK_HALF', env)
+        fjobs, states = [], []
+        for d, segs, _ in jobs:
+            st = alloc2d(d, d, DEV)[1]
+            states.append(st)
+            fjobs.append(N.FactorJob(d, [N.Segment(kind, t.to(DEV), **kw) for kind, t, kw in segs], st, True, True, None))
+        o.factor_update(fjobs, 0.95)
+        torch.cuda.synchronize()
+        for st, (d, segs, raw) in zip(states, jobs):
+            assert_factor_close(st, O.factor_ema(raw, None, 0.95), tol=2e-5 if env == '1' else 1e-3)
+        results[env] = [st.clone() for st in states]
+    for x, y in zip(results['1'], results['0']):
+        assert_factor_close(x, y)
+
+
 def test_multi_segment_and_running_average(ops):
     """LinearMultiLayer: sum over calls, each with its own 1/rows; then a second EMA update."""
     gen = torch.Generator().manual_seed(11)
