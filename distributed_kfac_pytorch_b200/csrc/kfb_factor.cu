@@ -323,6 +323,16 @@ __device__ __forceinline__ float pad_load(const T* p, int dtype) {
   return widen16(__ldg(reinterpret_cast<const unsigned short*>(p)), dtype);
 }
 
+// fp32 value that came from a 16-bit capture -> its 16 bits again (exact)
+__device__ __forceinline__ uint32_t narrow16(float v, int dtype) {
+  return dtype == KFB_F16 ? (uint32_t)__half_as_ushort(__float2half_rn(v)) : (__float_as_uint(v) >> 16);
+}
+// four consecutive elements of a 16-bit staging copy (PadJob::out16)
+__device__ __forceinline__ void store4_16(float* dst, size_t e, const float* v, int dtype) {
+  *reinterpret_cast<uint2*>(reinterpret_cast<unsigned short*>(dst) + e) =
+      make_uint2(narrow16(v[0], dtype) | (narrow16(v[1], dtype) << 16), narrow16(v[2], dtype) | (narrow16(v[3], dtype) << 16));
+}
+
 template <typename T>
 __device__ __forceinline__ void pad_quad(const PadJob& p, uint32_t e0) {
   // (plane', y, x) of the first of this thread's four consecutive floats; plane' = plane*kw + kx
@@ -347,7 +357,9 @@ __device__ __forceinline__ void pad_quad(const PadJob& p, uint32_t e0) {
       if (++y == p.hp) { y = 0; if (++kx == p.kw) { kx = 0; img += plane_elems; } }
     }
   }
-  if (e0 + 3 < total) {
+  if (sizeof(T) == 2 && p.out16) {        // total is a multiple of 8 there
+    store4_16(p.dst, e0, v, p.dtype);
+  } else if (e0 + 3 < total) {
     *reinterpret_cast<float4*>(p.dst + e0) = make_float4(v[0], v[1], v[2], v[3]);
   } else {
     for (int i = 0; i < 4 && e0 + i < total; ++i) p.dst[e0 + i] = v[i];
@@ -376,7 +388,8 @@ __device__ __forceinline__ void pad_group(const PadJob& p, uint32_t q) {
     for (int j = 0; j < kSpan; ++j)
       if ((unsigned)(s0 + j) < (unsigned)p.w) v[j] = pad_load(srow + s0 + j, p.dtype);
   }
-  float* out = p.dst + ((size_t)plane * KW * p.hp + y) * p.wp + x0;
+  const size_t out_e = ((size_t)plane * KW * p.hp + y) * p.wp + x0;
+  float* out = p.dst + out_e;
   const size_t plane_stride = (size_t)p.hp * p.wp;
   const int nvalid = p.ow_valid - x0;               // pixels of this group that exist (may be <= 0)
 #pragma unroll
@@ -386,7 +399,12 @@ __device__ __forceinline__ void pad_group(const PadJob& p, uint32_t q) {
     o.y = nvalid > 1 ? v[SX + kx] : 0.f;
     o.z = nvalid > 2 ? v[2 * SX + kx] : 0.f;
     o.w = nvalid > 3 ? v[3 * SX + kx] : 0.f;
-    *reinterpret_cast<float4*>(out + kx * plane_stride) = o;
+    if (sizeof(T) == 2 && p.out16) {
+      const float ov[4] = {o.x, o.y, o.z, o.w};
+      store4_16(p.dst, out_e + kx * plane_stride, ov, p.dtype);
+    } else {
+      *reinterpret_cast<float4*>(out + kx * plane_stride) = o;
+    }
   }
 }
 
@@ -647,13 +665,18 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
         pj.pad_h = ds.ph; pj.pad_w = ds.pw; pj.ow_valid = ds.ow;
         const int64_t images = ds.K / ((int64_t)ds.oh * ds.ow);
         const bool pointwise = ds.kh == 1 && ds.kw == 1;
+        bool keep16 = false;
         if (pointwise) {
           pj.kw = 1; pj.sy = ds.sh; pj.sx = ds.sw;
           pj.hp = ds.oh; pj.wp = ds.ow;
         } else {
           pj.kw = ds.kw; pj.sy = 1; pj.sx = ds.sw;
           pj.hp = (ds.oh - 1) * ds.sh + ds.kh;
-          pj.wp = (ds.ow + 3) / 4 * 4;
+          // a 16-bit capture keeps its type in the planes (eight pixels per 16-byte group) unless the layer has a
+          // bias feature, whose constant the producers write as fp32
+          keep16 = half16 && ds.dtype != KFB_F32 && !ds.has_bias;
+          pj.wp = keep16 ? (ds.ow + 7) / 8 * 8 : (ds.ow + 3) / 4 * 4;
+          pj.out16 = keep16 ? 1 : 0;
         }
         pj.total = images * ds.c * pj.kw * pj.hp * pj.wp;
         magic_div(pj.wp, &pj.mul_wp, &pj.sh_wp);
@@ -671,18 +694,19 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
             images * ds.oh * pj.wp < ((int64_t)1 << 31)) {
           plan->seg_pad.back() = (int)plan->pads.size();
           plan->pad_off.push_back(plan->stage_floats);
-          plan->stage_floats += align_up((size_t)pj.total, 64);
+          plan->stage_floats += align_up((size_t)(keep16 ? (pj.total + 1) / 2 : pj.total), 64);
           plan->pads.push_back(pj);
+          ds.fmt = keep16 ? ds.dtype : 0;
           ds.dtype = KFB_F32;
-          ds.h = pj.hp; ds.w = pj.wp;
+          ds.h = pj.hp; ds.w = keep16 ? pj.wp / 2 : pj.wp;      // 16-bit planes: everything in 4-byte words (fmt)
           ds.ph = ds.pw = 0;
           if (pointwise) {
             ds.sh = ds.sw = 1;
             if (!ds.has_bias) ds.kind = KFB_SEG_NCHW;
           } else {
             ds.nomask = 1;
-            ds.ow_valid = ds.ow;
-            ds.ow = pj.wp;                       // X rows now count padded pixels
+            ds.ow_valid = keep16 ? (ds.ow + 1) / 2 : ds.ow;
+            ds.ow = ds.w;                        // X rows now count padded pixels (pixel pairs)
             ds.K = images * ds.oh * ds.ow;
             ds.sw = 1;                           // the x-stride is applied by the copy
           }

@@ -410,8 +410,8 @@ def test_16bit_captures_feed_f16_mmas(monkeypatch, dtype):
     """AMP captures that TMA can fetch (NCHW / Linear rows) stay 16-bit all the way into shared memory and are
     multiplied by kind::f16 MMAs: the products are exact, so against the float64 factor of the SAME 16-bit
     values the error is fp32 accumulation only - fifty times inside the TF32 tolerance.  In place (S % 8 == 0),
-    through the 16-bit copy (14 x 14, 7 x 7 maps), split along K (last-arriver finish), two segments, and rows
-    with a bias; KFB_SYRK_HALF=0 (fp32 staging copies + kind::tf32) must agree within the TF32 tolerance."""
+    through the 16-bit copy (14 x 14, 7 x 7 maps), split along K (last-arriver finish), two segments, rows
+    with a bias, and k x k convs through 16-bit staging planes; KFB_SYRK_HALF=0 (fp32 staging copies + kind::tf32) must agree within the TF32 tolerance."""
     N.set_ops(None)
     o = N.get_ops()
     o._enter(torch.zeros(1, device=DEV))
@@ -429,6 +429,16 @@ def test_16bit_captures_feed_f16_mmas(monkeypatch, dtype):
                  O.conv2d_G([g.float() for g in g2])))
     a = torch.randn(700, 650, generator=gen).to(dtype)
     jobs.append((651, [(N.KFB_SEG_ROWS, a, dict(n=700, c=650, weight=1.0 / 700, has_bias=True, ld=650))], O.linear_A([a.float()], True)))
+    # k x k convs without a bias: the per-kx staging planes keep the 16-bit type (eight pixels per 16-byte group);
+    # every CONV_CASES geometry without a bias, i.e. odd widths, strides, 7x7 taps, a 7x7 map, K chunks
+    for n, c, h, w, k, st, pd, bias in CONV_CASES:
+        if bias:
+            continue
+        x = torch.randn(n, c, h, w, generator=gen).to(dtype)
+        d, segs = conv_segments(x, k, st, pd, False)
+        sg = segs[0]
+        jobs.append((d, [(N.KFB_SEG_IM2COL, x, dict(n=n, c=c, weight=sg.weight, h=h, w=w, kernel=k, stride=st, padding=pd))],
+                     O.conv2d_A([x.float()], k, st, pd, False)))
     results = {}
     for env in ('1', '0'):
         monkeypatch.setenv('KFB_SYRK_HALF', env)
