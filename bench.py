@@ -276,13 +276,28 @@ class StageTimer(object):
         setattr(ops, name, self)
 
     def __call__(self, *a, **kw):
+        """The window opens when the NATIVE entry point `kfb_<name>` is entered (CudaOps.on_native_call), i.e.
+        after the Python side has marshalled the job array: with the GPU caught up with the host (ordinary steps
+        are 0.37 ms of host work against 0.64 ms of kernels, less margin when the cores are busy or clocked
+        down) an event recorded before the marshalling would count that host time as kernel time."""
         if not self.on:
             return self.inner(*a, **kw)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        out = self.inner(*a, **kw)
+        begin = []
+
+        def hook(entry):
+            if entry == 'kfb_' + self.name and not begin:
+                e = torch.cuda.Event(enable_timing=True)
+                e.record()
+                begin.append(e)
+        prev, self.ops.on_native_call = self.ops.on_native_call, hook
+        try:
+            out = self.inner(*a, **kw)
+        finally:
+            self.ops.on_native_call = prev
+        e1 = torch.cuda.Event(enable_timing=True)
         e1.record()
-        self.pairs.append((e0, e1))
+        if begin:
+            self.pairs.append((begin[0], e1))
         return out
 
     def mean_ms(self):

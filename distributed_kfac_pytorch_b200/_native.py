@@ -235,7 +235,11 @@ class CudaOps(object):
         self._keepalive = None
 
     # -- helpers
+    on_native_call = None      # profiling hook: called with the entry point's name right before the call
+
     def _call(self, name, *args):
+        if self.on_native_call is not None:
+            self.on_native_call(name)
         rc = getattr(self.lib, name)(*args)
         if rc != 0:
             raise NativeError('%s failed (%d): %s' % (name, rc, self.lib.kfb_last_error().decode()))
