@@ -12,5 +12,22 @@ from . import utils
 from . import comm
 from . import layers
 
+
+
+def set_mma_mode(mode):
+    """Precision of the GEMM-shaped kernels, process-wide (no counterpart in the reference, whose math is
+    fp32 throughout): 1 = single-pass TF32 tensor cores (default; inside the parity tolerance), 2 = the same
+    with error-compensated 3xTF32 products in the preconditioning chain (gradients as accurate as fp32, about
+    1 ms more per step on ResNet-50), 0 = exact fp32 FMA, no tensor cores.  Also: environment KFB_MMA_MODE."""
+    from ._native import get_ops
+    get_ops().set_mma_mode(mode)
+
+
+def get_mma_mode():
+    from ._native import get_ops
+    return get_ops().get_mma_mode()
+
+
 __version__ = '0.1.0'
-__all__ = ['KFAC', 'CommMethod', 'KFACParamScheduler', 'modules', 'utils', 'comm', 'layers']
+__all__ = ['KFAC', 'CommMethod', 'KFACParamScheduler', 'modules', 'utils', 'comm', 'layers', 'set_mma_mode',
+           'get_mma_mode']

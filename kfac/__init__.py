@@ -4,8 +4,8 @@ reference's example scripts (``kfac.KFAC``, ``kfac.CommMethod``, ``kfac.comm.bac
 import sys as _sys
 
 import distributed_kfac_pytorch_b200 as _impl
-from distributed_kfac_pytorch_b200 import (KFAC, CommMethod, KFACParamScheduler, comm, layers,
-                                           modules, utils)
+from distributed_kfac_pytorch_b200 import (KFAC, CommMethod, KFACParamScheduler, comm, get_mma_mode, layers,
+                                           modules, set_mma_mode, utils)
 
 for _name in ('comm', 'layers', 'modules', 'utils', 'preconditioner', 'scheduler'):
     _sys.modules[__name__ + '.' + _name] = getattr(_impl, _name)
@@ -14,4 +14,5 @@ _sys.modules[__name__ + '.layers.utils'] = _impl.layers.utils
 for _sub in ('base', 'conv', 'linear', 'embedding'):
     _sys.modules[__name__ + '.layers.' + _sub] = getattr(_impl.layers, _sub)
 
-__all__ = ['KFAC', 'CommMethod', 'KFACParamScheduler', 'comm', 'layers', 'modules', 'utils']
+__all__ = ['KFAC', 'CommMethod', 'KFACParamScheduler', 'comm', 'layers', 'modules', 'utils', 'set_mma_mode',
+           'get_mma_mode']
