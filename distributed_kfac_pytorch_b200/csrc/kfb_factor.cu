@@ -672,9 +672,8 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
         } else {
           pj.kw = ds.kw; pj.sy = 1; pj.sx = ds.sw;
           pj.hp = (ds.oh - 1) * ds.sh + ds.kh;
-          // a 16-bit capture keeps its type in the planes (eight pixels per 16-byte group) unless the layer has a
-          // bias feature, whose constant the producers write as fp32
-          keep16 = half16 && ds.dtype != KFB_F32 && !ds.has_bias;
+          // a 16-bit capture keeps its type in the planes (eight pixels per 16-byte group)
+          keep16 = half16 && ds.dtype != KFB_F32;
           pj.wp = keep16 ? (ds.ow + 7) / 8 * 8 : (ds.ow + 3) / 4 * 4;
           pj.out16 = keep16 ? 1 : 0;
         }
@@ -705,7 +704,7 @@ int plan_factor(const kfb_factor_job* jobs, int n_jobs, int num_sms, bool allow_
             if (!ds.has_bias) ds.kind = KFB_SEG_NCHW;
           } else {
             ds.nomask = 1;
-            ds.ow_valid = keep16 ? (ds.ow + 1) / 2 : ds.ow;
+            ds.ow_valid = ds.ow;                 // in PIXELS also for 16-bit planes (two per word)
             ds.ow = ds.w;                        // X rows now count padded pixels (pixel pairs)
             ds.K = images * ds.oh * ds.ow;
             ds.sw = 1;                           // the x-stride is applied by the copy

@@ -520,8 +520,14 @@ __global__ void __launch_bounds__(Cfg<kPair>::kThreads, 1) syrk_tc_kernel(const 
               const uint32_t nb_ = fast_div(kb, s.mul_s, s.sh_s);
               const uint32_t rb = kb - nb_ * uS;
               const uint32_t xb = rb - fast_div(rb, s.mul_w, s.sh_w) * uow;
-              sts_f32(st + bias_slot * kTileBytes + bias_row * 128 + (uint32_t)((((lane >> 2) ^ (bias_row & 7)) << 4) | ((lane & 3) << 2)),
-                      (kb < k_end32 && xb < (uint32_t)s.ow_valid) ? 1.f : 0.f);
+              float one = (kb < k_end32 && xb < (uint32_t)s.ow_valid) ? 1.f : 0.f;
+              if (s.fmt) {
+                // 16-bit planes: a word is two pixels of the row; ow_valid counts PIXELS here
+                const uint32_t h1 = s.fmt == KFB_F16 ? 0x3C00u : 0x3F80u;
+                const uint32_t p0 = 2u * xb;
+                one = __uint_as_float(kb < k_end32 ? ((p0 < (uint32_t)s.ow_valid ? h1 : 0u) | (p0 + 1u < (uint32_t)s.ow_valid ? h1 << 16 : 0u)) : 0u);
+              }
+              sts_f32(st + bias_slot * kTileBytes + bias_row * 128 + (uint32_t)((((lane >> 2) ^ (bias_row & 7)) << 4) | ((lane & 3) << 2)), one);
               umma::fence_proxy_async_smem();
             }
             cp_async_arrive(full_a + 8 * stage);

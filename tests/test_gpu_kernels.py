@@ -429,16 +429,15 @@ def test_16bit_captures_feed_f16_mmas(monkeypatch, dtype):
                  O.conv2d_G([g.float() for g in g2])))
     a = torch.randn(700, 650, generator=gen).to(dtype)
     jobs.append((651, [(N.KFB_SEG_ROWS, a, dict(n=700, c=650, weight=1.0 / 700, has_bias=True, ld=650))], O.linear_A([a.float()], True)))
-    # k x k convs without a bias: the per-kx staging planes keep the 16-bit type (eight pixels per 16-byte group);
-    # every CONV_CASES geometry without a bias, i.e. odd widths, strides, 7x7 taps, a 7x7 map, K chunks
+    # k x k convs: the per-kx staging planes keep the 16-bit type (eight pixels per 16-byte group); every
+    # CONV_CASES geometry: odd widths, strides, 7x7 taps, a 7x7 map, K chunks, bias features (two 16-bit ones per word)
     for n, c, h, w, k, st, pd, bias in CONV_CASES:
-        if bias:
-            continue
         x = torch.randn(n, c, h, w, generator=gen).to(dtype)
-        d, segs = conv_segments(x, k, st, pd, False)
+        d, segs = conv_segments(x, k, st, pd, bias)
         sg = segs[0]
-        jobs.append((d, [(N.KFB_SEG_IM2COL, x, dict(n=n, c=c, weight=sg.weight, h=h, w=w, kernel=k, stride=st, padding=pd))],
-                     O.conv2d_A([x.float()], k, st, pd, False)))
+        jobs.append((d, [(N.KFB_SEG_IM2COL, x, dict(n=n, c=c, weight=sg.weight, has_bias=bias, h=h, w=w, kernel=k, stride=st,
+                                                    padding=pd))],
+                     O.conv2d_A([x.float()], k, st, pd, bias)))
     results = {}
     for env in ('1', '0'):
         monkeypatch.setenv('KFB_SYRK_HALF', env)
