@@ -417,6 +417,11 @@ __device__ __forceinline__ void pad_transpose(const PadJob& p, uint32_t e0) {
   const uint32_t n = row - c * (uint32_t)p.hp;
   const T* srow = reinterpret_cast<const T*>(p.src) + ((size_t)n * p.channels + c) * p.ow_valid;
   if (sizeof(T) == 2 && p.out16) {        // the copy keeps the 16-bit type: raw bits, zero padding
+    const unsigned short* s16 = reinterpret_cast<const unsigned short*>(srow) + x0;
+    if (x0 + 3 < p.ow_valid && (((uintptr_t)s16) & 7) == 0) {         // four whole pixels in one 8-byte load
+      *reinterpret_cast<uint2*>(reinterpret_cast<unsigned short*>(p.dst) + e0) = __ldg(reinterpret_cast<const uint2*>(s16));
+      return;
+    }
     unsigned short u[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) u[i] = x0 + i < p.ow_valid ? __ldg(reinterpret_cast<const unsigned short*>(srow) + x0 + i) : (unsigned short)0;
