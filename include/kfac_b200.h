@@ -88,8 +88,9 @@ typedef struct kfb_segment {
   int64_t ld;            /* ROWS: row pitch in elements */
   float weight;          /* e.g. 1/(N*S^3) for conv, 1/M for linear */
   int32_t dtype;         /* element type of `data`: KFB_F32 (0), KFB_F16 (1) or KFB_BF16 (2).  16-bit captures
-                            (AMP autocast activations / output gradients) are widened to fp32 as they are
-                            gathered; accumulation and the factor stay fp32 */
+                            (AMP autocast activations / output gradients) are multiplied as they are, by
+                            16-bit tensor-core instructions with exact products (or widened to fp32 where
+                            that path does not apply); accumulation and the factor stay fp32 */
   const float* dev_scale; /* NULL, or a DEVICE float that multiplies `weight` when the kernels run; 0 drops the
                             segment altogether (its data may then hold inf / nan).  Written by
                             kfb_capture_filter: the GradScaler handling of kfac/layers/base.py:397-407
